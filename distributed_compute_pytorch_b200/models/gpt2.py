@@ -1,0 +1,82 @@
+"""GPT-2 small (north-star config ``BASELINE.json:configs[4]``: DDP bf16, seq 1024, large gradient
+buckets fused with the optimizer step; not part of the reference).  124,439,808 parameters with the
+LM head tied to the token embedding.  Linear layers run the tcgen05 GEMM; attention uses the
+library SDPA kernel (attention is not among the north-star's hand-written ops)."""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+from .. import ops
+
+
+@dataclass
+class GPT2Config:
+    vocab_size: int = 50257
+    n_positions: int = 1024
+    n_embd: int = 768
+    n_layer: int = 12
+    n_head: int = 12
+
+
+class Block(nn.Module):
+    def __init__(self, cfg: GPT2Config):
+        super().__init__()
+        self.ln_1 = nn.LayerNorm(cfg.n_embd)
+        self.attn_qkv = ops.Linear(cfg.n_embd, 3 * cfg.n_embd)
+        self.attn_proj = ops.Linear(cfg.n_embd, cfg.n_embd)
+        self.ln_2 = nn.LayerNorm(cfg.n_embd)
+        self.mlp_fc = ops.Linear(cfg.n_embd, 4 * cfg.n_embd)
+        self.mlp_proj = ops.Linear(4 * cfg.n_embd, cfg.n_embd)
+        self.n_head = cfg.n_head
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B, T, C = x.shape
+        qkv = self.attn_qkv(self.ln_1(x).view(B * T, C)).view(B, T, 3, self.n_head, C // self.n_head)
+        q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))
+        y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+        y = y.transpose(1, 2).reshape(B * T, C)
+        x = x + self.attn_proj(y).view(B, T, C)
+        h = F.gelu(self.mlp_fc(self.ln_2(x).view(B * T, C)), approximate="tanh")
+        return x + self.mlp_proj(h).view(B, T, C)
+
+
+class GPT2(nn.Module):
+    def __init__(self, cfg: GPT2Config = GPT2Config()):
+        super().__init__()
+        self.cfg = cfg
+        self.wte = nn.Embedding(cfg.vocab_size, cfg.n_embd)
+        self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
+        self.h = nn.ModuleList(Block(cfg) for _ in range(cfg.n_layer))
+        self.ln_f = nn.LayerNorm(cfg.n_embd)
+        self.apply(self._init)
+        for n, p in self.named_parameters():
+            if n.endswith("proj.weight"):
+                nn.init.normal_(p, mean=0.0, std=0.02 / math.sqrt(2 * cfg.n_layer))
+
+    @staticmethod
+    def _init(m):
+        if isinstance(m, (nn.Linear, nn.Embedding)):
+            nn.init.normal_(m.weight, mean=0.0, std=0.02)
+            if isinstance(m, nn.Linear) and m.bias is not None:
+                nn.init.zeros_(m.bias)
+
+    def forward(self, idx: torch.Tensor, targets: torch.Tensor = None):
+        B, T = idx.shape
+        pos = torch.arange(T, device=idx.device)
+        x = self.wte(idx) + self.wpe(pos)
+        for blk in self.h:
+            x = blk(x)
+        x = self.ln_f(x)
+        if x.is_cuda:
+            from ..ops import cuda
+            logits = cuda.linear(x.view(B * T, -1), self.wte.weight, None, False)
+        else:
+            logits = F.linear(x.view(B * T, -1), self.wte.weight)
+        if targets is None:
+            return logits.view(B, T, -1)
+        return ops.cross_entropy(logits.float() if not logits.is_cuda else logits, targets.reshape(-1))

@@ -1,0 +1,150 @@
+"""Reference-compatible DDP MNIST example on the B200-native framework.
+
+Same flags, prints, loops and checkpoint as /root/reference/main.py (ref:main.py:55-156), running on
+``distributed_compute_pytorch_b200`` instead of torch.distributed / torch DDP.  Deliberate deviations
+(SURVEY.md section 9): CPU runs use ``torch.device('cpu')`` instead of crashing on ``.to(rank)``; the
+model is DDP-wrapped whenever world_size > 1; only rank 0 writes ``mnist.pt`` (followed by a barrier);
+``--no-cuda`` really selects the CPU; data is synthetic MNIST-shaped unless ``--data mnist`` finds
+the files locally (there is no network to download them, ref:main.py:107).
+"""
+import argparse
+import os
+import time
+
+import torch
+from torch.utils.data import DataLoader
+
+import distributed_compute_pytorch_b200 as dist
+from distributed_compute_pytorch_b200 import DistributedDataParallel, DistributedSampler, ops
+from distributed_compute_pytorch_b200.models import ConvNet
+from distributed_compute_pytorch_b200.utils import SyntheticMNIST
+
+
+def setup(rank, world_size, backend=None):
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")   # ref:main.py:48 uses "localhost"
+    os.environ.setdefault("MASTER_PORT", "12355")       # ref:main.py:49
+    dist.init_process_group(backend, rank=rank, world_size=world_size)
+
+
+def cleanup():
+    dist.destroy_process_group()
+
+
+def train(opt, model, rank, train_loader, optimizer, epoch, device=None):
+    device = rank if device is None else device
+    model.train()
+    for b, (img, label) in enumerate(train_loader):
+        img, label = img.to(device), label.to(device)
+        optimizer.zero_grad()
+        out = model(img)
+        loss = ops.nll_loss(out, label)
+        loss.backward()
+        optimizer.step()
+        if b % 10 == 0:
+            dist.all_reduce(loss, op=dist.ReduceOp.SUM)
+            if rank == 0:
+                print(f"epoch: {epoch} [{b}/{len(train_loader)} \
+          ({100. * b/len(train_loader)}%)]\t Loss:{loss.item()}")
+        if opt.max_steps and b + 1 >= opt.max_steps:
+            break
+
+
+def test(opt, model, rank, test_loader, optimizer, epoch, device=None):
+    device = rank if device is None else device
+    model.eval()
+    test_loss_tensor = torch.zeros((), device=device)
+    correct_tensor = torch.zeros((), dtype=torch.int64, device=device)
+    datalen = 0
+    with torch.no_grad():
+        for b, (img, label) in enumerate(test_loader):
+            img, label = img.to(device), label.to(device)
+            out = model(img)
+            # device-side accumulation: no per-batch host sync (the reference does two, ref:main.py:81-85)
+            test_loss_tensor += ops.nll_loss(out, label, reduction='sum')
+            correct_tensor += ops.correct_count(out, label)
+            datalen += len(img)
+            if opt.max_steps and b + 1 >= opt.max_steps:
+                break
+    dist.all_reduce(test_loss_tensor, op=dist.ReduceOp.SUM)
+    dist.all_reduce(correct_tensor, op=dist.ReduceOp.SUM)
+    if rank == 0:
+        n = len(test_loader.dataset)
+        print('\nTest set: Average loss: {:.4f}, Accuracy: {}/{} ({:.0f}%)\n'.format(
+            test_loss_tensor.item(), correct_tensor.item(), n, 100. * correct_tensor.item() / n))
+    return test_loss_tensor, correct_tensor
+
+
+def make_dataset(opt, train=True):
+    if opt.data == "mnist":
+        from torchvision import datasets, transforms
+        return datasets.MNIST('./data/', train=train, download=False, transform=transforms.Compose(
+            [transforms.ToTensor(), transforms.Normalize((0.1307,), (0.3081,))]))
+    return SyntheticMNIST(opt.data_size if train else max(opt.data_size // 6, 1), seed=1234 if train else 4321)
+
+
+def proc(rank, world_size, opt, use_cuda):
+    print(f"running DDP example on rank {rank}")
+    setup(rank, world_size, opt.backend)
+
+    torch.manual_seed(0)
+    device = torch.device('cuda', rank % max(torch.cuda.device_count(), 1)) if use_cuda else torch.device('cpu')
+    if use_cuda:
+        torch.cuda.set_device(device)
+
+    train_dataset = make_dataset(opt, True)
+    train_sampler = DistributedSampler(train_dataset, num_replicas=world_size, rank=rank)
+    train_loader = DataLoader(train_dataset, batch_size=opt.batch_size, shuffle=False,
+                              num_workers=0, pin_memory=use_cuda, sampler=train_sampler)
+    test_dataset = make_dataset(opt, False)
+    test_sampler = DistributedSampler(test_dataset, num_replicas=world_size, rank=rank)
+    test_loader = DataLoader(test_dataset, batch_size=opt.batch_size, shuffle=False, sampler=test_sampler)  # noqa: F841 (unused in the reference too)
+
+    model = ConvNet().to(device)
+    if world_size > 1:
+        model = DistributedDataParallel(model, device_ids=[device.index] if use_cuda else None)
+
+    optimizer = ops.Adadelta(model.parameters(), lr=opt.lr)
+    scheduler = ops.StepLR(optimizer, step_size=1, gamma=opt.gamma)
+
+    for epoch in range(opt.epochs):
+        t0 = time.time()
+        train(opt, model, rank, train_loader, optimizer, epoch, device)
+        test(opt, model, rank, train_loader, optimizer, epoch, device)   # the reference evaluates on the train loader (ref:main.py:130)
+        scheduler.step()
+        print(f"time to complete this epoch: {time.time() - t0} seconds")
+    if rank == 0:
+        torch.save(model.state_dict(), opt.checkpoint)
+    dist.barrier()
+    cleanup()
+
+
+def _str2bool(v):
+    return str(v).lower() in ("1", "true", "yes", "y", "")
+
+
+def build_parser():
+    parser = argparse.ArgumentParser()
+    parser.add_argument('--batch_size', type=int, default=128, help="batch size of train and test")
+    parser.add_argument('--lr', type=float, default=0.001, help="LR of optimizer")
+    parser.add_argument('--epochs', type=int, default=20, help="#of epochs")
+    parser.add_argument('--no-cuda', nargs='?', const=True, default=False, type=_str2bool, help="disables CUDA if True")
+    parser.add_argument('--gamma', default=0.7, type=float, help="gamma value for lr update")
+    parser.add_argument('--gpus', default=4, type=int, help="# of GPUs")
+    # additions (not in the reference)
+    parser.add_argument('--data', default="synthetic", choices=["synthetic", "mnist"])
+    parser.add_argument('--data-size', type=int, default=60000, help="synthetic train-set size")
+    parser.add_argument('--backend', default=None, help="gloo|nccl|b200|cpu (default: GPU backend iff CUDA)")
+    parser.add_argument('--max-steps', type=int, default=0, help="stop each epoch pass after this many batches (0 = all)")
+    parser.add_argument('--checkpoint', default="mnist.pt")
+    return parser
+
+
+def main(argv=None):
+    opt = build_parser().parse_args(argv)
+    use_cuda = not opt.no_cuda and torch.cuda.is_available()
+    world_size = min(opt.gpus, torch.cuda.device_count()) if use_cuda else 2
+    dist.spawn(proc, args=(world_size, opt, use_cuda), nprocs=world_size, join=True)
+
+
+if __name__ == '__main__':
+    main()

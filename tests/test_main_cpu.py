@@ -1,0 +1,39 @@
+"""BASELINE.json configs[0]: main.py small CNN DDP on synthetic MNIST-shaped data, world_size=2 on
+CPU - runs to completion, ranks hold identical params, mnist.pt keys match the reference's."""
+import os
+import subprocess
+import sys
+
+import torch
+
+import main as app
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_cli_flags_match_reference():
+    opt = app.build_parser().parse_args([])
+    assert (opt.batch_size, opt.lr, opt.epochs, opt.gamma, opt.gpus, opt.no_cuda) == (128, 0.001, 20, 0.7, 4, False)
+    assert app.build_parser().parse_args(["--no-cuda", "True"]).no_cuda is True
+    assert app.build_parser().parse_args(["--no-cuda", "False"]).no_cuda is False  # the reference treats 'False' as truthy
+
+
+def test_main_world2_cpu(tmp_path, free_port):
+    env = dict(os.environ, MASTER_PORT=str(free_port), MASTER_ADDR="127.0.0.1", PYTHONPATH=ROOT)
+    ck = tmp_path / "mnist.pt"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "main.py"), "--epochs", "2", "--batch_size", "16", "--data-size", "256",
+                        "--no-cuda", "True", "--checkpoint", str(ck), "--lr", "1.0"],
+                       capture_output=True, text=True, timeout=600, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = r.stdout
+    assert "running DDP example on rank 0" in out and "running DDP example on rank 1" in out
+    assert "epoch: 0 [0/8" in out and "Loss:" in out
+    assert "Test set: Average loss:" in out and "Accuracy:" in out
+    assert out.count("time to complete this epoch:") == 4  # every rank, every epoch
+    sd = torch.load(ck)
+    expect = ["module." + k for k in ("conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias", "fc1.weight", "fc1.bias",
+                                      "fc2.weight", "fc2.bias", "batchnorm.weight", "batchnorm.bias", "batchnorm.running_mean",
+                                      "batchnorm.running_var", "batchnorm.num_batches_tracked")]
+    assert list(sd.keys()) == expect
+    assert tuple(sd["module.fc1.weight"].shape) == (128, 9216) and sd["module.batchnorm.num_batches_tracked"].item() == 16
+    assert hasattr(sd, "_metadata")
