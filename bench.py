@@ -1,0 +1,279 @@
+"""Headline benchmark: images/sec of the reference model's DDP training step (BASELINE.json metric;
+BASELINE.md row 2: ConvNet, synthetic MNIST shape [B,1,28,28], batch 128/GPU, fp32, weak scaling).
+
+    python bench.py --gpus N --steps K --warmup W                  # this framework
+    python bench.py --impl reference --gpus N --steps K --warmup W # unmodified reference (baseline/_ref) on torch DDP + NCCL
+
+For N > 1 launch under torchrun (one rank per GPU); without torchrun env the script spawns its own ranks.
+One JSON line on rank 0.  `value` = device-timed steps on device-resident inputs (CUDA events, barrier +
+synchronize on both sides, max over ranks); `e2e` = the same metric through the public API including, every
+step, the H2D copy of the step's inputs from pinned host memory and a D2H read of the loss.
+"""
+import argparse
+import contextlib
+import importlib.util
+import io
+import json
+import os
+import sys
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+POOL_BATCHES = 512  # rotating input pool: 512 x 128 x 784 x 4 B = 205 MB > 126 MB L2
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (the reference's --batch_size default, ref:main.py:139)")
+    ap.add_argument("--lr", type=float, default=0.001)
+    ap.add_argument("--no-graph", action="store_true", help="ours: eager DDP path instead of the CUDA-graph step")
+    return ap.parse_args()
+
+
+def env_rank():
+    if "RANK" in os.environ and "WORLD_SIZE" in os.environ:
+        return int(os.environ["RANK"]), int(os.environ.get("LOCAL_RANK", os.environ["RANK"])), int(os.environ["WORLD_SIZE"])
+    return None
+
+
+def make_pool(batch, device, pinned, seed):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(POOL_BATCHES, batch, 1, 28, 28, generator=g)
+    y = torch.randint(0, 10, (POOL_BATCHES, batch), generator=g)
+    if pinned:
+        return x.pin_memory(), y.pin_memory()
+    return x.to(device), y.to(device)
+
+
+def max_over_ranks(val, device, dist_mod, world):
+    if world == 1:
+        return val
+    t = torch.tensor([val], dtype=torch.float64, device=device)
+    dist_mod.all_reduce(t, op=dist_mod.ReduceOp.MAX)
+    return t.item()
+
+
+# ----------------------------------------------------------------------------------------- ours ----
+def run_ours(opt, rank, local_rank, world):
+    import distributed_compute_pytorch_b200 as dcp
+    from distributed_compute_pytorch_b200 import ops
+    from distributed_compute_pytorch_b200.models import ConvNet
+    from distributed_compute_pytorch_b200.ops import cuda as K
+    from distributed_compute_pytorch_b200.parallel.engine import GraphedTrainStep
+    from distributed_compute_pytorch_b200.utils import ClockSampler
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29533")
+    dcp.init_process_group("nccl", rank=rank, world_size=world, device_id=local_rank)
+    be = dcp.distributed._world().cuda
+    torch.manual_seed(0)
+    model = ConvNet().to(dev)
+    if world > 1:
+        model = dcp.DistributedDataParallel(model, device_ids=[local_rank])
+    optimizer = ops.Adadelta(model.parameters(), lr=opt.lr)
+    model.train()
+    xs, ys = make_pool(opt.batch, dev, pinned=False, seed=100 + rank)
+    hx, hy = make_pool(opt.batch, dev, pinned=True, seed=100 + rank)
+
+    if opt.no_graph:
+        def step(x, y):
+            optimizer.zero_grad()
+            loss = ops.nll_loss(model(x.to(dev, non_blocking=True)), y.to(dev, non_blocking=True))
+            loss.backward()
+            optimizer.step()
+            return loss.detach()
+        per_step = None
+    else:
+        step = GraphedTrainStep(model, optimizer, lambda o, t: ops.nll_loss(o, t), xs[0], ys[0], device=dev)
+        per_step = step.launches_per_step
+
+    def timed(pool_x, pool_y, nsteps, read_loss):
+        loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        dcp.barrier(); torch.cuda.synchronize()
+        l0 = K.launch_count + be.launches
+        t0 = time.perf_counter()
+        start.record()
+        last = 0.0
+        for i in range(nsteps):
+            loss = step(pool_x[i % POOL_BATCHES], pool_y[i % POOL_BATCHES])
+            if read_loss:
+                loss_host.copy_(loss, non_blocking=True)
+                torch.cuda.current_stream().synchronize()
+                last = float(loss_host)
+        end.record()
+        dcp.barrier(); torch.cuda.synchronize()
+        wall = time.perf_counter() - t0
+        eager_launches = K.launch_count + be.launches - l0
+        return start.elapsed_time(end), wall, last, eager_launches
+
+    timed(xs, ys, opt.warmup, False)
+    with ClockSampler(local_rank) as clocks:
+        ms, wall, _, eager_l = timed(xs, ys, opt.steps, False)
+    timed(hx, hy, max(3, opt.warmup // 2), True)
+    ms_e2e, wall_e2e, last_loss, _ = timed(hx, hy, opt.steps, True)
+    ms = max_over_ranks(ms, dev, dcp, world)
+    ms_e2e = max_over_ranks(ms_e2e, dev, dcp, world)
+    gb = opt.batch * world
+    launches = per_step * opt.steps if per_step is not None else eager_l
+    rec = {
+        "metric": "images/sec", "value": gb * opt.steps / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": opt.steps,
+        "warmup": opt.warmup, "ms_per_step": ms / opt.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp32 (tf32 tensor-core multiply where tcgen05 kernels are used, the precision cuDNN's default gives the reference)",
+        "data": "synthetic MNIST-shaped [B,1,28,28] float32 + int64 labels, random-init weights", "impl": "ours",
+        "config": {"model": "ConvNet (ref:main.py:20-45)", "global_batch": gb, "per_gpu_batch": opt.batch, "seq_len": None,
+                   "parallelism": f"dp{world}", "optimizer": "Adadelta lr=0.001", "graph": not opt.no_graph,
+                   "l2": f"inputs larger than L2: rotating pool of {POOL_BATCHES} batches ({POOL_BATCHES * opt.batch * 784 * 4 / 1e6:.0f} MB)",
+                   "nvls": be.nvls},
+        "clocks": clocks.summary(),
+        "e2e": {"value": gb * opt.steps / (ms_e2e / 1e3), "unit": "images/s", "ms_per_step": ms_e2e / opt.steps,
+                "h2d_bytes_per_step": opt.batch * 784 * 4 + opt.batch * 8, "d2h_bytes_per_step": 4, "wall_ms_per_step": wall_e2e * 1e3 / opt.steps,
+                "last_loss": last_loss},
+        "gpu_launches": launches, "wall_ms_per_step": wall * 1e3 / opt.steps,
+    }
+    if rank == 0:
+        print(json.dumps(rec), flush=True)
+    dcp.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------ reference ----
+def load_reference():
+    ref_main = os.path.join(ROOT, "baseline", "_ref", "main.py")
+    if not os.path.exists(ref_main):
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        try:
+            import install_ref
+            with contextlib.redirect_stdout(io.StringIO()):
+                install_ref.install()
+        except Exception:
+            pass
+    if not os.path.exists(ref_main):
+        return None, "baseline/_ref/main.py missing and /root/reference not reachable from this box"
+    try:
+        spec = importlib.util.spec_from_file_location("reference_main", ref_main)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return mod, None
+    except Exception as e:  # e.g. torchvision missing
+        return None, f"importing the reference failed: {type(e).__name__}: {e}"
+
+
+class _Loader:
+    """Stands in for the MNIST DataLoader (no network): yields `n` (img, label) batches from a pool."""
+
+    def __init__(self, xs, ys, n):
+        self.xs, self.ys, self.n = xs, ys, n
+        self.dataset = range(n * xs.shape[1])
+
+    def __len__(self):
+        return self.n
+
+    def __iter__(self):
+        for i in range(self.n):
+            yield self.xs[i % POOL_BATCHES], self.ys[i % POOL_BATCHES]
+
+
+def run_reference(opt, rank, local_rank, world):
+    ref, why = load_reference()
+    if ref is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference", "unavailable": why}), flush=True)
+        return
+    import torch.distributed as tdist
+    from torch import optim
+    from distributed_compute_pytorch_b200.utils import ClockSampler
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29534")
+    # deviation 1: the reference hard-codes "gloo" (ref:main.py:50); the bar is its NCCL build
+    tdist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    torch.manual_seed(0)                                   # ref:main.py:103
+    model = ref.ConvNet().to(local_rank)                   # ref:main.py:118
+    if torch.cuda.device_count() > 1:                      # ref:main.py:119
+        model = ref.DistributedDataParallel(model, device_ids=[local_rank])   # ref:main.py:122
+    optimizer = optim.Adadelta(model.parameters(), lr=opt.lr)                 # ref:main.py:124
+    xs, ys = make_pool(opt.batch, dev, pinned=False, seed=100 + rank)
+    hx, hy = make_pool(opt.batch, dev, pinned=True, seed=100 + rank)
+    ns = argparse.Namespace(batch_size=opt.batch, lr=opt.lr)
+
+    def timed(pool_x, pool_y, nsteps):
+        loader = _Loader(pool_x, pool_y, nsteps)
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tdist.barrier(); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        start.record()
+        with contextlib.redirect_stdout(io.StringIO()):    # the reference prints a loss line every 10 batches
+            ref.train(ns, model, local_rank, loader, optimizer, 0)      # the reference's own hot loop, ref:main.py:55-68
+        end.record()
+        tdist.barrier(); torch.cuda.synchronize()
+        return start.elapsed_time(end), time.perf_counter() - t0
+
+    def maxr(v):
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+        return t.item()
+
+    timed(xs, ys, opt.warmup)
+    with ClockSampler(local_rank) as clocks:
+        ms, wall = timed(xs, ys, opt.steps)
+    timed(hx, hy, max(3, opt.warmup // 2))
+    ms_e2e, wall_e2e = timed(hx, hy, opt.steps)
+    ms, ms_e2e = maxr(ms), maxr(ms_e2e)
+    gb = opt.batch * world
+    rec = {
+        "metric": "images/sec", "value": gb * opt.steps / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": opt.steps,
+        "warmup": opt.warmup, "ms_per_step": ms / opt.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "fp32 (cuDNN default allow_tf32 for conv)", "data": "synthetic MNIST-shaped [B,1,28,28] float32 + int64 labels, random-init weights",
+        "impl": "reference",
+        "config": {"model": "ConvNet (baseline/_ref/main.py, unmodified)", "global_batch": gb, "per_gpu_batch": opt.batch, "seq_len": None,
+                   "parallelism": f"dp{world}", "optimizer": "torch.optim.Adadelta lr=0.001", "stack": "reference train() + torch DDP + NCCL + cuDNN/cuBLAS",
+                   "deviations": "backend gloo->nccl; MNIST files -> synthetic tensors",
+                   "l2": f"inputs larger than L2: rotating pool of {POOL_BATCHES} batches"},
+        "clocks": clocks.summary(),
+        "e2e": {"value": gb * opt.steps / (ms_e2e / 1e3), "unit": "images/s", "ms_per_step": ms_e2e / opt.steps,
+                "h2d_bytes_per_step": opt.batch * 784 * 4 + opt.batch * 8, "d2h_bytes_per_step": 0.4,
+                "note": "reference reads the loss on rank 0 every 10th batch (ref:main.py:64-68)", "wall_ms_per_step": wall_e2e * 1e3 / opt.steps},
+        "gpu_launches": 0, "wall_ms_per_step": wall * 1e3 / opt.steps,
+    }
+    if rank == 0:
+        print(json.dumps(rec), flush=True)
+    tdist.destroy_process_group()
+
+
+def _entry(rank, world, port, opt):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"] = str(rank), str(rank), str(world)
+    (run_reference if opt.impl == "reference" else run_ours)(opt, rank, rank, world)
+
+
+def main():
+    opt = parse()
+    er = env_rank()
+    if er is not None:
+        rank, local_rank, world = er
+        (run_reference if opt.impl == "reference" else run_ours)(opt, rank, local_rank, world)
+        return
+    if opt.gpus <= 1:
+        os.environ.setdefault("MASTER_PORT", str(29500 + os.getpid() % 400))
+        (run_reference if opt.impl == "reference" else run_ours)(opt, 0, 0, 1)
+        return
+    import socket
+    import distributed_compute_pytorch_b200 as dcp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]
+    dcp.spawn(_entry, args=(opt.gpus, port, opt), nprocs=opt.gpus, join=True)
+
+
+if __name__ == "__main__":
+    main()

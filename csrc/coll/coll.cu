@@ -1,0 +1,527 @@
+// Hand-written NVLink collectives for sm_100a: every kernel reads / writes peer GPUs' memory directly
+// through the symmetric heap (csrc/symm) - no NCCL, no host staging (the reference's gloo backend
+// bounces CUDA tensors through pinned host memory, ref:main.py:50; its NCCL baseline uses ncclComm).
+//
+//   all_reduce  one-shot  : push own copy into every peer's slot, one signal, reduce locally (latency floor)
+//               two-shot  : pull-reduce own 1/W slice from all peers, push the result to all peers
+//               NVLS      : multimem.ld_reduce (in-switch reduction) + multimem.st (in-switch broadcast)
+//   broadcast, all_gather, reduce_scatter, reduce, gather, scatter, send/recv, barrier
+//
+// Cross-rank ordering uses per-CTA signal words with monotonically increasing epochs (common.cuh),
+// so nothing is ever reset and every kernel can be captured in a CUDA graph and replayed.
+// Staged (non-symmetric tensor) variants double-buffer the bounce area on a per-CTA call counter, which
+// removes the trailing barrier: a rank can only be two calls ahead of a peer after that peer has
+// finished reading the older half.
+#include <type_traits>
+
+#include "coll/coll_common.cuh"
+
+namespace {
+
+constexpr int kThreads = 512;
+
+struct Span { size_t begin, end; };  // vector index range
+
+__device__ __forceinline__ Span rank_slice(size_t nvec, int world, int r) {
+  size_t per = (nvec + world - 1) / world;
+  size_t b = per * r; if (b > nvec) b = nvec;
+  size_t e = b + per; if (e > nvec) e = nvec;
+  return {b, e};
+}
+
+__device__ __forceinline__ uint32_t call_parity(const DcpDevCtx& c, int chan) {
+  return *((volatile uint32_t*)dcp_calls(c.peer[c.rank], chan, blockIdx.x)) & 1u;
+}
+__device__ __forceinline__ void call_advance(const DcpDevCtx& c, int chan) {
+  // caller guarantees a __syncthreads() between the parity read and this
+  if (threadIdx.x == 0) { volatile uint32_t* p = dcp_calls(c.peer[c.rank], chan, blockIdx.x); *p = *p + 1; }
+}
+
+// -------------------------------------------------------------------------------------------------
+// all_reduce, one-shot push.  slot layout in the one-shot region: [half][src rank][slot_bytes].
+// -------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_allreduce_oneshot(DcpDevCtx c, const T* __restrict__ in, T* __restrict__ out, size_t n,
+                                                                 float scale, int op, int chan, size_t region_off, size_t slot_bytes) {
+  using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+  constexpr int V = Vec<T>::N;
+  const int W = c.world;
+  const uint32_t half = call_parity(c, chan);
+  const size_t my_slot = region_off + ((size_t)half * W + c.rank) * slot_bytes;
+  const bool aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  const size_t nvec = aligned ? n / V : 0;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t v = tid; v < nvec; v += stride) {
+    uint4 val = ld16(in + v * V);
+    for (int p = 0; p < W; ++p) st16_stream(c.peer[p] + my_slot + v * 16, val);
+  }
+  for (size_t i = nvec * V + tid; i < n; i += stride) {
+    T val = in[i];
+    for (int p = 0; p < W; ++p) reinterpret_cast<T*>(c.peer[p] + my_slot)[i] = val;
+  }
+  uint32_t e = dcp_signal_all(c, chan);
+  dcp_wait_all(c, chan, e);
+  const char* base = c.peer[c.rank] + region_off + (size_t)half * W * slot_bytes;
+  for (size_t v = tid; v < nvec; v += stride) {
+    Acc acc[V];
+    Vec<T> x; x.u = ld16(base + v * 16);
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+    for (int p = 1; p < W; ++p) {
+      x.u = ld16(base + (size_t)p * slot_bytes + v * 16);
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
+    }
+#pragma unroll
+    for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
+    st16(out + v * V, x.u);
+  }
+  for (size_t i = nvec * V + tid; i < n; i += stride) {
+    Acc acc = Tr::up(reinterpret_cast<const T*>(base)[i]);
+    for (int p = 1; p < W; ++p) acc = red_apply<Acc>(op, acc, Tr::up(reinterpret_cast<const T*>(base + (size_t)p * slot_bytes)[i]));
+    out[i] = Tr::down(red_finish<T>(acc, scale, W, op));
+  }
+  call_advance(c, chan);
+}
+
+// -------------------------------------------------------------------------------------------------
+// all_reduce, two-shot (P2P or NVLS) on a buffer that sits at heap offset `off` on every rank.
+// in != nullptr: copy in -> buffer first (staged path); out != nullptr: copy buffer -> out last.
+// `n` elements; the buffer must be 16-byte aligned (offsets are); tail elements go to rank 0.
+// -------------------------------------------------------------------------------------------------
+template <typename T, bool kNvls>
+__global__ void __launch_bounds__(kThreads) k_allreduce_twoshot(DcpDevCtx c, const T* __restrict__ in, T* __restrict__ out, size_t off,
+                                                                 size_t half_bytes, size_t n, float scale, int op, int chan) {
+  using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+  constexpr int V = Vec<T>::N;
+  const int W = c.world;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  const bool staged = in != nullptr;
+  if (staged) off += (size_t)call_parity(c, chan) * half_bytes;
+  char* mine = c.peer[c.rank] + off;
+  const size_t nvec = n / V;
+  if (staged) {
+    const bool al = (reinterpret_cast<uintptr_t>(in) & 15) == 0;
+    if (al) for (size_t v = tid; v < nvec; v += stride) st16(mine + v * 16, ld16_stream(in + v * V));
+    else for (size_t v = tid; v < nvec; v += stride)
+      for (int i = 0; i < V; ++i) reinterpret_cast<T*>(mine)[v * V + i] = in[v * V + i];
+    for (size_t i = nvec * V + tid; i < n; i += stride) reinterpret_cast<T*>(mine)[i] = in[i];
+  }
+  dcp_barrier(c, chan);
+  const Span s = rank_slice(nvec, W, c.rank);
+  // vector v is always handled by the thread with v % stride == tid - in copy-in, reduce and copy-out and
+  // on every rank - so the CTA that staged an element (and chose the parity half) is the one that reads it
+  const size_t v0 = s.begin + ((tid + stride - (s.begin % stride)) % stride);
+  if constexpr (kNvls && NvlsOk<T>::value) {
+    char* mc = c.mc + off;
+    for (size_t v = v0; v < s.end; v += stride) {
+      uint4 r = multimem_ld_reduce_add<T>(mc + v * 16);
+      if (op == DCP_AVG) r = vec_scale<T>(r, scale);
+      multimem_st16(mc + v * 16, r);
+    }
+  } else {
+    for (size_t v = v0; v < s.end; v += stride) {
+      Acc acc[V]; Vec<T> x;
+      uint4 raw[DCP_MAX_RANKS];
+#pragma unroll
+      for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = ld16_stream(c.peer[p] + off + v * 16);  // all loads in flight first
+      x.u = raw[0];
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+#pragma unroll
+      for (int p = 1; p < DCP_MAX_RANKS; ++p) if (p < W) {
+        x.u = raw[p];
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
+      }
+#pragma unroll
+      for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
+#pragma unroll
+      for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) st16_stream(c.peer[p] + off + v * 16, x.u);
+    }
+  }
+  if (c.rank == 0) {  // tail (< one vector) in two-shot fashion as well
+    for (size_t i = nvec * V + tid; i < n; i += stride) {
+      Acc acc = Tr::up(reinterpret_cast<const T*>(c.peer[0] + off)[i]);
+      for (int p = 1; p < W; ++p) acc = red_apply<Acc>(op, acc, Tr::up(reinterpret_cast<const T*>(c.peer[p] + off)[i]));
+      T r = Tr::down(red_finish<T>(acc, scale, W, op));
+      for (int p = 0; p < W; ++p) reinterpret_cast<T*>(c.peer[p] + off)[i] = r;
+    }
+  }
+  dcp_barrier(c, chan);
+  if (out != nullptr) {
+    const bool al = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    if (al) for (size_t v = tid; v < nvec; v += stride) st16(out + v * V, ld16(mine + v * 16));
+    else for (size_t v = tid; v < nvec; v += stride)
+      for (int i = 0; i < V; ++i) out[v * V + i] = reinterpret_cast<const T*>(mine)[v * V + i];
+    for (size_t i = nvec * V + tid; i < n; i += stride) out[i] = reinterpret_cast<const T*>(mine)[i];
+  }
+  if (staged) { __syncthreads(); call_advance(c, chan); }
+}
+
+// -------------------------------------------------------------------------------------------------
+// Byte movers (dtype-agnostic): broadcast / all_gather / gather / scatter.
+// mode bits: which of the W "lanes" this rank pushes and where.
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nbytes, size_t tid, size_t stride, bool stream_store) {
+  const bool al = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0;
+  size_t nvec = al ? nbytes / 16 : 0;
+  for (size_t v = tid; v < nvec; v += stride) {
+    uint4 x = ld16(src + v * 16);
+    if (stream_store) st16_stream(dst + v * 16, x); else st16(dst + v * 16, x);
+  }
+  for (size_t i = nvec * 16 + tid; i < nbytes; i += stride) dst[i] = src[i];
+}
+
+// Rank `root` pushes nbytes to every rank's buffer at `off` (+ parity half when staged), everyone
+// copies out.  sym: buffer is the user's symmetric tensor (in place on root, leading barrier needed).
+__global__ void __launch_bounds__(kThreads) k_broadcast(DcpDevCtx c, char* __restrict__ data, size_t off, size_t half_bytes, size_t nbytes,
+                                                         int root, int chan, int sym) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  if (!sym) off += (size_t)call_parity(c, chan) * half_bytes;
+  else dcp_barrier(c, chan);  // peers may still be reading their copy of the tensor
+  if (c.rank == root) {
+    const char* src = sym ? c.peer[root] + off : data;
+    if (c.nvls && !sym && (nbytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
+      for (size_t v = tid; v < nbytes / 16; v += stride) multimem_st16(c.mc + off + v * 16, ld16(src + v * 16));
+    } else {
+      for (int p = 0; p < c.world; ++p) {
+        if (sym && p == root) continue;
+        copy_bytes(c.peer[p] + off, src, nbytes, tid, stride, true);
+      }
+    }
+  }
+  dcp_barrier(c, chan);
+  if (!sym) {
+    if (c.rank != root) copy_bytes(data, c.peer[c.rank] + off, nbytes, tid, stride, false);
+    __syncthreads();
+    call_advance(c, chan);
+  }
+}
+
+// Every rank pushes its `nbytes` shard to slot [rank] of every peer's buffer (or only to `root`'s when
+// root >= 0: gather).  Staged: copy all W shards out to `out` (contiguous [W][nbytes]) afterwards.
+__global__ void __launch_bounds__(kThreads) k_allgather(DcpDevCtx c, const char* __restrict__ in, char* __restrict__ out, size_t off,
+                                                         size_t half_bytes, size_t nbytes, size_t slot_stride, int root, int chan, int sym) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  if (!sym) off += (size_t)call_parity(c, chan) * half_bytes;
+  else dcp_barrier(c, chan);
+  const size_t my = off + (size_t)c.rank * slot_stride;
+  for (int p = 0; p < c.world; ++p) {
+    if (root >= 0 && p != root) continue;
+    copy_bytes(c.peer[p] + my, in, nbytes, tid, stride, true);
+  }
+  dcp_barrier(c, chan);
+  if (!sym) {
+    if (root < 0 || c.rank == root)
+      for (int p = 0; p < c.world; ++p) copy_bytes(out + (size_t)p * nbytes, c.peer[c.rank] + off + (size_t)p * slot_stride, nbytes, tid, stride, false);
+    __syncthreads();
+    call_advance(c, chan);
+  }
+}
+
+// Rank `root` pushes shard p (in + p*nbytes) to rank p's buffer; everyone copies its shard out.
+__global__ void __launch_bounds__(kThreads) k_scatter(DcpDevCtx c, const char* __restrict__ in, char* __restrict__ out, size_t off,
+                                                       size_t half_bytes, size_t nbytes, int root, int chan) {
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  off += (size_t)call_parity(c, chan) * half_bytes;
+  if (c.rank == root)
+    for (int p = 0; p < c.world; ++p) copy_bytes(c.peer[p] + off, in + (size_t)p * nbytes, nbytes, tid, stride, true);
+  dcp_barrier(c, chan);
+  copy_bytes(out, c.peer[c.rank] + off, nbytes, tid, stride, false);
+  __syncthreads();
+  call_advance(c, chan);
+}
+
+// -------------------------------------------------------------------------------------------------
+// reduce_scatter / reduce: stage own full input, then pull-reduce the slice(s) this rank owns.
+//   root < 0 : reduce_scatter - rank r produces elements [r*n_out, (r+1)*n_out) of the reduction
+//   root >= 0: reduce - `root` produces all n_in elements, others only contribute
+// sym: input already at heap offset `off` on every rank (trailing barrier protects it from reuse).
+// -------------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kThreads) k_reduce_scatter(DcpDevCtx c, const T* __restrict__ in, T* __restrict__ out, size_t off,
+                                                              size_t half_bytes, size_t n_in, size_t n_out, float scale, int op, int root,
+                                                              int chan, int sym) {
+  using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+  constexpr int V = Vec<T>::N;
+  const int W = c.world;
+  const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+  // staged input: single buffer + trailing barrier (the reduce partition differs from the copy-in
+  // partition, so the per-CTA parity trick of the other staged kernels does not apply here)
+  if (!sym) copy_bytes(c.peer[c.rank] + off, reinterpret_cast<const char*>(in), n_in * sizeof(T), tid, stride, false);
+  dcp_barrier(c, chan);
+  if (root < 0 || c.rank == root) {
+    const size_t first = root < 0 ? (size_t)c.rank * n_out : 0;
+    const size_t soff = off + first * sizeof(T);
+    const bool al = ((soff | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    const size_t nvec = al ? n_out / V : 0;
+    for (size_t v = tid; v < nvec; v += stride) {
+      Acc acc[V]; Vec<T> x;
+      uint4 raw[DCP_MAX_RANKS];
+#pragma unroll
+      for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = ld16_stream(c.peer[p] + soff + v * 16);
+      x.u = raw[0];
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+#pragma unroll
+      for (int p = 1; p < DCP_MAX_RANKS; ++p) if (p < W) {
+        x.u = raw[p];
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
+      }
+#pragma unroll
+      for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
+      st16(out + v * V, x.u);
+    }
+    for (size_t i = nvec * V + tid; i < n_out; i += stride) {
+      Acc acc = Tr::up(reinterpret_cast<const T*>(c.peer[0] + soff)[i]);
+      for (int p = 1; p < W; ++p) acc = red_apply<Acc>(op, acc, Tr::up(reinterpret_cast<const T*>(c.peer[p] + soff)[i]));
+      out[i] = Tr::down(red_finish<T>(acc, scale, W, op));
+    }
+  }
+  dcp_barrier(c, chan);
+}
+
+// -------------------------------------------------------------------------------------------------
+// send / recv through per-source receive slots.  Block b moves its share of the message and owns
+// flag word [peer][b]; sequence numbers are kept per (peer, block) in local control memory.
+// -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t* p2p_word(char* heap, size_t region, int peer, int block) {
+  return reinterpret_cast<uint32_t*>(heap + region) + (size_t)peer * DCP_P2P_BLOCKS + block;
+}
+
+__global__ void __launch_bounds__(kThreads) k_send(DcpDevCtx c, const char* __restrict__ in, size_t nbytes, int dst) {
+  char* me = c.peer[c.rank];
+  const int b = blockIdx.x;
+  volatile uint32_t* seqp = p2p_word(me, DcpHeapLayout::kSendSeqOff, dst, b);
+  const uint32_t seq = *seqp + 1;
+  // the slot is free once the receiver acknowledged the previous message
+  if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PAckOff, dst, b), seq - 1);
+  __syncthreads();
+  char* slot = c.peer[dst] + c.p2p_slot_off + (size_t)c.rank * c.p2p_slot_bytes;
+  // contiguous share per block so that flags cover disjoint ranges
+  size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
+  size_t lo = per * b; if (lo > nbytes) lo = nbytes;
+  size_t hi = lo + per; if (hi > nbytes) hi = nbytes;
+  copy_bytes(slot + lo, in + lo, hi - lo, threadIdx.x, blockDim.x, true);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    st_release_sys(p2p_word(c.peer[dst], DcpHeapLayout::kP2PFlagOff, c.rank, b), seq);
+    *seqp = seq;
+  }
+}
+
+__global__ void __launch_bounds__(kThreads) k_recv(DcpDevCtx c, char* __restrict__ out, size_t nbytes, int src) {
+  char* me = c.peer[c.rank];
+  const int b = blockIdx.x;
+  volatile uint32_t* seqp = p2p_word(me, DcpHeapLayout::kRecvSeqOff, src, b);
+  const uint32_t seq = *seqp + 1;
+  if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PFlagOff, src, b), seq);
+  __syncthreads();
+  const char* slot = me + c.p2p_slot_off + (size_t)src * c.p2p_slot_bytes;
+  size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
+  size_t lo = per * b; if (lo > nbytes) lo = nbytes;
+  size_t hi = lo + per; if (hi > nbytes) hi = nbytes;
+  copy_bytes(out + lo, slot + lo, hi - lo, threadIdx.x, blockDim.x, false);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    st_release_sys(p2p_word(c.peer[src], DcpHeapLayout::kP2PAckOff, c.rank, b), seq);
+    *seqp = seq;
+  }
+}
+
+__global__ void k_barrier(DcpDevCtx c, int chan) { dcp_barrier(c, chan); }
+
+// ---- host side -------------------------------------------------------------------------------------
+int grid_for(size_t nbytes, int max_ctas) {
+  size_t per_cta = (size_t)kThreads * 16 * 4;  // ~4 vectors per thread before adding CTAs
+  long g = (long)((nbytes + per_cta - 1) / per_cta);
+  if (g < 1) g = 1;
+  if (max_ctas <= 0) max_ctas = 64;
+  if (g > max_ctas) g = max_ctas;
+  if (g > DCP_MAX_BLOCKS) g = DCP_MAX_BLOCKS;
+  return (int)g;
+}
+
+size_t elem_size(int dtype) {
+  switch (dtype) { case DCP_F32: case DCP_I32: return 4; case DCP_BF16: case DCP_F16: return 2; case DCP_I64: case DCP_F64: return 8; case DCP_U8: return 1; }
+  return 0;
+}
+
+#define DISPATCH_DTYPE(dtype, ...)                                             \
+  switch (dtype) {                                                             \
+    case DCP_F32: { using T = float; __VA_ARGS__; break; }                     \
+    case DCP_BF16: { using T = __nv_bfloat16; __VA_ARGS__; break; }            \
+    case DCP_F16: { using T = __half; __VA_ARGS__; break; }                    \
+    case DCP_I32: { using T = int32_t; __VA_ARGS__; break; }                   \
+    case DCP_I64: { using T = int64_t; __VA_ARGS__; break; }                   \
+    case DCP_F64: { using T = double; __VA_ARGS__; break; }                    \
+    case DCP_U8: { using T = uint8_t; __VA_ARGS__; break; }                    \
+    default: dcp_set_error("unsupported dtype %d", dtype); return -1;          \
+  }
+
+}  // namespace
+
+extern "C" {
+
+const DcpDevCtx* dcp_symm_ctx(void* h);
+size_t dcp_symm_bytes(void* h);
+
+static inline long heap_offset(const DcpDevCtx& c, const void* p, size_t heap_bytes) {
+  const char* base = c.peer[c.rank];
+  const char* q = static_cast<const char*>(p);
+  if (q >= base && q < base + heap_bytes) return (long)(q - base);
+  return -1;
+}
+
+// Region split of the staging area: [one-shot slots: 2 x W x oneshot_slot][bounce: 2 halves]
+static inline size_t oneshot_slot_bytes(const DcpDevCtx& c) {
+  size_t s = c.staging_bytes / 8 / (2 * DCP_MAX_RANKS);  // 1/8 of staging for one-shot slots
+  return s / 16 * 16;
+}
+static inline size_t bounce_off(const DcpDevCtx& c) { return c.staging_off + oneshot_slot_bytes(c) * 2 * DCP_MAX_RANKS; }
+static inline size_t bounce_half(const DcpDevCtx& c) { return ((c.staging_bytes - oneshot_slot_bytes(c) * 2 * DCP_MAX_RANKS) / 2) / 256 * 256; }
+
+size_t dcp_coll_oneshot_max_bytes(void* h) { return oneshot_slot_bytes(*dcp_symm_ctx(h)); }
+size_t dcp_coll_bounce_max_bytes(void* h) { return bounce_half(*dcp_symm_ctx(h)); }
+
+// algo: 1 one-shot, 2 two-shot P2P, 3 NVLS.  In-place on `buf` (n elements).  If `buf` lies inside the
+// symmetric heap the peers read it directly; otherwise it is bounced through the staging area.
+int dcp_all_reduce(void* h, void* buf, size_t n, int dtype, int op, int algo, int chan, int max_ctas, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  const size_t es = elem_size(dtype), nbytes = n * es;
+  if (n == 0) return 0;
+  if ((op == DCP_BAND || op == DCP_BOR || op == DCP_BXOR) && (dtype == DCP_F32 || dtype == DCP_BF16 || dtype == DCP_F16 || dtype == DCP_F64)) {
+    dcp_set_error("bitwise reduction on a floating dtype"); return -1;
+  }
+  const float scale = 1.0f / (float)c.world;
+  const long off = heap_offset(c, buf, dcp_symm_bytes(h));
+  if (algo == 1) {
+    if (nbytes > oneshot_slot_bytes(c)) { dcp_set_error("one-shot all_reduce limited to %zu bytes", oneshot_slot_bytes(c)); return -1; }
+    int grid = grid_for(nbytes, max_ctas);
+    DISPATCH_DTYPE(dtype, (k_allreduce_oneshot<T><<<grid, kThreads, 0, stream>>>(c, (const T*)buf, (T*)buf, n, scale, op, chan, c.staging_off, oneshot_slot_bytes(c))));
+  } else {
+    const bool nvls = algo == 3;
+    if (nvls && (!c.nvls || !(dtype == DCP_F32 || dtype == DCP_BF16 || dtype == DCP_F16) || !(op == DCP_SUM || op == DCP_AVG))) {
+      dcp_set_error("NVLS all_reduce needs a multicast mapping, f32/bf16/f16 and SUM/AVG"); return -1;
+    }
+    if (off >= 0 && (off % 16) == 0) {
+      int grid = grid_for(nbytes / c.world + 1, max_ctas);
+      if (nvls) { DISPATCH_DTYPE(dtype, (k_allreduce_twoshot<T, true><<<grid, kThreads, 0, stream>>>(c, nullptr, nullptr, (size_t)off, 0, n, scale, op, chan))); }
+      else { DISPATCH_DTYPE(dtype, (k_allreduce_twoshot<T, false><<<grid, kThreads, 0, stream>>>(c, nullptr, nullptr, (size_t)off, 0, n, scale, op, chan))); }
+    } else {
+      const size_t cap = bounce_half(c) / es;
+      for (size_t done = 0; done < n; done += cap) {
+        size_t m = n - done < cap ? n - done : cap;
+        int grid = grid_for(m * es, max_ctas);
+        char* p = (char*)buf + done * es;
+        if (nvls) { DISPATCH_DTYPE(dtype, (k_allreduce_twoshot<T, true><<<grid, kThreads, 0, stream>>>(c, (const T*)p, (T*)p, bounce_off(c), bounce_half(c), m, scale, op, chan))); }
+        else { DISPATCH_DTYPE(dtype, (k_allreduce_twoshot<T, false><<<grid, kThreads, 0, stream>>>(c, (const T*)p, (T*)p, bounce_off(c), bounce_half(c), m, scale, op, chan))); }
+      }
+    }
+  }
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int dcp_broadcast(void* h, void* buf, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  if (nbytes == 0) return 0;
+  const long off = heap_offset(c, buf, dcp_symm_bytes(h));
+  if (off >= 0 && off % 16 == 0) {
+    k_broadcast<<<grid_for(nbytes, max_ctas), kThreads, 0, stream>>>(c, (char*)buf, (size_t)off, 0, nbytes, root, chan, 1);
+  } else {
+    const size_t cap = bounce_half(c);
+    for (size_t done = 0; done < nbytes; done += cap) {
+      size_t m = nbytes - done < cap ? nbytes - done : cap;
+      k_broadcast<<<grid_for(m, max_ctas), kThreads, 0, stream>>>(c, (char*)buf + done, bounce_off(c), bounce_half(c), m, root, chan, 0);
+    }
+  }
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// out: [W][nbytes] contiguous.  root < 0: all_gather; root >= 0: gather to root (out may be null elsewhere).
+int dcp_all_gather(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  if (nbytes == 0) return 0;
+  const long off = out ? heap_offset(c, out, dcp_symm_bytes(h)) : -1;
+  if (root < 0 && off >= 0 && off % 16 == 0 && nbytes % 16 == 0) {
+    k_allgather<<<grid_for(nbytes, max_ctas), kThreads, 0, stream>>>(c, (const char*)in, nullptr, (size_t)off, 0, nbytes, nbytes, -1, chan, 1);
+  } else {
+    const size_t cap = bounce_half(c) / c.world / 16 * 16;
+    for (size_t done = 0; done < nbytes; done += cap) {
+      size_t m = nbytes - done < cap ? nbytes - done : cap;
+      // strided copy-out: shard p lands at out + p*nbytes + done, so launch per chunk with adjusted bases
+      if (done == 0 && m == nbytes) {
+        k_allgather<<<grid_for(m, max_ctas), kThreads, 0, stream>>>(c, (const char*)in, (char*)out, bounce_off(c), bounce_half(c), m, cap, root, chan, 0);
+      } else {
+        dcp_set_error("all_gather/gather shard of %zu bytes exceeds the bounce capacity %zu; use a symmetric output tensor", nbytes, cap);
+        return -1;
+      }
+    }
+  }
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// in: [W][nbytes] contiguous on root.
+int dcp_scatter(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  if (nbytes == 0) return 0;
+  if (nbytes > bounce_half(c)) { dcp_set_error("scatter shard exceeds the bounce capacity"); return -1; }
+  k_scatter<<<grid_for(nbytes, max_ctas), kThreads, 0, stream>>>(c, (const char*)in, (char*)out, bounce_off(c), bounce_half(c), nbytes, root, chan);
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// root < 0: reduce_scatter (in: W*n_out elements, out: n_out).  root >= 0: reduce (in: n_out elements, out on root).
+int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dtype, int op, int root, int chan, int max_ctas, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  const size_t es = elem_size(dtype);
+  if (n_out == 0) return 0;
+  const size_t n_in = root < 0 ? n_out * c.world : n_out;
+  const float scale = 1.0f / (float)c.world;
+  const long off = heap_offset(c, in, dcp_symm_bytes(h));
+  const int sym = off >= 0 && off % 16 == 0;
+  if (!sym && n_in * es > bounce_half(c)) { dcp_set_error("reduce_scatter/reduce input exceeds the bounce capacity; use a symmetric input tensor"); return -1; }
+  int grid = grid_for(n_out * es, max_ctas);
+  DISPATCH_DTYPE(dtype, (k_reduce_scatter<T><<<grid, kThreads, 0, stream>>>(c, (const T*)in, (T*)out, sym ? (size_t)off : bounce_off(c), bounce_half(c),
+                                                                            n_in, n_out, scale, op, root, chan, sym)));
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += c.p2p_slot_bytes) {
+    size_t m = nbytes - done < c.p2p_slot_bytes ? nbytes - done : c.p2p_slot_bytes;
+    k_send<<<DCP_P2P_BLOCKS, kThreads, 0, stream>>>(c, (const char*)in + done, m, dst);
+    if (nbytes == 0) break;
+  }
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += c.p2p_slot_bytes) {
+    size_t m = nbytes - done < c.p2p_slot_bytes ? nbytes - done : c.p2p_slot_bytes;
+    k_recv<<<DCP_P2P_BLOCKS, kThreads, 0, stream>>>(c, (char*)out + done, m, src);
+    if (nbytes == 0) break;
+  }
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int dcp_barrier_launch(void* h, int chan, cudaStream_t stream) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  k_barrier<<<1, 32, 0, stream>>>(c, chan);
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

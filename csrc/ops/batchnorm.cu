@@ -1,0 +1,195 @@
+// Fused BatchNorm(+ReLU), forward and backward, over [M, C] row-major activations - which covers both
+// BatchNorm1d on [N, F] (the reference's `self.batchnorm`, ref:main.py:29,40-41, fused with its ReLU)
+// and BatchNorm2d on channels-last [N,H,W,C] (M = N*H*W) for the ResNet configs.
+//
+//   stats kernel : per-channel sum / sum-of-squares, fp32 per thread -> fp64 atomics into a 2*C (or 3*C)
+//                  scratch accumulator that the launcher zeroes first
+//   apply kernel : mean/rstd from the accumulator, normalise + affine + optional ReLU; CTA 0 also updates
+//                  running_mean / running_var (unbiased) / num_batches_tracked and saves mean, rstd
+//   backward     : same two-phase shape: reduce sum(dy'), sum(dy' * xhat) -> dx, dgamma, dbeta, with
+//                  dy' = dy * (y > 0) when the ReLU is fused
+// SyncBatchNorm: the launcher hands the accumulator to the P2P one-shot all_reduce between the two
+// phases (parallel/p2p_backend.py), so the statistics cross NVLink as 2*C+1 doubles.
+#include "ops/ops_common.cuh"
+
+namespace {
+
+constexpr int kRows = 8;       // row lanes per CTA
+constexpr int kCols = 32;      // channels per CTA (one warp wide -> coalesced 128 B rows for f32)
+
+// acc layout: [0,C) sum, [C,2C) sumsq
+template <typename T>
+__global__ void __launch_bounds__(kRows * kCols) k_bn_stats(const T* __restrict__ x, double* __restrict__ acc, long M, int C, long rows_per_cta) {
+  __shared__ float s1[kRows][kCols + 1], s2[kRows][kCols + 1];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * kCols + cx;
+  const long r0 = (long)blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  float a = 0.f, b = 0.f;
+  if (c < C)
+    for (long r = r0 + ry; r < r1; r += kRows) { float v = to_f(x[r * C + c]); a += v; b += v * v; }
+  s1[ry][cx] = a; s2[ry][cx] = b;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+#pragma unroll
+    for (int i = 1; i < kRows; ++i) { a += s1[i][cx]; b += s2[i][cx]; }
+    atomicAdd(&acc[c], (double)a);
+    atomicAdd(&acc[C + c], (double)b);
+  }
+}
+
+// count = number of rows that went into acc (local M, or the global count for SyncBN)
+template <typename T>
+__global__ void k_bn_apply(const T* __restrict__ x, T* __restrict__ y, const double* __restrict__ acc, const float* __restrict__ gamma,
+                           const float* __restrict__ beta, float* __restrict__ run_mean, float* __restrict__ run_var, long long* __restrict__ nbt,
+                           float* __restrict__ save_mean, float* __restrict__ save_rstd, long M, int C, double count, float eps, float momentum,
+                           int relu, int training) {
+  extern __shared__ float sm[];  // scale[C], shift[C]
+  float* scale = sm; float* shift = sm + C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var;
+    if (training) {
+      double m = acc[c] / count;
+      double v = acc[C + c] / count - m * m;
+      if (v < 0) v = 0;
+      mean = (float)m; var = (float)v;
+    } else { mean = run_mean[c]; var = run_var[c]; }
+    float rstd = rsqrtf(var + eps);
+    float g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    scale[c] = g * rstd; shift[c] = bt - mean * g * rstd;
+    if (blockIdx.x == 0 && training) {
+      save_mean[c] = mean; save_rstd[c] = rstd;
+      if (run_mean) {
+        float unbiased = count > 1 ? var * (float)(count / (count - 1.0)) : var;
+        run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mean;
+        run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && training && nbt) *nbt += 1;
+  __syncthreads();
+  const long total = M * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    int c = i % C;
+    float v = to_f(x[i]) * scale[c] + shift[c];
+    if (relu) v = fmaxf(v, 0.f);
+    y[i] = from_f<T>(v);
+  }
+}
+
+// acc layout: [0,C) sum(dy'), [C,2C) sum(dy' * xhat)
+template <typename T>
+__global__ void __launch_bounds__(kRows * kCols) k_bn_bwd_reduce(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
+                                                                  const float* __restrict__ mean, const float* __restrict__ rstd,
+                                                                  double* __restrict__ acc, long M, int C, long rows_per_cta, int relu) {
+  __shared__ float s1[kRows][kCols + 1], s2[kRows][kCols + 1];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int c = blockIdx.x * kCols + cx;
+  const long r0 = (long)blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  float a = 0.f, b = 0.f;
+  if (c < C) {
+    const float mu = mean[c], rs = rstd[c];
+    for (long r = r0 + ry; r < r1; r += kRows) {
+      float g = to_f(dy[r * C + c]);
+      if (relu && !(to_f(y[r * C + c]) > 0.f)) g = 0.f;
+      a += g; b += g * (to_f(x[r * C + c]) - mu) * rs;
+    }
+  }
+  s1[ry][cx] = a; s2[ry][cx] = b;
+  __syncthreads();
+  if (ry == 0 && c < C) {
+#pragma unroll
+    for (int i = 1; i < kRows; ++i) { a += s1[i][cx]; b += s2[i][cx]; }
+    atomicAdd(&acc[c], (double)a);
+    atomicAdd(&acc[C + c], (double)b);
+  }
+}
+
+template <typename T>
+__global__ void k_bn_bwd_apply(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                               const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+                               const double* __restrict__ acc, float* __restrict__ dgamma, float* __restrict__ dbeta, long M, int C, double count,
+                               int relu) {
+  extern __shared__ float sm[];  // k1[C] = gamma*rstd, k2[C] = sum_dy/count, k3[C] = sum_dy_xhat/count
+  float* k1 = sm; float* k2 = sm + C; float* k3 = sm + 2 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float g = gamma ? gamma[c] : 1.f;
+    k1[c] = g * rstd[c];
+    k2[c] = (float)(acc[c] / count);
+    k3[c] = (float)(acc[C + c] / count);
+    if (blockIdx.x == 0) {
+      // under SyncBN acc[0..2C) holds the cross-rank sums; parameter gradients use the local copy kept
+      // in acc[2C..4C) (DDP averages them afterwards)
+      if (dgamma) dgamma[c] = (float)acc[3 * C + c];
+      if (dbeta) dbeta[c] = (float)acc[2 * C + c];
+    }
+  }
+  __syncthreads();
+  const long total = M * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    int c = i % C;
+    float g = to_f(dy[i]);
+    if (relu && !(to_f(y[i]) > 0.f)) g = 0.f;
+    float xhat = (to_f(x[i]) - mean[c]) * rstd[c];
+    dx[i] = from_f<T>(k1[c] * (g - k2[c] - xhat * k3[c]));
+  }
+}
+
+// copies acc[0..2C) into acc[2C..4C) (keeps the local sums for dgamma/dbeta before a cross-rank reduce)
+__global__ void k_bn_keep_local(double* acc, int C) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < 2 * C) acc[2 * C + i] = acc[i];
+}
+
+void stats_grid(long M, int C, dim3* grid, long* rows_per_cta) {
+  int cx = ceil_div(C, kCols);
+  long want = (148L * 4 + cx - 1) / cx;           // ~4 CTAs per SM in total
+  long maxy = (M + kRows * 4 - 1) / (kRows * 4);  // at least 4 rows per lane
+  long gy = want < maxy ? want : maxy; if (gy < 1) gy = 1; if (gy > 65535) gy = 65535;
+  *rows_per_cta = (M + gy - 1) / gy;
+  *grid = dim3(cx, (unsigned)gy);
+}
+
+}  // namespace
+
+extern "C" {
+
+// scratch: >= 4*C doubles.  Phase 1 of forward: zero + accumulate (sum, sumsq).
+int dcp_bn_stats(const void* x, void* scratch, long M, int C, int dtype, cudaStream_t s) {
+  DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, s));
+  dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);
+  DISPATCH_ACT(dtype, (k_bn_stats<T><<<grid, kRows * kCols, 0, s>>>((const T*)x, (double*)scratch, M, C, rpc)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+// Phase 2 of forward.  training=0: uses running stats, scratch may be null.
+int dcp_bn_apply(const void* x, void* y, const void* scratch, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
+                 float* save_mean, float* save_rstd, long M, int C, double count, float eps, float momentum, int relu, int training, int dtype,
+                 cudaStream_t s) {
+  int grid = grid_1d(M * C, 256, 148 * 8);
+  size_t smem = sizeof(float) * 2 * C;
+  DISPATCH_ACT(dtype, (k_bn_apply<T><<<grid, 256, smem, s>>>((const T*)x, (T*)y, (const double*)scratch, gamma, beta, run_mean, run_var,
+                                                             (long long*)nbt, save_mean, save_rstd, M, C, count, eps, momentum, relu, training)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+// Backward phase 1: zero + accumulate (sum dy', sum dy'*xhat) into scratch[0..2C) and keep a local copy in [2C..4C).
+int dcp_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, void* scratch, long M, int C, int relu,
+                      int dtype, cudaStream_t s) {
+  DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, s));
+  dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);
+  DISPATCH_ACT(dtype, (k_bn_bwd_reduce<T><<<grid, kRows * kCols, 0, s>>>((const T*)x, (const T*)y, (const T*)dy, mean, rstd, (double*)scratch, M, C, rpc, relu)));
+  k_bn_keep_local<<<ceil_div(2 * C, 256), 256, 0, s>>>((double*)scratch, C);
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+// Backward phase 2.  count: rows behind scratch[0..2C) (global for SyncBN).
+int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, const float* mean, const float* rstd, const float* gamma,
+                     const void* scratch, float* dgamma, float* dbeta, long M, int C, double count, int relu, int dtype, cudaStream_t s) {
+  int grid = grid_1d(M * C, 256, 148 * 8);
+  size_t smem = sizeof(float) * 3 * C;
+  DISPATCH_ACT(dtype, (k_bn_bwd_apply<T><<<grid, 256, smem, s>>>((const T*)x, (const T*)y, (const T*)dy, (T*)dx, mean, rstd, gamma,
+                                                                 (const double*)scratch, dgamma, dbeta, M, C, count, relu)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,165 @@
+// Element-wise / pooling kernels: ReLU, residual add+ReLU, dropout (element and channel), max-pool,
+// global average pool, eval correct-count.  These are the K2/K4-K6/K10-K11/K19 call sites of the
+// reference model (ref:main.py:33-37,41-42,83-85); where a producer kernel can absorb them (conv and
+// BatchNorm epilogues) the layers use the fused form instead and these only serve the stand-alone case.
+// All activations are channels-last ([N,H,W,C] physical) or 2-D; f32 and bf16.
+#include "ops/ops_common.cuh"
+
+namespace {
+constexpr int kT = 256;
+
+template <typename T> __global__ void k_relu_fwd(const T* __restrict__ x, T* __restrict__ y, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) y[i] = from_f<T>(fmaxf(to_f(x[i]), 0.f));
+}
+// dx = dy * (y > 0)
+template <typename T> __global__ void k_relu_bwd(const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    dx[i] = to_f(y[i]) > 0.f ? dy[i] : from_f<T>(0.f);
+}
+template <typename T> __global__ void k_add_relu_fwd(const T* __restrict__ a, const T* __restrict__ b, T* __restrict__ y, long n) {
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
+    y[i] = from_f<T>(fmaxf(to_f(a[i]) + to_f(b[i]), 0.f));
+}
+
+// mode 0: element-wise; 1: per (n,c) with NHWC physical layout (inner = C, hw = H*W); 2: per (n,c) NCHW physical
+__device__ __forceinline__ uint64_t drop_index(long i, int mode, long inner, long hw) {
+  if (mode == 0) return (uint64_t)i;
+  if (mode == 1) { long c = i % inner; long n = i / (inner * hw); return (uint64_t)(n * inner + c); }
+  return (uint64_t)(i / hw);
+}
+// y = x * keep / (1-p).  The same call with x = dy regenerates the mask for backward.
+template <typename T> __global__ void k_dropout(const T* __restrict__ x, T* __restrict__ y, long n, float p, uint64_t seed, uint64_t stream,
+                                                const long long* __restrict__ step, int mode, long inner, long hw) {
+  const float scale = 1.f / (1.f - p);
+  const uint64_t st = stream + (step ? (uint64_t)(*step) * 0x10000ull : 0ull);
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    float u = philox_uniform(seed, st, drop_index(i, mode, inner, hw));
+    y[i] = u >= p ? from_f<T>(to_f(x[i]) * scale) : from_f<T>(0.f);
+  }
+}
+
+// Max-pool over channels-last input.  arg stores the window position (kh*k+kw) of the maximum.
+// out_nchw: write y (and read dy in backward) in NCHW-contiguous order so a following flatten is free.
+template <typename T> __global__ void k_maxpool_fwd(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ arg, int N, int H, int W, int C,
+                                                    int Ho, int Wo, int k, int s, int pad, int out_nchw) {
+  long total = (long)N * Ho * Wo * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    int c = i % C; long r = i / C; int wo = r % Wo; r /= Wo; int ho = r % Ho; int n = r / Ho;
+    float best = -INFINITY; int bi = 0;
+    for (int kh = 0; kh < k; ++kh) for (int kw = 0; kw < k; ++kw) {
+      int h = ho * s - pad + kh, w = wo * s - pad + kw;
+      if (h < 0 || h >= H || w < 0 || w >= W) continue;
+      float v = to_f(x[(((long)n * H + h) * W + w) * C + c]);
+      if (v > best) { best = v; bi = kh * k + kw; }
+    }
+    long o = out_nchw ? (((long)n * C + c) * Ho + ho) * Wo + wo : i;
+    y[o] = from_f<T>(best);
+    arg[i] = (uint8_t)bi;
+  }
+}
+// Gather form: every input pixel sums the windows whose maximum it was (no atomics, no zero fill).
+template <typename T> __global__ void k_maxpool_bwd(const T* __restrict__ dy, const uint8_t* __restrict__ arg, T* __restrict__ dx, int N, int H, int W,
+                                                    int C, int Ho, int Wo, int k, int s, int pad, int out_nchw) {
+  long total = (long)N * H * W * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    int c = i % C; long r = i / C; int w = r % W; r /= W; int h = r % H; int n = r / H;
+    float acc = 0.f;
+    int ho_lo = max(0, (h + pad - k + s) / s), ho_hi = min(Ho - 1, (h + pad) / s);
+    int wo_lo = max(0, (w + pad - k + s) / s), wo_hi = min(Wo - 1, (w + pad) / s);
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+      int kh = h + pad - ho * s, kw = w + pad - wo * s;
+      if (kh < 0 || kh >= k || kw < 0 || kw >= k) continue;
+      long oi = (((long)n * Ho + ho) * Wo + wo) * C + c;
+      if (arg[oi] == kh * k + kw) acc += to_f(dy[out_nchw ? (((long)n * C + c) * Ho + ho) * Wo + wo : oi]);
+    }
+    dx[i] = from_f<T>(acc);
+  }
+}
+
+// [N, HW, C] -> [N, C] mean; one block per (n, 32-channel group), threads = 32 channels x 8 row lanes
+template <typename T> __global__ void k_gap_fwd(const T* __restrict__ x, T* __restrict__ y, int HW, int C) {
+  __shared__ float sm[8][33];
+  int n = blockIdx.y, c = blockIdx.x * 32 + (threadIdx.x & 31), lane = threadIdx.x >> 5;
+  float acc = 0.f;
+  if (c < C) for (int r = lane; r < HW; r += 8) acc += to_f(x[((long)n * HW + r) * C + c]);
+  sm[lane][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (lane == 0 && c < C) {
+    float t = 0.f;
+    for (int l = 0; l < 8; ++l) t += sm[l][threadIdx.x];
+    y[(long)n * C + c] = from_f<T>(t / HW);
+  }
+}
+template <typename T> __global__ void k_gap_bwd(const T* __restrict__ dy, T* __restrict__ dx, long total, int HW, int C) {
+  const float inv = 1.f / HW;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    int c = i % C; long n = i / ((long)HW * C);
+    dx[i] = from_f<T>(to_f(dy[n * C + c]) * inv);
+  }
+}
+
+// rows whose argmax equals the label; one warp per row; accumulates into *count (int64, caller zeroes)
+template <typename T> __global__ void k_correct_count(const T* __restrict__ x, const long long* __restrict__ target, long long* __restrict__ count, int M, int C) {
+  int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  int hit = 0;
+  if (row < M) {
+    float best = -INFINITY; int bi = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) { float v = to_f(x[(long)row * C + c]); if (v > best) { best = v; bi = c; } }
+    for (int o = 16; o > 0; o >>= 1) {
+      float ob = __shfl_xor_sync(0xffffffffu, best, o); int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ob > best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+    }
+    hit = (lane == 0 && bi == (int)target[row]) ? 1 : 0;
+  }
+  unsigned m = __ballot_sync(0xffffffffu, hit);
+  (void)m;
+  if (hit) atomicAdd((unsigned long long*)count, 1ull);
+}
+}  // namespace
+
+extern "C" {
+
+int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s) {
+  DISPATCH_ACT(dtype, (k_relu_fwd<T><<<grid_1d(n, kT), kT, 0, s>>>((const T*)x, (T*)y, n)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_relu_bwd(const void* y, const void* dy, void* dx, long n, int dtype, cudaStream_t s) {
+  DISPATCH_ACT(dtype, (k_relu_bwd<T><<<grid_1d(n, kT), kT, 0, s>>>((const T*)y, (const T*)dy, (T*)dx, n)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_add_relu_fwd(const void* a, const void* b, void* y, long n, int dtype, cudaStream_t s) {
+  DISPATCH_ACT(dtype, (k_add_relu_fwd<T><<<grid_1d(n, kT), kT, 0, s>>>((const T*)a, (const T*)b, (T*)y, n)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_dropout(const void* x, void* y, long n, float p, unsigned long long seed, unsigned long long stream_id, const void* step, int mode, long inner,
+                long hw, int dtype, cudaStream_t s) {
+  DISPATCH_ACT(dtype, (k_dropout<T><<<grid_1d(n, kT), kT, 0, s>>>((const T*)x, (T*)y, n, p, seed, stream_id, (const long long*)step, mode, inner, hw)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_maxpool_fwd(const void* x, void* y, void* arg, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s) {
+  long total = (long)N * Ho * Wo * C;
+  DISPATCH_ACT(dtype, (k_maxpool_fwd<T><<<grid_1d(total, kT), kT, 0, s>>>((const T*)x, (T*)y, (uint8_t*)arg, N, H, W, C, Ho, Wo, k, st, pad, out_nchw)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_maxpool_bwd(const void* dy, const void* arg, void* dx, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s) {
+  long total = (long)N * H * W * C;
+  DISPATCH_ACT(dtype, (k_maxpool_bwd<T><<<grid_1d(total, kT), kT, 0, s>>>((const T*)dy, (const uint8_t*)arg, (T*)dx, N, H, W, C, Ho, Wo, k, st, pad, out_nchw)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_gap_fwd(const void* x, void* y, int N, int HW, int C, int dtype, cudaStream_t s) {
+  dim3 grid(ceil_div(C, 32), N);
+  DISPATCH_ACT(dtype, (k_gap_fwd<T><<<grid, 256, 0, s>>>((const T*)x, (T*)y, HW, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_gap_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, cudaStream_t s) {
+  long total = (long)N * HW * C;
+  DISPATCH_ACT(dtype, (k_gap_bwd<T><<<grid_1d(total, kT), kT, 0, s>>>((const T*)dy, (T*)dx, total, HW, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_correct_count(const void* x, const void* target, void* count, int M, int C, int dtype, cudaStream_t s) {
+  DCP_CUDA_CHECK(cudaMemsetAsync(count, 0, 8, s));
+  DISPATCH_ACT(dtype, (k_correct_count<T><<<ceil_div(M, 8), 256, 0, s>>>((const T*)x, (const long long*)target, (long long*)count, M, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+}  // extern "C"

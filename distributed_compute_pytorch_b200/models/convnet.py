@@ -26,7 +26,7 @@ class ConvNet(nn.Module):
         self.fc1 = ops.Linear(9216, 128)
         self.fc2 = ops.Linear(128, 10)
         self.batchnorm = ops.BatchNorm1d(128, fuse_relu=True)
-        self.pool = ops.MaxPool2d(2)
+        self.pool = ops.MaxPool2d(2, out_nchw=True)
 
     def features(self, x: torch.Tensor) -> torch.Tensor:
         """Everything up to the logits."""

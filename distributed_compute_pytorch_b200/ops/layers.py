@@ -141,13 +141,14 @@ class ReLU(nn.Module):
 
 
 class MaxPool2d(nn.Module):
-    def __init__(self, kernel_size: int, stride: Optional[int] = None, padding: int = 0):
+    def __init__(self, kernel_size: int, stride: Optional[int] = None, padding: int = 0, out_nchw: bool = False):
         super().__init__()
         self.kernel_size, self.stride, self.padding = kernel_size, stride or kernel_size, padding
+        self.out_nchw = out_nchw  # CUDA: write the result NCHW-contiguous so a following flatten(1) is a view
 
     def forward(self, x):
         if x.is_cuda:
-            return _k().max_pool2d(x, self.kernel_size, self.stride, self.padding)
+            return _k().max_pool2d(x, self.kernel_size, self.stride, self.padding, self.out_nchw)
         return F.max_pool2d(x, self.kernel_size, self.stride, self.padding)
 
 
