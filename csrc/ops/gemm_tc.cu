@@ -1,0 +1,334 @@
+// Tensor-core GEMM and implicit-GEMM convolution for sm_100a: tcgen05.mma issued by one elected thread,
+// operands staged in shared memory by TMA (128-byte swizzle), fp32 accumulator in TMEM, read back with
+// tcgen05.ld for a fused bias / ReLU / cast epilogue.  One kernel serves
+//   * Linear forward / data-grad / weight-grad (K8, K12 of the reference model, ref:main.py:39,43) through
+//     the operand-major flags (K-major or MN-major per operand, so no transposes are materialised), and
+//   * convolution forward and data-gradient (K3, ref:main.py:34) as an implicit GEMM: the A tile of filter
+//     tap (r, s) is a 4-D TMA box {C, Wb, Hb, Nb} of the channels-last activation shifted by (r, s); TMA's
+//     out-of-bounds zero fill implements the padding.
+// CTA = 128 x BN output tile; warp 0 = TMA producer, warp 1 = MMA issuer (+ TMEM allocator), warps 2-5 =
+// epilogue (each owns 32 TMEM lanes).  4-stage mbarrier pipeline, 128-byte-wide K slabs (32 tf32 or
+// 64 bf16 elements).  gridDim.z splits K (fp32 atomics epilogue).
+#include <cudaTypedefs.h>
+
+#include "ops/tc_common.cuh"
+
+struct TcGemmParams {
+  int M, N;                 // logical output extent (rows, cols)
+  int k_stages;             // number of 128-byte K slabs in total
+  int BN;                   // N tile (32 / 64 / 128 <= kMaxBN)
+  int b_bytes;              // bytes of one B stage (>= BN * 128; MN-major B is loaded in whole 128-byte chunks)
+  int a_mn, b_mn;           // operand majors
+  // implicit conv (A via 4-D map): stage s -> tap = s / cchunks, channel chunk = s % cchunks
+  int conv, S, cchunks, Cin, pad, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
+  // epilogue
+  void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
+};
+
+namespace {
+using namespace tc;
+
+constexpr int kBM = 128, kStages = 4, kMaxBN = 128, kTmemCols = 128;
+constexpr int kABytes = kBM * 128;            // 16 KB per stage
+constexpr int kThreads = 192;
+
+struct __align__(8) Pipe {
+  uint64_t full[kStages], empty[kStages], acc_full;
+  uint32_t tmem_base;
+};
+
+template <bool kTF32>
+__global__ void __launch_bounds__(kThreads, 1)
+k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment is required by the 128-byte swizzle atoms
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int b_bytes = p.b_bytes;
+  const int stage_bytes = kABytes + b_bytes;
+  Pipe* pipe = reinterpret_cast<Pipe*>(smem + kStages * stage_bytes);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  constexpr int kElem = kTF32 ? 4 : 2;
+  constexpr int kBK = 128 / kElem;             // elements per K slab
+  constexpr int kUmmaK = 32 / kElem;           // elements per MMA
+  constexpr int kChunk = 128 / kElem;          // M/N elements per 128-byte chunk (MN-major)
+
+  // K range of this split
+  const int per = (p.k_stages + gridDim.z - 1) / gridDim.z;
+  const int ks0 = blockIdx.z * per, ks1 = min(p.k_stages, ks0 + per);
+  const int nst = ks1 - ks0;
+
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); }
+      mbar_init(&pipe->acc_full, 1);
+      mbar_fence_init();
+    }
+    __syncwarp();
+    tmem_alloc<kTmemCols>(&pipe->tmem_base);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *((volatile uint32_t*)&pipe->tmem_base);
+
+  const int m_tile = blockIdx.x, n_tile = blockIdx.y;
+  // conv: decode the tile into (image group, box row, box col)
+  int n0 = 0, h0 = 0, w0 = 0;
+  if (p.conv) {
+    int t = m_tile;
+    const int tw = t % p.tiles_w; t /= p.tiles_w;
+    const int th = t % p.tiles_h; t /= p.tiles_h;
+    n0 = t * p.Nb; h0 = th * p.Hb; w0 = tw * p.Wb;
+  }
+
+  if (nst > 0) {
+    if (warp == 0 && lane == 0) {
+      // ================= TMA producer =================
+      for (int i = 0; i < nst; ++i) {
+        const int st = i % kStages, ph = (i / kStages) & 1;
+        mbar_wait(&pipe->empty[st], ph ^ 1);
+        uint8_t* sa = smem + st * stage_bytes;
+        uint8_t* sb = sa + kABytes;
+        mbar_expect_tx(&pipe->full[st], kABytes + b_bytes);
+        const int ks = ks0 + i;
+        int kb = ks * kBK;  // K coordinate for B (and for GEMM A)
+        if (p.conv) {
+          const int tap = ks / p.cchunks, cc = ks % p.cchunks;
+          const int r = tap / p.S, s = tap % p.S;
+          tma_load_4d(sa, &map_a, &pipe->full[st], cc * kBK, w0 - p.pad + s, h0 - p.pad + r, n0);
+          kb = tap * p.Cin + cc * kBK;
+        } else if (!p.a_mn) {
+          tma_load_2d(sa, &map_a, &pipe->full[st], kb, m_tile * kBM);
+        } else {
+          for (int j = 0; j < kBM / kChunk; ++j)
+            tma_load_2d(sa + j * (kBK * 128), &map_a, &pipe->full[st], m_tile * kBM + j * kChunk, kb);
+        }
+        if (!p.b_mn) {
+          tma_load_2d(sb, &map_b, &pipe->full[st], kb, n_tile * p.BN);
+        } else {
+          for (int j = 0; j < (p.BN + kChunk - 1) / kChunk; ++j)
+            tma_load_2d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, kb);
+        }
+      }
+    } else if (warp == 1 && lane == 0) {
+      // ================= MMA issuer =================
+      const uint32_t idesc = make_idesc(kTF32, p.a_mn != 0, p.b_mn != 0, kBM, p.BN);
+      for (int i = 0; i < nst; ++i) {
+        const int st = i % kStages, ph = (i / kStages) & 1;
+        mbar_wait(&pipe->full[st], ph);
+        tc_fence_after();
+        const uint32_t sa = smem_u32(smem + st * stage_bytes), sb = sa + kABytes;
+#pragma unroll
+        for (int j = 0; j < kBK / kUmmaK; ++j) {
+          // MN-major: k-rows are 128 B apart (TMA box rows); tf32 needs the BASE32B layout (4-row atoms)
+          constexpr uint32_t kMnSbo = kTF32 ? 512 : 1024, kMnLayout = kTF32 ? 1 : 2;
+          const uint64_t da = p.a_mn ? make_smem_desc(sa + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sa + j * 32, 0, 1024);
+          const uint64_t db = p.b_mn ? make_smem_desc(sb + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sb + j * 32, 0, 1024);
+          umma<kTF32>(tmem, da, db, idesc, (i | j) != 0);
+        }
+        umma_commit(&pipe->empty[st]);   // smem slot reusable once these MMAs retire
+      }
+      umma_commit(&pipe->acc_full);      // accumulator complete
+    }
+  }
+  if (warp >= 2) {
+    // ================= epilogue: TMEM -> registers -> global =================
+    const int lg = warp & 3;                       // TMEM lane group this warp may access
+    const int row = lg * 32 + lane;                // row inside the tile
+    if (nst > 0) {
+      mbar_wait(&pipe->acc_full, 0);
+      tc_fence_after();
+    }
+    long out_row = -1;
+    if (p.conv) {
+      const int nl = row / (p.Hb * p.Wb), hl = (row / p.Wb) % p.Hb, wl = row % p.Wb;
+      const int n = n0 + nl, h = h0 + hl, w = w0 + wl;
+      if (n < p.Nimg && h < p.Ho && w < p.Wo) out_row = ((long)n * p.Ho + h) * p.Wo + w;
+    } else {
+      const long gm = (long)m_tile * kBM + row;
+      if (gm < p.M) out_row = gm;
+    }
+    const bool add_bias = p.bias != nullptr && blockIdx.z == 0;
+    for (int c0 = 0; c0 < p.BN; c0 += 32) {
+      uint32_t r[32];
+      if (nst > 0) {
+        tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + c0, r);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = 0;
+      }
+      if (out_row < 0) continue;
+      const int gn0 = n_tile * p.BN + c0;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int gn = gn0 + j;
+        if (gn >= p.N) break;
+        float v = __uint_as_float(r[j]);
+        if (add_bias) v += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn]) : ((const float*)p.bias)[gn];
+        if (p.relu) v = fmaxf(v, 0.f);
+        r[j] = __float_as_uint(v);
+      }
+      const int ncol = min(32, p.N - gn0);
+      if (p.atomic) {
+        float* o = (float*)p.out + out_row * p.ldc + gn0;
+        for (int j = 0; j < ncol; ++j) atomicAdd(o + j, __uint_as_float(r[j]));
+      } else if (p.out_bf16) {
+        __nv_bfloat16* o = (__nv_bfloat16*)p.out + out_row * p.ldc + gn0;
+        if (ncol == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            uint4 v;
+            __nv_bfloat162 t0 = __floats2bfloat162_rn(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
+            __nv_bfloat162 t1 = __floats2bfloat162_rn(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
+            __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
+            __nv_bfloat162 t3 = __floats2bfloat162_rn(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
+            v.x = *reinterpret_cast<uint32_t*>(&t0); v.y = *reinterpret_cast<uint32_t*>(&t1);
+            v.z = *reinterpret_cast<uint32_t*>(&t2); v.w = *reinterpret_cast<uint32_t*>(&t3);
+            *reinterpret_cast<uint4*>(o + j) = v;
+          }
+        } else {
+          for (int j = 0; j < ncol; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
+        }
+      } else {
+        float* o = (float*)p.out + out_row * p.ldc + gn0;
+        if (ncol == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<uint4*>(o + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
+        } else {
+          for (int j = 0; j < ncol; ++j) o[j] = __uint_as_float(r[j]);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc<kTmemCols>(tmem);
+}
+
+// ---- host: tensor maps ------------------------------------------------------------------------------
+PFN_cuTensorMapEncodeTiled get_encode() {
+  static PFN_cuTensorMapEncodeTiled fn = nullptr;
+  if (!fn) {
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void**)&fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) fn = nullptr;
+  }
+  return fn;
+}
+
+// 2-D map over a row-major [rows][cols] matrix; box = {box_cols (<= 128 B), box_rows}
+int make_map_2d(CUtensorMap* m, const void* base, int elem_bytes, long rows, long cols, long ld_elems, int box_cols, int box_rows,
+                bool mn_major = false) {
+  auto enc = get_encode();
+  if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld_elems * elem_bytes};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  // fp32 operands read MN-major must land in the 32-byte-atom swizzle (see tc_common.cuh)
+  CUtensorMapSwizzle sw = (mn_major && elem_bytes == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = enc(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(2d rows=%ld cols=%ld ld=%ld box=%dx%d) failed: %d", rows, cols, ld_elems, box_cols, box_rows, (int)r); return -1; }
+  return 0;
+}
+// 4-D map over channels-last [N][H][W][C]; box = {Cb, Wb, Hb, Nb}
+int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb) {
+  auto enc = get_encode();
+  if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * elem_bytes, (cuuint64_t)W * C * elem_bytes, (cuuint64_t)H * W * C * elem_bytes};
+  cuuint32_t box[4] = {(cuuint32_t)Cb, (cuuint32_t)Wb, (cuuint32_t)Hb, (cuuint32_t)Nb};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+  CUresult r = enc(m, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(4d N=%d H=%d W=%d C=%d box=%d,%d,%d,%d) failed: %d", N, H, W, C, Cb, Wb, Hb, Nb, (int)r); return -1; }
+  return 0;
+}
+
+size_t smem_bytes(int b_bytes) { return (size_t)kStages * (kABytes + b_bytes) + sizeof(Pipe) + 1024; }
+int b_stage_bytes(int BN, int b_mn, int es) { int chunk = 128 / es, bk = 128 / es; return b_mn ? ((BN + chunk - 1) / chunk) * bk * 128 : BN * 128; }
+
+template <bool kTF32> int launch(const CUtensorMap& ma, const CUtensorMap& mb, const TcGemmParams& p, dim3 grid, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_tc_gemm<kTF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(kMaxBN * 128)));
+    attr_set = true;
+  }
+  k_tc_gemm<kTF32><<<grid, kThreads, smem_bytes(p.b_bytes), s>>>(ma, mb, p);
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pick_bn(int N) { return N <= 32 ? 32 : (N <= 64 ? 64 : 128); }
+
+}  // namespace
+
+extern "C" {
+
+// C[M,N] (+)= op(A) . op(B)^T with fp32 accumulation on tcgen05.
+//   a_mn = 0: A is [M][K] row-major (lda);   a_mn = 1: A is [K][M] row-major (lda)
+//   b_mn = 0: B is [N][K] row-major (ldb);   b_mn = 1: B is [K][N] row-major (ldb)
+// dtype: DCP_F32 (tf32 multiply) or DCP_BF16.  out: fp32 or bf16 (out_bf16), ldc elements.  ksplit > 1 => `out`
+// must be fp32 and zero-initialised (atomic accumulation; relu is rejected).  K must be a multiple of the 128-byte slab.
+int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
+                int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s) {
+  const int es = dtype == DCP_F32 ? 4 : 2, bk = 128 / es;
+  if (dtype != DCP_F32 && dtype != DCP_BF16) { dcp_set_error("tc gemm: dtype must be f32 or bf16"); return -1; }
+  if (K % bk) { dcp_set_error("tc gemm: K=%d must be a multiple of %d", K, bk); return -1; }
+  if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
+  TcGemmParams p{};
+  p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
+  p.b_bytes = b_stage_bytes(p.BN, b_mn, es);
+  p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
+  CUtensorMap ma, mb;
+  if (!a_mn) { if (make_map_2d(&ma, A, es, M, K, lda, bk, kBM)) return -1; }
+  else { if (make_map_2d(&ma, A, es, K, M, lda, bk, bk, true)) return -1; }
+  if (!b_mn) { if (make_map_2d(&mb, B, es, N, K, ldb, bk, p.BN)) return -1; }
+  else { if (make_map_2d(&mb, B, es, K, N, ldb, bk, bk, true)) return -1; }
+  dim3 grid((M + kBM - 1) / kBM, (N + p.BN - 1) / p.BN, ksplit < 1 ? 1 : ksplit);
+  return dtype == DCP_F32 ? launch<true>(ma, mb, p, grid, s) : launch<false>(ma, mb, p, grid, s);
+}
+
+// Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
+//   x: channels-last [N,H,W,C]; wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] (fp32 or bf16).
+// C must be a multiple of the 128-byte slab (32 f32 / 64 bf16).  (Wb,Hb,Nb): box of output pixels per CTA, product 128.
+int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho,
+                int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s) {
+  const int es = dtype == DCP_F32 ? 4 : 2, bk = 128 / es;
+  if (C % bk) { dcp_set_error("tc conv: C=%d must be a multiple of %d", C, bk); return -1; }
+  if (Wb * Hb * Nb != kBM) { dcp_set_error("tc conv: box %dx%dx%d must cover %d pixels", Wb, Hb, Nb, kBM); return -1; }
+  TcGemmParams p{};
+  p.N = Kout; p.BN = pick_bn(Kout); p.b_bytes = p.BN * 128; p.conv = 1; p.S = S; p.cchunks = C / bk; p.Cin = C; p.pad = pad;
+  p.k_stages = R * S * p.cchunks;
+  p.Wb = Wb; p.Hb = Hb; p.Nb = Nb; p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
+  p.out = y; p.ldc = Kout; p.bias = bias; p.relu = relu; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
+  p.M = p.tiles_w * p.tiles_h * ((N + Nb - 1) / Nb) * kBM;
+  CUtensorMap ma, mb;
+  if (make_map_4d(&ma, x, es, N, H, W, C, bk, Wb, Hb, Nb)) return -1;
+  if (make_map_2d(&mb, wmat, es, Kout, (long)R * S * C, (long)R * S * C, bk, p.BN)) return -1;
+  dim3 grid(p.M / kBM, (Kout + p.BN - 1) / p.BN, 1);
+  return dtype == DCP_F32 ? launch<true>(ma, mb, p, grid, s) : launch<false>(ma, mb, p, grid, s);
+}
+
+}  // extern "C"
+
+// Weight repack for the data-gradient: wt[c][(r', s', k)] = w[k][R-1-r'][S-1-s'][c]  (w is [K][R][S][C]).
+namespace {
+template <typename T> __global__ void k_flip_weights(const T* __restrict__ w, T* __restrict__ wt, int K, int R, int S, int C) {
+  const long total = (long)K * R * S * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    // i indexes wt: ((c * R + r') * S + s') * K + k
+    int k = i % K; long t = i / K; int s2 = t % S; t /= S; int r2 = t % R; int c = t / R;
+    wt[i] = w[(((long)k * R + (R - 1 - r2)) * S + (S - 1 - s2)) * C + c];
+  }
+}
+}  // namespace
+extern "C" int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s) {
+  long total = (long)K * R * S * C;
+  DISPATCH_ACT(dtype, (k_flip_weights<T><<<grid_1d(total, 256), 256, 0, s>>>((const T*)w, (T*)wt, K, R, S, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}

@@ -1,32 +1,138 @@
-"""tcgen05 / TMEM / TMA tensor-core paths (csrc/ops/gemm_tc.cu, conv_tc.cu): shape gating + launchers.
+"""tcgen05 / TMEM / TMA tensor-core paths (csrc/ops/gemm_tc.cu): shape gating + launchers.
 
 ``*_supported`` decide per shape whether the tensor-core kernel can take the op; everything else
-falls back to the CUDA-core kernels in conv_linear_simt.cu.
+falls back to the CUDA-core kernels in conv_linear_simt.cu.  fp32 tensors are multiplied in tf32 with
+fp32 accumulation (what cuDNN's default does for the reference's convolutions); bf16 stays bf16.
 """
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 
-_declared = False
+_lib = None
+NUM_SMS = 148
 
 
 def declare(lib) -> None:
-    global _declared
-    _declared = True
+    global _lib
+    vp, i, l = C.c_void_p, C.c_int, C.c_long
+    lib.dcp_tc_gemm.restype = C.c_int
+    lib.dcp_tc_gemm.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, vp]
+    lib.dcp_tc_conv.restype = C.c_int
+    lib.dcp_tc_conv.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
+    lib.dcp_flip_weights.restype = C.c_int
+    lib.dcp_flip_weights.argtypes = [vp, vp, i, i, i, i, i, vp]
+    _lib = lib
+
+
+def _k():
+    from . import cuda
+    return cuda
+
+
+def _bk(dtype) -> int:
+    return 32 if dtype == torch.float32 else 64
+
+
+def _ok_dtype(dtype) -> bool:
+    return dtype in (torch.float32, torch.bfloat16)
+
+
+def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit=1) -> None:
+    """out[M,N] (+)= op(A) op(B)^T on tcgen05 (see dcp_tc_gemm)."""
+    k = _k()
+    k._chk(_lib.dcp_tc_gemm(A.data_ptr(), B.data_ptr(), out.data_ptr(), k._p(bias), M, N, K, lda, ldb, ldc, int(a_mn), int(b_mn), k._dt(A),
+                            int(out.dtype == torch.bfloat16), int(bias is not None and bias.dtype == torch.bfloat16), int(relu), int(ksplit),
+                            k._stream()))
+
+
+def _ksplit(M: int, N: int, K: int, dtype) -> int:
+    tiles = -(-M // 128) * -(-N // (32 if N <= 32 else 64 if N <= 64 else 128))
+    stages = K // _bk(dtype)
+    if tiles >= NUM_SMS // 2 or stages < 8:
+        return 1
+    return max(1, min(stages // 2, NUM_SMS // tiles))
 
 
 def linear_supported(M: int, N: int, K: int, dtype) -> bool:
-    return False
+    """GEMM with output [M, N] and contraction K."""
+    return _ok_dtype(dtype) and K % _bk(dtype) == 0 and M % 8 == 0 and N % 8 == 0 and M >= 8 and N >= 16
+
+
+def linear_fwd(x2, w, b, y, relu) -> None:
+    M, K = x2.shape
+    N = w.shape[0]
+    ks = _ksplit(M, N, K, x2.dtype) if (y.dtype == torch.float32 and not relu) else 1
+    if ks > 1:
+        y.zero_()
+    gemm(x2, w, y, b, M, N, K, K, K, N, 0, 0, relu, ks)
+
+
+def linear_dgrad(dy, w, dx) -> None:
+    """dx[M,K] = dy[M,N] . w[N,K]: A = dy (K-major over N), B = w read MN-major."""
+    M, N = dy.shape
+    K = w.shape[1]
+    ks = _ksplit(M, K, N, dy.dtype) if dx.dtype == torch.float32 else 1
+    if ks > 1:
+        dx.zero_()
+    gemm(dy, w, dx, None, M, K, N, N, K, K, 0, 1, False, ks)
+
+
+def linear_wgrad(dy, x2, dw32, db32) -> None:
+    """dw[N,K] = dy[M,N]^T . x[M,K]: both operands MN-major (contraction over the batch M)."""
+    M, N = dy.shape
+    K = x2.shape[1]
+    ks = _ksplit(N, K, M, dy.dtype)
+    if ks > 1:
+        dw32.zero_()
+    gemm(dy, x2, dw32, None, N, K, M, N, K, K, 1, 1, False, ks)
+    if db32 is not None:
+        k = _k()
+        k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), M, N, k._dt(dy), k._stream()))
+
+
+def _pick_box(Wo: int, Ho: int, N: int):
+    best = None
+    for wb in (1, 2, 4, 8, 16, 32, 64, 128):
+        for hb in (1, 2, 4, 8, 16, 32, 64, 128):
+            if 128 % (wb * hb):
+                continue
+            nb = 128 // (wb * hb)
+            if nb < 1:
+                continue
+            cover = (-(-Wo // wb) * wb) * (-(-Ho // hb) * hb) * (-(-N // nb) * nb)
+            key = (cover, -wb)
+            if best is None or key < best[0]:
+                best = (key, (wb, hb, nb))
+    return best[1]
 
 
 def conv_fwd_supported(p, dtype) -> bool:
-    return False
+    return _ok_dtype(dtype) and p.stride == 1 and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16 and os.environ.get("DCP_TC_CONV", "1") == "1"
+
+
+def conv2d_fwd(x, w, b, y, p, relu) -> None:
+    k = _k()
+    wb, hb, nb = _pick_box(p.Wo, p.Ho, p.N)
+    k._chk(_lib.dcp_tc_conv(x.data_ptr(), w.data_ptr(), y.data_ptr(), k._p(b), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo, wb, hb, nb,
+                            k._dt(x), int(y.dtype == torch.bfloat16), int(b is not None and b.dtype == torch.bfloat16), int(relu), k._stream()))
 
 
 def conv_dgrad_supported(p, dtype) -> bool:
-    return False
+    return (_ok_dtype(dtype) and p.stride == 1 and p.K % _bk(dtype) == 0 and p.C % 8 == 0 and p.C >= 16 and p.R - 1 - p.pad >= 0
+            and os.environ.get("DCP_TC_CONV", "1") == "1")
+
+
+def conv2d_dgrad(dy, w, dx, p) -> None:
+    """dx = conv(dy, flipped weights) with padding R-1-pad: the same implicit-GEMM kernel as forward."""
+    k = _k()
+    wt = torch.empty(p.C * p.R * p.S * p.K, dtype=w.dtype, device=w.device)
+    k._chk(_lib.dcp_flip_weights(w.data_ptr(), wt.data_ptr(), p.K, p.R, p.S, p.C, k._dt(w), k._stream()))
+    wb, hb, nb = _pick_box(p.W, p.H, p.N)
+    k._chk(_lib.dcp_tc_conv(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), None, p.N, p.Ho, p.Wo, p.K, p.C, p.R, p.S, p.R - 1 - p.pad, p.H, p.W,
+                            wb, hb, nb, k._dt(dy), int(dx.dtype == torch.bfloat16), 0, 0, k._stream()))
 
 
 def conv_wgrad_supported(p, dtype) -> bool:

@@ -1,0 +1,83 @@
+"""tcgen05 GEMM / implicit-GEMM conv kernels vs fp32 references: every operand-major combination,
+tf32 and bf16, split-K, bias/ReLU epilogue, ragged M/N, conv forward + data-gradient."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def _tc():
+    from distributed_compute_pytorch_b200.ops import cuda, tc
+    cuda.lib()
+    return tc
+
+
+def _rel_err(a, b):
+    return ((a.double() - b.double()).abs().max() / (b.double().abs().max() + 1e-12)).item()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+@pytest.mark.parametrize("M,N,K", [(128, 128, 256), (256, 64, 128), (200, 72, 384), (128, 32, 64), (384, 256, 1024)])
+def test_gemm_all_majors(dtype, a_mn, b_mn, M, N, K):
+    tc = _tc()
+    torch.manual_seed(M + N + K)
+    A = torch.randn(M, K, device=DEV)
+    B = torch.randn(N, K, device=DEV)
+    ref = A.to(dtype).double() @ B.to(dtype).double().t()
+    Ast = (A.t().contiguous() if a_mn else A).to(dtype).contiguous()
+    Bst = (B.t().contiguous() if b_mn else B).to(dtype).contiguous()
+    out = torch.full((M, N), float("nan"), device=DEV)
+    tc.gemm(Ast, Bst, out, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn)
+    torch.cuda.synchronize()
+    tol = 2e-3 if dtype == torch.float32 else 1e-5   # tf32 multiplies truncate fp32 inputs; bf16 inputs are exact
+    assert _rel_err(out, ref) < tol, (_rel_err(out, ref), dtype, a_mn, b_mn)
+
+
+def test_gemm_splitk_bias_relu_bf16_out():
+    tc = _tc()
+    torch.manual_seed(0)
+    M, N, K = 128, 128, 9216   # fc1 of the reference (ref:main.py:27)
+    A, B, bias = torch.randn(M, K, device=DEV), torch.randn(N, K, device=DEV) * 0.02, torch.randn(N, device=DEV)
+    ref = A.double() @ B.double().t() + bias.double()
+    for ks in (1, 4, 144):
+        out = torch.zeros(M, N, device=DEV)
+        tc.gemm(A, B, out, bias, M, N, K, K, K, N, 0, 0, False, ks)
+        assert _rel_err(out, ref) < 2e-3, ks
+    out = torch.empty(M, N, device=DEV)
+    tc.gemm(A, B, out, bias, M, N, K, K, K, N, 0, 0, True, 1)
+    assert _rel_err(out, ref.clamp(min=0)) < 2e-3
+    Ab, Bb, bb = A.bfloat16(), B.bfloat16(), bias.bfloat16()
+    outb = torch.empty(M, N, device=DEV, dtype=torch.bfloat16)
+    tc.gemm(Ab, Bb, outb, bb, M, N, K, K, K, N, 0, 0, False, 1)
+    refb = Ab.double() @ Bb.double().t() + bb.double()
+    assert _rel_err(outb, refb) < 1e-2
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("N,C,H,W,K,R,pad", [(128, 32, 26, 26, 64, 3, 0), (4, 64, 14, 14, 128, 3, 1), (6, 128, 7, 9, 64, 1, 0), (2, 64, 20, 20, 32, 3, 1)])
+def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
+    from distributed_compute_pytorch_b200.ops import cuda
+    tc = _tc()
+    if C % (32 if dtype == torch.float32 else 64):
+        pytest.skip("C not a multiple of the K slab for this dtype")
+    torch.manual_seed(0)
+    x = torch.randn(N, C, H, W, device=DEV).to(dtype).contiguous(memory_format=torch.channels_last)
+    w = (torch.randn(K, C, R, R, device=DEV) * 0.1).to(dtype).contiguous(memory_format=torch.channels_last)
+    b = torch.randn(K, device=DEV).to(dtype)
+    p = cuda._convp(x.shape, w.shape, 1, pad)
+    assert tc.conv_fwd_supported(p, dtype)
+    y = torch.empty((N, K, p.Ho, p.Wo), dtype=dtype, device=DEV, memory_format=torch.channels_last)
+    tc.conv2d_fwd(x, w, b, y, p, True)
+    ref = F.relu(F.conv2d(x.double(), w.double(), b.double(), 1, pad))
+    tol = 3e-3 if dtype == torch.float32 else 1.5e-2
+    assert _rel_err(y, ref) < tol, _rel_err(y, ref)
+    if tc.conv_dgrad_supported(p, dtype):
+        dy = torch.randn_like(y)
+        dx = torch.empty_like(x)
+        tc.conv2d_dgrad(dy, w, dx, p)
+        xr = x.double().requires_grad_(True)
+        F.conv2d(xr, w.double(), None, 1, pad).backward(dy.double())
+        assert _rel_err(dx, xr.grad) < tol, _rel_err(dx, xr.grad)
