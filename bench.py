@@ -35,6 +35,8 @@ def parse():
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (the reference's --batch_size default, ref:main.py:139)")
     ap.add_argument("--lr", type=float, default=0.001)
     ap.add_argument("--no-graph", action="store_true", help="ours: eager DDP path instead of the CUDA-graph step")
+    ap.add_argument("--engine", default="fused", choices=["fused", "autograd"],
+                    help="ours: fused = parallel.FusedConvNetTrainer (flat-shift tcgen05 convs); autograd = layer-by-layer ops under GraphedTrainStep")
     return ap.parse_args()
 
 
@@ -85,7 +87,11 @@ def run_ours(opt, rank, local_rank, world):
     xs, ys = make_pool(opt.batch, dev, pinned=False, seed=100 + rank)
     hx, hy = make_pool(opt.batch, dev, pinned=True, seed=100 + rank)
 
-    if opt.no_graph:
+    if opt.engine == "fused":
+        from distributed_compute_pytorch_b200.parallel.convnet_trainer import FusedConvNetTrainer
+        step = FusedConvNetTrainer(model, optimizer, opt.batch, use_graph=not opt.no_graph)
+        per_step = step.launches_per_step if not opt.no_graph else None
+    elif opt.no_graph:
         def step(x, y):
             optimizer.zero_grad()
             loss = ops.nll_loss(model(x.to(dev, non_blocking=True)), y.to(dev, non_blocking=True))
@@ -132,7 +138,7 @@ def run_ours(opt, rank, local_rank, world):
         "dtype": "fp32 (tf32 tensor-core multiply where tcgen05 kernels are used, the precision cuDNN's default gives the reference)",
         "data": "synthetic MNIST-shaped [B,1,28,28] float32 + int64 labels, random-init weights", "impl": "ours",
         "config": {"model": "ConvNet (ref:main.py:20-45)", "global_batch": gb, "per_gpu_batch": opt.batch, "seq_len": None,
-                   "parallelism": f"dp{world}", "optimizer": "Adadelta lr=0.001", "graph": not opt.no_graph,
+                   "parallelism": f"dp{world}", "optimizer": "Adadelta lr=0.001", "graph": not opt.no_graph, "engine": opt.engine,
                    "l2": f"inputs larger than L2: rotating pool of {POOL_BATCHES} batches ({POOL_BATCHES * opt.batch * 784 * 4 / 1e6:.0f} MB)",
                    "nvls": be.nvls},
         "clocks": clocks.summary(),

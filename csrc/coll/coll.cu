@@ -163,14 +163,25 @@ __global__ void __launch_bounds__(kThreads) k_allreduce_twoshot(DcpDevCtx c, con
 // Byte movers (dtype-agnostic): broadcast / all_gather / gather / scatter.
 // mode bits: which of the W "lanes" this rank pushes and where.
 // -------------------------------------------------------------------------------------------------
+// The byte range is cut into 16-byte chunks and chunk c is ALWAYS handled by the thread with c % stride == tid,
+// whatever the alignment of the two pointers.  The staged kernels rely on this: the CTA that pushed a chunk
+// (and chose the parity half from its own call counter) is the CTA that later copies it out.
 __device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nbytes, size_t tid, size_t stride, bool stream_store) {
-  const bool al = ((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0;
-  size_t nvec = al ? nbytes / 16 : 0;
-  for (size_t v = tid; v < nvec; v += stride) {
-    uint4 x = ld16(src + v * 16);
-    if (stream_store) st16_stream(dst + v * 16, x); else st16(dst + v * 16, x);
+  const uintptr_t mis = reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src);
+  const bool al16 = (mis & 15) == 0, al4 = (mis & 3) == 0;
+  const size_t nchunk = (nbytes + 15) / 16;
+  for (size_t c = tid; c < nchunk; c += stride) {
+    const size_t b = c * 16;
+    const size_t len = nbytes - b < 16 ? nbytes - b : 16;
+    if (al16 && len == 16) {
+      uint4 x = ld16(src + b);
+      if (stream_store) st16_stream(dst + b, x); else st16(dst + b, x);
+    } else if (al4 && (len & 3) == 0) {
+      for (size_t j = 0; j < len; j += 4) *reinterpret_cast<uint32_t*>(dst + b + j) = *reinterpret_cast<const uint32_t*>(src + b + j);
+    } else {
+      for (size_t j = 0; j < len; ++j) dst[b + j] = src[b + j];
+    }
   }
-  for (size_t i = nvec * 16 + tid; i < nbytes; i += stride) dst[i] = src[i];
 }
 
 // Rank `root` pushes nbytes to every rank's buffer at `off` (+ parity half when staged), everyone

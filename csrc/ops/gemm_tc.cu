@@ -19,8 +19,12 @@ struct TcGemmParams {
   int BN;                   // N tile (32 / 64 / 128 <= kMaxBN)
   int b_bytes;              // bytes of one B stage (>= BN * 128; MN-major B is loaded in whole 128-byte chunks)
   int a_mn, b_mn;           // operand majors
-  // implicit conv (A via 4-D map): stage s -> tap = s / cchunks, channel chunk = s % cchunks
+  // conv = 1, implicit conv forward / data-grad (A via 4-D map): stage s -> tap = s / cchunks, channel chunk = s % cchunks
+  // conv = 2, conv weight-grad: K runs over boxes of output pixels; A chunk u of accumulator group g is the
+  //           activation box shifted by filter tap (unit / cchunks) for channel chunk (unit % cchunks); B is the dy box
   int conv, S, cchunks, Cin, pad, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
+  int stages;                   // pipeline depth (<= kStages)
+  int groups, units, a_bytes;   // accumulator groups per CTA (1 except wgrad), (tap, chunk) units in total, bytes of one A stage
   // epilogue
   void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
 };
@@ -28,7 +32,8 @@ struct TcGemmParams {
 namespace {
 using namespace tc;
 
-constexpr int kBM = 128, kStages = 4, kMaxBN = 128, kTmemCols = 128;
+constexpr int kBM = 128, kStages = 4, kMaxBN = 128;
+constexpr int kMaxGroups = 3;                 // wgrad: up to 3 accumulator groups (3 x 16 KB of A per stage)
 constexpr int kABytes = kBM * 128;            // 16 KB per stage
 constexpr int kThreads = 192;
 
@@ -37,15 +42,17 @@ struct __align__(8) Pipe {
   uint32_t tmem_base;
 };
 
-template <bool kTF32>
+template <bool kTF32, int kTmemCols>
 __global__ void __launch_bounds__(kThreads, 1)
 k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int b_bytes = p.b_bytes;
-  const int stage_bytes = kABytes + b_bytes;
-  Pipe* pipe = reinterpret_cast<Pipe*>(smem + kStages * stage_bytes);
+  const int a_bytes = p.a_bytes;
+  const int stage_bytes = a_bytes + b_bytes;
+  const int nstages = p.stages;
+  Pipe* pipe = reinterpret_cast<Pipe*>(smem + nstages * stage_bytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   constexpr int kElem = kTF32 ? 4 : 2;
   constexpr int kBK = 128 / kElem;             // elements per K slab
@@ -75,7 +82,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int m_tile = blockIdx.x, n_tile = blockIdx.y;
   // conv: decode the tile into (image group, box row, box col)
   int n0 = 0, h0 = 0, w0 = 0;
-  if (p.conv) {
+  if (p.conv == 1) {
     int t = m_tile;
     const int tw = t % p.tiles_w; t /= p.tiles_w;
     const int th = t % p.tiles_h; t /= p.tiles_h;
@@ -86,12 +93,31 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     if (warp == 0 && lane == 0) {
       // ================= TMA producer =================
       for (int i = 0; i < nst; ++i) {
-        const int st = i % kStages, ph = (i / kStages) & 1;
+        const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(&pipe->empty[st], ph ^ 1);
         uint8_t* sa = smem + st * stage_bytes;
-        uint8_t* sb = sa + kABytes;
-        mbar_expect_tx(&pipe->full[st], kABytes + b_bytes);
+        uint8_t* sb = sa + a_bytes;
         const int ks = ks0 + i;
+        if (p.conv == 2) {
+          // weight-grad: this stage = one box of kBK output pixels
+          int t = ks;
+          const int tw = t % p.tiles_w; t /= p.tiles_w;
+          const int th = t % p.tiles_h; t /= p.tiles_h;
+          const int pn = t * p.Nb, ph0 = th * p.Hb, pw0 = tw * p.Wb;
+          constexpr int kUnitsPerGroup = kBM / kChunk;
+          const int u0 = m_tile * p.groups * kUnitsPerGroup;
+          const int nu = min(p.units - u0, p.groups * kUnitsPerGroup);
+          const int nbc = (p.BN + kChunk - 1) / kChunk;
+          mbar_expect_tx(&pipe->full[st], (nu + nbc) * (kBK * 128));
+          for (int j = 0; j < nbc; ++j)
+            tma_load_4d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, pw0, ph0, pn);
+          for (int u = 0; u < nu; ++u) {
+            const int unit = u0 + u, tap = unit / p.cchunks, cc = unit % p.cchunks;
+            tma_load_4d(sa + u * (kBK * 128), &map_a, &pipe->full[st], cc * kChunk, pw0 - p.pad + tap % p.S, ph0 - p.pad + tap / p.S, pn);
+          }
+          continue;
+        }
+        mbar_expect_tx(&pipe->full[st], kABytes + b_bytes);
         int kb = ks * kBK;  // K coordinate for B (and for GEMM A)
         if (p.conv) {
           const int tap = ks / p.cchunks, cc = ks % p.cchunks;
@@ -115,17 +141,21 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       // ================= MMA issuer =================
       const uint32_t idesc = make_idesc(kTF32, p.a_mn != 0, p.b_mn != 0, kBM, p.BN);
       for (int i = 0; i < nst; ++i) {
-        const int st = i % kStages, ph = (i / kStages) & 1;
+        const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(&pipe->full[st], ph);
         tc_fence_after();
-        const uint32_t sa = smem_u32(smem + st * stage_bytes), sb = sa + kABytes;
+        const uint32_t sa0 = smem_u32(smem + st * stage_bytes), sb = sa0 + a_bytes;
+        for (int g = 0; g < p.groups; ++g) {
+        const uint32_t sa = sa0 + g * kABytes;
+        const uint32_t tmem_g = tmem + g * p.BN;
 #pragma unroll
         for (int j = 0; j < kBK / kUmmaK; ++j) {
           // MN-major: k-rows are 128 B apart (TMA box rows); tf32 needs the BASE32B layout (4-row atoms)
           constexpr uint32_t kMnSbo = kTF32 ? 512 : 1024, kMnLayout = kTF32 ? 1 : 2;
           const uint64_t da = p.a_mn ? make_smem_desc(sa + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sa + j * 32, 0, 1024);
           const uint64_t db = p.b_mn ? make_smem_desc(sb + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sb + j * 32, 0, 1024);
-          umma<kTF32>(tmem, da, db, idesc, (i | j) != 0);
+          umma<kTF32>(tmem_g, da, db, idesc, (i | j) != 0);
+        }
         }
         umma_commit(&pipe->empty[st]);   // smem slot reusable once these MMAs retire
       }
@@ -140,6 +170,26 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       mbar_wait(&pipe->acc_full, 0);
       tc_fence_after();
     }
+    if (p.conv == 2) {
+      // weight-grad: row = (unit-in-group, channel-in-chunk), column = output channel; dw[k][tap][c] += acc
+      constexpr int kUnitsPerGroup = kBM / kChunk;
+      for (int g = 0; g < p.groups; ++g) {
+        const int unit = (m_tile * p.groups + g) * kUnitsPerGroup + row / kChunk;
+        const bool valid = unit < p.units;
+        const int tap = unit / p.cchunks, cc = unit % p.cchunks;
+        float* orow = (float*)p.out + (long)tap * p.Cin + cc * kChunk + (row % kChunk);
+        for (int c0 = 0; c0 < p.BN; c0 += 32) {
+          uint32_t r[32];
+          if (nst > 0) { tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + g * p.BN + c0, r); tmem_ld_wait(); }
+          if (!valid || nst <= 0) continue;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const int k = n_tile * p.BN + c0 + j;
+            if (k < p.N) atomicAdd(orow + (long)k * p.ldc, __uint_as_float(r[j]));   // lanes = consecutive c: coalesced
+          }
+        }
+      }
+    } else {
     long out_row = -1;
     if (p.conv) {
       const int nl = row / (p.Hb * p.Wb), hl = (row / p.Wb) % p.Hb, wl = row % p.Wb;
@@ -201,6 +251,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         }
       }
     }
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -235,7 +286,7 @@ int make_map_2d(CUtensorMap* m, const void* base, int elem_bytes, long rows, lon
   return 0;
 }
 // 4-D map over channels-last [N][H][W][C]; box = {Cb, Wb, Hb, Nb}
-int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb) {
+int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb, bool mn_major = false) {
   auto enc = get_encode();
   if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
@@ -243,22 +294,29 @@ int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, 
   cuuint32_t box[4] = {(cuuint32_t)Cb, (cuuint32_t)Wb, (cuuint32_t)Hb, (cuuint32_t)Nb};
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
-  CUresult r = enc(m, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  CUtensorMapSwizzle sw = (mn_major && elem_bytes == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
+  CUresult r = enc(m, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(4d N=%d H=%d W=%d C=%d box=%d,%d,%d,%d) failed: %d", N, H, W, C, Cb, Wb, Hb, Nb, (int)r); return -1; }
   return 0;
 }
 
-size_t smem_bytes(int b_bytes) { return (size_t)kStages * (kABytes + b_bytes) + sizeof(Pipe) + 1024; }
+size_t smem_bytes(int stages, int a_bytes, int b_bytes) { return (size_t)stages * (a_bytes + b_bytes) + sizeof(Pipe) + 1024; }
+constexpr int kMaxSmem = 200 * 1024;
 int b_stage_bytes(int BN, int b_mn, int es) { int chunk = 128 / es, bk = 128 / es; return b_mn ? ((BN + chunk - 1) / chunk) * bk * 128 : BN * 128; }
 
-template <bool kTF32> int launch(const CUtensorMap& ma, const CUtensorMap& mb, const TcGemmParams& p, dim3 grid, cudaStream_t s) {
+template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUtensorMap& mb, const TcGemmParams& p, dim3 grid, cudaStream_t s) {
   static bool attr_set = false;
   if (!attr_set) {
-    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_tc_gemm<kTF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(kMaxBN * 128)));
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_tc_gemm<kTF32, kTmemCols>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        kMaxSmem));
     attr_set = true;
   }
-  k_tc_gemm<kTF32><<<grid, kThreads, smem_bytes(p.b_bytes), s>>>(ma, mb, p);
+  TcGemmParams q = p;
+  q.stages = kStages;
+  while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes) > (size_t)kMaxSmem) --q.stages;
+  if (smem_bytes(q.stages, q.a_bytes, q.b_bytes) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }
+  k_tc_gemm<kTF32, kTmemCols><<<grid, kThreads, smem_bytes(q.stages, q.a_bytes, q.b_bytes), s>>>(ma, mb, q);
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -282,7 +340,7 @@ int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M
   if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
   TcGemmParams p{};
   p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
-  p.b_bytes = b_stage_bytes(p.BN, b_mn, es);
+  p.b_bytes = b_stage_bytes(p.BN, b_mn, es); p.a_bytes = kABytes; p.groups = 1;
   p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
   CUtensorMap ma, mb;
   if (!a_mn) { if (make_map_2d(&ma, A, es, M, K, lda, bk, kBM)) return -1; }
@@ -290,7 +348,7 @@ int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M
   if (!b_mn) { if (make_map_2d(&mb, B, es, N, K, ldb, bk, p.BN)) return -1; }
   else { if (make_map_2d(&mb, B, es, K, N, ldb, bk, bk, true)) return -1; }
   dim3 grid((M + kBM - 1) / kBM, (N + p.BN - 1) / p.BN, ksplit < 1 ? 1 : ksplit);
-  return dtype == DCP_F32 ? launch<true>(ma, mb, p, grid, s) : launch<false>(ma, mb, p, grid, s);
+  return dtype == DCP_F32 ? launch<true, 128>(ma, mb, p, grid, s) : launch<false, 128>(ma, mb, p, grid, s);
 }
 
 // Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
@@ -302,7 +360,7 @@ int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int 
   if (C % bk) { dcp_set_error("tc conv: C=%d must be a multiple of %d", C, bk); return -1; }
   if (Wb * Hb * Nb != kBM) { dcp_set_error("tc conv: box %dx%dx%d must cover %d pixels", Wb, Hb, Nb, kBM); return -1; }
   TcGemmParams p{};
-  p.N = Kout; p.BN = pick_bn(Kout); p.b_bytes = p.BN * 128; p.conv = 1; p.S = S; p.cchunks = C / bk; p.Cin = C; p.pad = pad;
+  p.N = Kout; p.BN = pick_bn(Kout); p.b_bytes = p.BN * 128; p.a_bytes = kABytes; p.groups = 1; p.conv = 1; p.S = S; p.cchunks = C / bk; p.Cin = C; p.pad = pad;
   p.k_stages = R * S * p.cchunks;
   p.Wb = Wb; p.Hb = Hb; p.Nb = Nb; p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
   p.out = y; p.ldc = Kout; p.bias = bias; p.relu = relu; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
@@ -311,7 +369,41 @@ int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int 
   if (make_map_4d(&ma, x, es, N, H, W, C, bk, Wb, Hb, Nb)) return -1;
   if (make_map_2d(&mb, wmat, es, Kout, (long)R * S * C, (long)R * S * C, bk, p.BN)) return -1;
   dim3 grid(p.M / kBM, (Kout + p.BN - 1) / p.BN, 1);
-  return dtype == DCP_F32 ? launch<true>(ma, mb, p, grid, s) : launch<false>(ma, mb, p, grid, s);
+  return dtype == DCP_F32 ? launch<true, 128>(ma, mb, p, grid, s) : launch<false, 128>(ma, mb, p, grid, s);
+}
+
+// Convolution weight gradient (stride 1) on tcgen05: dw[k][r][s][c] += sum_pixels dy[n,ho,wo,k] * x[n, ho-pad+r, wo-pad+s, c].
+// Both operands are read MN-major straight from the channels-last tensors (no im2col, no transposes): the K
+// dimension of the MMA runs over boxes of (Wb x Hb x Nb) = 32 (f32) / 64 (bf16) output pixels, the A operand of
+// accumulator group g is made of 128-byte channel chunks taken from the activation shifted by different filter
+// taps, B is the matching box of dy.  gridDim.z splits the pixel boxes; partial sums meet in fp32 atomics, so
+// dw32 ([Kout][R*S*C] fp32) is zeroed here.
+int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo,
+                      int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s) {
+  const int es = dtype == DCP_F32 ? 4 : 2, chunk = 128 / es;
+  if (C % chunk) { dcp_set_error("tc wgrad: C=%d must be a multiple of %d", C, chunk); return -1; }
+  if (Wb * Hb * Nb != chunk) { dcp_set_error("tc wgrad: pixel box must hold %d pixels", chunk); return -1; }
+  TcGemmParams p{};
+  p.conv = 2; p.N = Kout; p.BN = pick_bn(Kout); p.a_mn = 1; p.b_mn = 1; p.S = S; p.cchunks = C / chunk; p.Cin = C; p.pad = pad;
+  p.units = R * S * p.cchunks;
+  const int upg = kBM / chunk;                       // units per accumulator group
+  const int groups_total = (p.units + upg - 1) / upg;
+  p.groups = groups_total < kMaxGroups ? groups_total : kMaxGroups;
+  if (p.groups * p.BN > 512) p.groups = 512 / p.BN;
+  p.a_bytes = p.groups * kABytes;
+  p.b_bytes = b_stage_bytes(p.BN, 1, es);
+  p.Wb = Wb; p.Hb = Hb; p.Nb = Nb; p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
+  p.k_stages = p.tiles_w * p.tiles_h * ((N + Nb - 1) / Nb);
+  p.out = dw32; p.ldc = (long)R * S * C; p.atomic = 1;
+  DCP_CUDA_CHECK(cudaMemsetAsync(dw32, 0, sizeof(float) * (size_t)Kout * R * S * C, s));
+  CUtensorMap ma, mb;
+  if (make_map_4d(&ma, x, es, N, H, W, C, chunk, Wb, Hb, Nb, true)) return -1;
+  if (make_map_4d(&mb, dy, es, N, Ho, Wo, Kout, chunk, Wb, Hb, Nb, true)) return -1;
+  const int gtiles = (groups_total + p.groups - 1) / p.groups;
+  if (zsplit < 1) zsplit = 1;
+  if (zsplit > p.k_stages) zsplit = p.k_stages;
+  dim3 grid(gtiles, (Kout + p.BN - 1) / p.BN, zsplit);
+  return dtype == DCP_F32 ? launch<true, 512>(ma, mb, p, grid, s) : launch<false, 512>(ma, mb, p, grid, s);
 }
 
 }  // extern "C"

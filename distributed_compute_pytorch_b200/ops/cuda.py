@@ -58,6 +58,11 @@ def lib():
             "dcp_linear_wgrad_simt": [vp, vp, vp, vp, i, i, i, i, vp],
             "dcp_colsum": [vp, vp, l, i, i, vp], "dcp_cast_from_f32": [vp, vp, l, i, vp],
             "dcp_counter_advance": [vp, vp],
+            "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
+            "dcp_convnet_conv1_fwd": [vp, vp, vp, vp, i, vp],
+            "dcp_convnet_pool_fwd": [vp, vp, vp, i, f, ull, ull, vp, i, vp],
+            "dcp_convnet_pool_bwd": [vp, vp, vp, vp, i, f, ull, ull, vp, i, vp],
+            "dcp_convnet_conv1_wgrad": [vp, vp, vp, vp, i, vp],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)

@@ -22,6 +22,8 @@ def declare(lib) -> None:
     lib.dcp_tc_gemm.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, vp]
     lib.dcp_tc_conv.restype = C.c_int
     lib.dcp_tc_conv.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
+    lib.dcp_tc_conv_wgrad.restype = C.c_int
+    lib.dcp_tc_conv_wgrad.argtypes = [vp, vp, vp] + [i] * 15 + [vp]
     lib.dcp_flip_weights.restype = C.c_int
     lib.dcp_flip_weights.argtypes = [vp, vp, i, i, i, i, i, vp]
     _lib = lib
@@ -93,13 +95,13 @@ def linear_wgrad(dy, x2, dw32, db32) -> None:
         k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), M, N, k._dt(dy), k._stream()))
 
 
-def _pick_box(Wo: int, Ho: int, N: int):
+def _pick_box(Wo: int, Ho: int, N: int, pixels: int = 128):
     best = None
     for wb in (1, 2, 4, 8, 16, 32, 64, 128):
         for hb in (1, 2, 4, 8, 16, 32, 64, 128):
-            if 128 % (wb * hb):
+            if pixels % (wb * hb):
                 continue
-            nb = 128 // (wb * hb)
+            nb = pixels // (wb * hb)
             if nb < 1:
                 continue
             cover = (-(-Wo // wb) * wb) * (-(-Ho // hb) * hb) * (-(-N // nb) * nb)
@@ -136,4 +138,23 @@ def conv2d_dgrad(dy, w, dx, p) -> None:
 
 
 def conv_wgrad_supported(p, dtype) -> bool:
-    return False
+    return (_ok_dtype(dtype) and p.stride == 1 and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16
+            and os.environ.get("DCP_TC_CONV", "1") == "1")
+
+
+def conv2d_wgrad(dy, x, dw32, db32, p) -> None:
+    """dw (fp32 [K,R,S,C]) on tcgen05 with both operands read MN-major from the channels-last tensors."""
+    k = _k()
+    chunk = _bk(dy.dtype)
+    wb, hb, nb = _pick_box(p.Wo, p.Ho, p.N, chunk)
+    boxes = -(-p.Wo // wb) * -(-p.Ho // hb) * -(-p.N // nb)
+    units = p.R * p.S * (p.C // chunk)
+    groups_total = -(-units // (128 // chunk))
+    bn = 32 if p.K <= 32 else 64 if p.K <= 64 else 128
+    g = max(1, min(3, groups_total, 512 // bn))
+    ctas = -(-groups_total // g) * -(-p.K // bn)
+    zsplit = max(1, min(boxes, (2 * NUM_SMS) // ctas if ctas < NUM_SMS else 1))
+    k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo,
+                                  wb, hb, nb, k._dt(dy), zsplit, k._stream()))
+    if db32 is not None:
+        k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), p.N * p.Ho * p.Wo, p.K, k._dt(dy), k._stream()))

@@ -1,0 +1,186 @@
+"""Fused training step for the flagship model (the reference's ConvNet, ref:main.py:20-45, trained by the
+loop at ref:main.py:55-63): forward, loss, backward, bucketed gradient all-reduce and Adadelta update
+issued as ~30 hand-written kernels with no autograd bookkeeping in between, captured in ONE CUDA graph.
+
+Design notes
+* Activations of the convolutional trunk live in the flat 26x26 frame of conv1's output
+  (csrc/ops/conv_flat_tc.cu): conv2 forward, its data-gradient and its weight-gradient are shifted GEMMs on
+  tcgen05 with the filter resident in shared memory and each pixel tile loaded once.
+* Gradients are written straight into the DDP bucket views (no copy-in); bucket 0 (fc2, batchnorm, fc1 -
+  4.7 MB) is all-reduced on the side stream while the convolution backward is still running, bucket 1
+  (conv2, conv1 - 75 KB) right after - the same order and sizes as the library reducer uses for this model.
+* Every hyper-parameter the kernels need (lr, step, dropout stream) is read from device memory, so StepLR and
+  fresh dropout masks work across graph replays.
+Semantics are those of ``loss = nll_loss(model(x), y); loss.backward(); optimizer.step()`` on the same
+weights (tests/test_convnet_trainer_gpu.py checks gradients against the layer-by-layer autograd path).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import distributed as dist
+from ..models.convnet import ConvNet
+from ..ops import cuda as K
+from ..ops import tc
+from ..types import ReduceOp
+from .ddp import DistributedDataParallel
+
+READY_ORDER = ["fc2.bias", "fc2.weight", "batchnorm.weight", "batchnorm.bias", "fc1.bias", "fc1.weight",
+               "conv2.weight", "conv2.bias", "conv1.weight", "conv1.bias"]
+
+
+class FusedConvNetTrainer:
+    def __init__(self, model, optimizer, batch_size: int, use_graph: bool = True, seed: Optional[int] = None):
+        self.ddp = model if isinstance(model, DistributedDataParallel) else None
+        self.net: ConvNet = model.module if self.ddp is not None else model
+        if not isinstance(self.net, ConvNet):
+            raise TypeError("FusedConvNetTrainer drives models.ConvNet (optionally DDP-wrapped)")
+        self.opt, self.N = optimizer, int(batch_size)
+        net, N = self.net, self.N
+        dev = net.fc1.weight.device
+        self.dev = dev
+        K.lib()
+        self.world = dist.get_world_size() if dist.is_initialized() else 1
+        self.be = dist._world().cuda if (dist.is_initialized() and self.world > 1) else None
+        names = dict(net.named_parameters())
+        # ---- gradient storage: DDP bucket views (rebuilt in the known ready order) or one private flat buffer
+        if self.ddp is not None:
+            pos = {id(q): i for i, q in enumerate(self.ddp._params)}
+            order = [pos[id(names[n])] for n in READY_ORDER]
+            self.ddp._build_buckets(order, limits=[self.ddp.first_bucket_bytes, self.ddp.bucket_bytes_cap])
+            self.ddp._rebuilt = True
+            for i, p in enumerate(self.ddp._params):
+                p.grad = self.ddp._view_of[i]
+            self.buckets = [b.flat for b in self.ddp._buckets]
+        else:
+            total = sum(-(-names[n].numel() // 4) * 4 for n in READY_ORDER)
+            flat = torch.zeros(total, dtype=torch.float32, device=dev)
+            off = 0
+            for n in READY_ORDER:
+                p = names[n]
+                v = flat[off: off + p.numel()]
+                p.grad = v.view(p.shape) if p.is_contiguous() else v.as_strided(p.shape, p.stride())
+                off += -(-p.numel() // 4) * 4
+            self.buckets = [flat]
+        f32 = dict(dtype=torch.float32, device=dev)
+        P = N * 676
+        self.x = torch.zeros(N, 1, 28, 28, **f32)
+        self.y = torch.zeros(N, dtype=torch.int64, device=dev)
+        self.a1 = torch.empty(P, 32, **f32)
+        self.a2 = torch.empty(P, 64, **f32)
+        self.pooled = torch.empty(N, 9216, **f32)
+        self.arg = torch.empty(N * 9216, dtype=torch.uint8, device=dev)
+        self.h1 = torch.empty(N, 128, **f32); self.h2 = torch.empty(N, 128, **f32); self.h3 = torch.empty(N, 128, **f32)
+        self.logits = torch.empty(N, 10, **f32)
+        self.loss = torch.zeros((), **f32); self.lse = torch.empty(N, **f32); self.one = torch.ones((), **f32)
+        self.bn_scratch = torch.empty(4 * 128 + 2, dtype=torch.float64, device=dev)
+        self.bn_mean = torch.empty(128, **f32); self.bn_rstd = torch.empty(128, **f32)
+        self.dlogits = torch.empty(N, 10, **f32); self.dh3 = torch.empty(N, 128, **f32); self.dh2 = torch.empty(N, 128, **f32)
+        self.dh1 = torch.empty(N, 128, **f32); self.dpooled = torch.empty(N, 9216, **f32)
+        self.dy2 = torch.empty(P, 64, **f32); self.dz1 = torch.empty(P, 32, **f32)
+        self.wt2 = torch.empty(32 * 9 * 64, **f32)
+        self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
+        self.off_bwd = (C.c_int * 9)(*[-((2 - r) * 26 + (2 - s)) for r in range(3) for s in range(3)])
+        self.seed = int(torch.initial_seed() if seed is None else seed) & 0xFFFFFFFFFFFFFFFF
+        if K.graph_step is None:
+            K.graph_step = torch.zeros((), dtype=torch.int64, device=dev)
+        self.training = True
+        self.comm_ctas = 16
+        self.launches_per_step = 0
+        self.graph = None
+        if use_graph:
+            self._capture()
+
+    # ---------------------------------------------------------------------------------------------
+    def _issue(self) -> None:
+        """Enqueue one full training step on the current stream (and the comm stream for the buckets)."""
+        L, s, net, N = K.lib(), K._stream, self.net, self.N
+        ck = K._chk
+        p = {n: t for n, t in net.named_parameters()}
+        g = {n: t.grad for n, t in p.items()}
+        step_ptr = K.graph_step.data_ptr()
+        tr = int(self.training)
+        ck(L.dcp_counter_advance(step_ptr, s()))
+        # ---- forward
+        ck(L.dcp_convnet_conv1_fwd(self.x.data_ptr(), p["conv1.weight"].data_ptr(), p["conv1.bias"].data_ptr(), self.a1.data_ptr(), N, s()))
+        ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
+                              self.off_fwd, 26, 676, 24, 24, 0, 148, s()))
+        ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
+        ks = tc._ksplit(N, 128, 9216, torch.float32)
+        if ks > 1:
+            self.h1.zero_()
+        tc.gemm(self.pooled, p["fc1.weight"], self.h1, p["fc1.bias"], N, 128, 9216, 9216, 9216, 128, 0, 0, False, ks)
+        bn = net.batchnorm
+        ck(L.dcp_bn_stats(self.h1.data_ptr(), self.bn_scratch.data_ptr(), N, 128, 0, s()))
+        ck(L.dcp_bn_apply(self.h1.data_ptr(), self.h2.data_ptr(), self.bn_scratch.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
+                          bn.running_mean.data_ptr(), bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), self.bn_mean.data_ptr(),
+                          self.bn_rstd.data_ptr(), N, 128, float(N), bn.eps, bn.momentum, 1, 1, 0, s()))
+        ck(L.dcp_dropout(self.h2.data_ptr(), self.h3.data_ptr(), N * 128, net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, 0, 1, 1, 0, s()))
+        ck(L.dcp_linear_fwd_simt(self.h3.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(), self.logits.data_ptr(), N, 10, 128, 0, 0, s()))
+        ck(L.dcp_ce_fwd(self.logits.data_ptr(), self.y.data_ptr(), self.loss.data_ptr(), self.lse.data_ptr(), N, 10, 1.0 / N, 0, s()))
+        # ---- backward: head
+        ck(L.dcp_ce_bwd(self.logits.data_ptr(), self.y.data_ptr(), self.lse.data_ptr(), self.one.data_ptr(), self.dlogits.data_ptr(), N, 10, 1.0 / N, 0, s()))
+        ck(L.dcp_linear_wgrad_simt(self.dlogits.data_ptr(), self.h3.data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), N, 10, 128, 0, s()))
+        ck(L.dcp_linear_dgrad_simt(self.dlogits.data_ptr(), p["fc2.weight"].data_ptr(), self.dh3.data_ptr(), N, 10, 128, 0, s()))
+        ck(L.dcp_dropout(self.dh3.data_ptr(), self.dh2.data_ptr(), N * 128, net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, 0, 1, 1, 0, s()))
+        ck(L.dcp_bn_bwd_reduce(self.h1.data_ptr(), self.h2.data_ptr(), self.dh2.data_ptr(), self.bn_mean.data_ptr(), self.bn_rstd.data_ptr(),
+                               self.bn_scratch.data_ptr(), N, 128, 1, 0, s()))
+        ck(L.dcp_bn_bwd_apply(self.h1.data_ptr(), self.h2.data_ptr(), self.dh2.data_ptr(), self.dh1.data_ptr(), self.bn_mean.data_ptr(),
+                              self.bn_rstd.data_ptr(), bn.weight.data_ptr(), self.bn_scratch.data_ptr(), g["batchnorm.weight"].data_ptr(),
+                              g["batchnorm.bias"].data_ptr(), N, 128, float(N), 1, 0, s()))
+        tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
+        ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
+        ev0 = self._reduce_bucket(0)
+        tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+        # ---- backward: convolutional trunk
+        ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
+                                  self.seed, 1, step_ptr, tr, s()))
+        ck(tc._lib.dcp_tc_conv_wgrad(self.dy2.data_ptr(), self.a1.data_ptr(), g["conv2.weight"].data_ptr(), N, 26, 26, 32, 64, 3, 3, 0, 26, 26,
+                                     8, 4, 1, 0, 148, s()))
+        ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
+        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
+        ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
+                              self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
+        g["conv1.weight"].zero_(); g["conv1.bias"].zero_()
+        ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
+        ev1 = self._reduce_bucket(1)
+        for ev in (ev0, ev1):
+            if ev is not None:
+                torch.cuda.current_stream(self.dev).wait_event(ev)
+        self.opt.step()
+
+    def _reduce_bucket(self, idx: int):
+        if self.be is None or idx >= len(self.buckets):
+            return None
+        return self.be.all_reduce_async(self.buckets[idx], ReduceOp.AVG, max_ctas=self.comm_ctas)
+
+    def _capture(self) -> None:
+        dev = self.dev
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):       # optimizer state, pointer tables, allocator warm-up
+                self._issue()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        before = K.launch_count + (self.be.launches if self.be else 0)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph):
+            self._issue()
+        self.launches_per_step = K.launch_count + (self.be.launches if self.be else 0) - before
+        torch.cuda.synchronize(dev)
+
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One optimisation step on batch (x, y); returns the (device, static) mean NLL loss of the batch."""
+        self.x.copy_(x.view(self.N, 1, 28, 28), non_blocking=True)
+        self.y.copy_(y, non_blocking=True)
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self._issue()
+        return self.loss
+
+    __call__ = step

@@ -201,7 +201,12 @@ class DistributedDataParallel(nn.Module):
             views = []
             for i, off in zip(idxs, offs):
                 p = self._params[i]
-                v = flat[off: off + p.numel()].view(p.shape)
+                # same physical layout as the parameter (e.g. channels-last conv weights): kernels write the
+                # gradient in that order and the fused optimizer walks param / grad / state with one index
+                if p.is_contiguous():
+                    v = flat[off: off + p.numel()].view(p.shape)
+                else:
+                    v = flat[off: off + p.numel()].as_strided(p.shape, p.stride())
                 views.append(v)
                 self._bucket_of[i] = bi
                 self._view_of[i] = v

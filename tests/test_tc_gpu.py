@@ -81,3 +81,13 @@ def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
         xr = x.double().requires_grad_(True)
         F.conv2d(xr, w.double(), None, 1, pad).backward(dy.double())
         assert _rel_err(dx, xr.grad) < tol, _rel_err(dx, xr.grad)
+    if tc.conv_wgrad_supported(p, dtype):
+        dy = torch.randn_like(y)
+        dw32 = torch.empty_like(w, dtype=torch.float32)
+        db32 = torch.empty(K, dtype=torch.float32, device=DEV)
+        tc.conv2d_wgrad(dy, x, dw32, db32, p)
+        wr = w.double().requires_grad_(True)
+        br = b.double().requires_grad_(True)
+        F.conv2d(x.double(), wr, br, 1, pad).backward(dy.double())
+        assert _rel_err(dw32, wr.grad) < tol, _rel_err(dw32, wr.grad)
+        assert _rel_err(db32, br.grad) < tol
