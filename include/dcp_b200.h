@@ -1,0 +1,214 @@
+// Public C ABI of the native libraries (libdcp_host.so: host plumbing, g++; libdcp_cuda.so: sm_100a kernels, nvcc).
+// Everything is plain extern "C": Python binds it with ctypes (_native.py, _cuda_sigs.py, ops/cuda.py, ops/tc.py) and
+// C/C++ hosts can link it directly.  Device pointers are raw addresses; `stream` arguments are cudaStream_t.
+// All int-returning entry points return 0 on success and -1 on failure (message via dcp_last_error()).
+// GENERATED from the sources by tools/gen_header.py - the comments are the ones next to each definition.
+#pragma once
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __CUDACC__
+#include <cuda_runtime.h>
+#else
+typedef struct CUstream_st* cudaStream_t;
+#endif
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+struct DcpDevCtx;                   /* csrc/common.cuh */
+typedef struct ConvP { int N, H, W, C, K, R, S, stride, pad, Ho, Wo; } ConvP;
+
+/* ---- csrc/coll/coll.cu ---- */
+size_t dcp_coll_oneshot_max_bytes(void* h);
+size_t dcp_coll_bounce_max_bytes(void* h);
+// algo: 1 one-shot, 2 two-shot P2P, 3 NVLS.  In-place on `buf` (n elements).  If `buf` lies inside the
+// symmetric heap the peers read it directly; otherwise it is bounced through the staging area.
+int dcp_all_reduce(void* h, void* buf, size_t n, int dtype, int op, int algo, int chan, int max_ctas, cudaStream_t stream);
+int dcp_broadcast(void* h, void* buf, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
+// out: [W][nbytes] contiguous.  root < 0: all_gather; root >= 0: gather to root (out may be null elsewhere).
+int dcp_all_gather(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
+// in: [W][nbytes] contiguous on root.
+int dcp_scatter(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
+// root < 0: reduce_scatter (in: W*n_out elements, out: n_out).  root >= 0: reduce (in: n_out elements, out on root).
+int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dtype, int op, int root, int chan, int max_ctas, cudaStream_t stream);
+int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t stream);
+int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream);
+int dcp_barrier_launch(void* h, int chan, cudaStream_t stream);
+
+/* ---- csrc/ddp/reducer.cpp ---- */
+// Plan buckets.  `nbytes[i]` / `group_key[i]` describe tensor i in the order given (dtype+device folded
+// into group_key by the caller).  `limits` is the per-group sequence of size limits; the last entry
+// repeats.  A bucket is closed once its size reaches the current limit.  Buckets are numbered by
+// the position of their first tensor.  Returns the number of buckets; out_bucket_of[i] = bucket of i.
+int dcp_bucket_assign(const int64_t* nbytes, const int32_t* group_key, int n, const int64_t* limits, int nlimits, int32_t* out_bucket_of);
+void* dcp_reducer_create(const int32_t* bucket_of, int n, int nbuckets);
+void dcp_reducer_destroy(void* h);
+// Start a new backward pass.
+void dcp_reducer_reset(void* h);
+// Gradient of parameter `idx` has landed.  Returns how many buckets became launchable (in order)
+// and writes the first of them to *first; -1 if idx was already marked this iteration.
+int dcp_reducer_mark_ready(void* h, int idx, int* first);
+// Number of buckets not yet launched this iteration.
+int dcp_reducer_unlaunched(void* h);
+int dcp_reducer_ready_order(void* h, int32_t* out, int cap);
+
+/* ---- csrc/host/mesh.cpp ---- */
+// Every rank listens on an ephemeral port and publishes "<prefix>/addr/<rank>" = "host:port".
+// Rank i dials every j < i and accepts from every j > i; the dialler announces its rank.
+void* dcp_mesh_create(void* store, int rank, int world, const char* my_host, const char* prefix, double timeout_s);
+void dcp_mesh_destroy(void* h);
+int dcp_mesh_send(void* h, int dst, const void* p, int64_t n, int tag);
+int dcp_mesh_recv(void* h, int src, void* p, int64_t n, int tag);
+// Full-duplex exchange: progress the send to `dst` and the receive from `src` together so that a
+// ring of ranks that all send first cannot deadlock on full socket buffers.
+int dcp_mesh_sendrecv(void* h, int dst, const void* sp, int64_t sn, int src, void* rp, int64_t rn, int tag);
+int dcp_fd_listen(const char* name);
+// Connect to `name` and send `nfds` descriptors tagged with the sender's rank.
+int dcp_fd_send(const char* name, int my_rank, const int* fds, int nfds, double timeout_s);
+// Accept one connection on `lfd`, receive its descriptors.  Returns the sender's rank (>=0) or <0.
+int dcp_fd_recv(int lfd, int* out_fds, int max_fds, int* out_nfds, double timeout_s);
+void dcp_fd_close(int fd);
+
+/* ---- csrc/host/store.cpp ---- */
+void* dcp_store_server_start(const char* host, int port, int* out_port);
+void dcp_store_server_stop(void* h);
+void* dcp_store_client_connect(const char* host, int port, double timeout_s);
+void dcp_store_client_close(void* h);
+int64_t dcp_store_set(void* h, const char* key, const void* val, int64_t len);
+// Blocks until `key` exists or the timeout expires (-3).  The value stays inside the client until the
+// next call; fetch it with dcp_store_copy_last.
+int64_t dcp_store_get(void* h, const char* key, double timeout_s);
+int64_t dcp_store_copy_last(void* h, void* buf, int64_t cap);
+int64_t dcp_store_add(void* h, const char* key, int64_t delta);
+int64_t dcp_store_check(void* h, const char* key);
+int64_t dcp_store_delete(void* h, const char* key);
+int64_t dcp_store_num_keys(void* h);
+
+/* ---- csrc/ops/batchnorm.cu ---- */
+// scratch: >= 4*C doubles.  Phase 1 of forward: zero + accumulate (sum, sumsq).
+int dcp_bn_stats(const void* x, void* scratch, long M, int C, int dtype, cudaStream_t s);
+// Phase 2 of forward.  training=0: uses running stats, scratch may be null.
+int dcp_bn_apply(const void* x, void* y, const void* scratch, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, float* save_mean, float* save_rstd, long M, int C, double count, float eps, float momentum, int relu, int training, int dtype, cudaStream_t s);
+// Backward phase 1: zero + accumulate (sum dy', sum dy'*xhat) into scratch[0..2C) and keep a local copy in [2C..4C).
+int dcp_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, void* scratch, long M, int C, int relu, int dtype, cudaStream_t s);
+// Backward phase 2.  count: rows behind scratch[0..2C) (global for SyncBN).
+int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, const float* mean, const float* rstd, const float* gamma, const void* scratch, float* dgamma, float* dbeta, long M, int C, double count, int relu, int dtype, cudaStream_t s);
+
+/* ---- csrc/ops/conv_flat_tc.cu ---- */
+// in: [P, Cin] fp32 flat pixels (pitch W, HW pixels per image); wmat: [Cout][taps*Cin] fp32 (tap-major columns);
+// off[t]: flat row shift of tap t.  mode 0: out = (h < Hv && w < Wv) ? relu(acc + bias) : 0;  mode 1: out = mask > 0 ? acc : 0.
+int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps, const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, cudaStream_t s);
+
+/* ---- csrc/ops/conv_linear_simt.cu ---- */
+int dcp_conv2d_fwd_simt(const void* x, const void* w, const void* bias, void* y, ConvP p, int relu, int dtype, cudaStream_t s);
+int dcp_conv2d_dgrad_simt(const void* dy, const void* w, void* dx, ConvP p, int dtype, cudaStream_t s);
+// dw32: float [K, R*S*C] accumulator (zeroed here).  db32: float [K] or null.
+int dcp_conv2d_wgrad_simt(const void* dy, const void* x, float* dw32, float* db32, ConvP p, int dtype, cudaStream_t s);
+// y[M,N] = x[M,K] . w[N,K]^T + b
+int dcp_linear_fwd_simt(const void* x, const void* w, const void* bias, void* y, int M, int N, int K, int relu, int dtype, cudaStream_t s);
+// dx[M,K] = dy[M,N] . w[N,K]
+int dcp_linear_dgrad_simt(const void* dy, const void* w, void* dx, int M, int N, int K, int dtype, cudaStream_t s);
+// dw32[N,K] = dy[M,N]^T . x[M,K] (float accumulator, zeroed here); db32[N] = column sums of dy
+int dcp_linear_wgrad_simt(const void* dy, const void* x, float* dw32, float* db32, int M, int N, int K, int dtype, cudaStream_t s);
+// float column sums of [M, C] (+= into zeroed out)
+int dcp_colsum(const void* x, float* out, long M, int C, int dtype, cudaStream_t s);
+int dcp_cast_from_f32(const float* in, void* out, long n, int dtype, cudaStream_t s);
+
+/* ---- csrc/ops/convnet_fused.cu ---- */
+int dcp_convnet_conv1_fwd(const float* x, const float* w, const float* b, float* a1, int N, cudaStream_t s);
+int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
+int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* arg, float* dy2, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
+// dw1 / db1 are accumulated into: the caller zeroes them (they normally live in the gradient bucket).
+int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s);
+
+/* ---- csrc/ops/elementwise.cu ---- */
+int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
+int dcp_relu_bwd(const void* y, const void* dy, void* dx, long n, int dtype, cudaStream_t s);
+int dcp_add_relu_fwd(const void* a, const void* b, void* y, long n, int dtype, cudaStream_t s);
+int dcp_dropout(const void* x, void* y, long n, float p, unsigned long long seed, unsigned long long stream_id, const void* step, int mode, long inner, long hw, int dtype, cudaStream_t s);
+int dcp_maxpool_fwd(const void* x, void* y, void* arg, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s);
+int dcp_maxpool_bwd(const void* dy, const void* arg, void* dx, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s);
+int dcp_gap_fwd(const void* x, void* y, int N, int HW, int C, int dtype, cudaStream_t s);
+int dcp_gap_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, cudaStream_t s);
+int dcp_correct_count(const void* x, const void* target, void* count, int M, int C, int dtype, cudaStream_t s);
+
+/* ---- csrc/ops/gemm_tc.cu ---- */
+// C[M,N] (+)= op(A) . op(B)^T with fp32 accumulation on tcgen05.
+//   a_mn = 0: A is [M][K] row-major (lda);   a_mn = 1: A is [K][M] row-major (lda)
+//   b_mn = 0: B is [N][K] row-major (ldb);   b_mn = 1: B is [K][N] row-major (ldb)
+// dtype: DCP_F32 (tf32 multiply) or DCP_BF16.  out: fp32 or bf16 (out_bf16), ldc elements.  ksplit > 1 => `out`
+// must be fp32 and zero-initialised (atomic accumulation; relu is rejected).  K must be a multiple of the 128-byte slab.
+int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s);
+// Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
+//   x: channels-last [N,H,W,C]; wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] (fp32 or bf16).
+// C must be a multiple of the 128-byte slab (32 f32 / 64 bf16).  (Wb,Hb,Nb): box of output pixels per CTA, product 128.
+int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
+// Convolution weight gradient (stride 1) on tcgen05: dw[k][r][s][c] += sum_pixels dy[n,ho,wo,k] * x[n, ho-pad+r, wo-pad+s, c].
+// Both operands are read MN-major straight from the channels-last tensors (no im2col, no transposes): the K
+// dimension of the MMA runs over boxes of (Wb x Hb x Nb) = 32 (f32) / 64 (bf16) output pixels, the A operand of
+// accumulator group g is made of 128-byte channel chunks taken from the activation shifted by different filter
+// taps, B is the matching box of dy.  gridDim.z splits the pixel boxes; partial sums meet in fp32 atomics, so
+// dw32 ([Kout][R*S*C] fp32) is zeroed here.
+int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
+int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s);
+
+/* ---- csrc/ops/loss.cu ---- */
+int dcp_log_softmax_fwd(const void* x, void* y, int M, int C, int dtype, cudaStream_t s);
+int dcp_log_softmax_bwd(const void* y, const void* dy, void* dx, int M, int C, int dtype, cudaStream_t s);
+int dcp_nll_fwd(const void* logp, const void* target, float* loss, int M, int C, float scale, int dtype, cudaStream_t s);
+int dcp_nll_bwd(const void* target, const float* gout, void* dlogp, int M, int C, float scale, int dtype, cudaStream_t s);
+int dcp_ce_fwd(const void* x, const void* target, float* loss, float* lse, int M, int C, float scale, int dtype, cudaStream_t s);
+int dcp_ce_bwd(const void* x, const void* target, const float* lse, const float* gout, void* dx, int M, int C, float scale, int dtype, cudaStream_t s);
+
+/* ---- csrc/ops/optim.cu ---- */
+// Advance the device step counter (call once per optimizer.step(), before dcp_optim_step).
+int dcp_optim_advance(float* hp, cudaStream_t s);
+// kind: 0 Adadelta, 1 SGD, 2 Adam.  grad_dtype: DCP_F32 or DCP_BF16.  max_numel sizes the grid.
+int dcp_optim_step(const void* table, int ntensors, long long max_numel, const float* hp, int kind, int grad_dtype, cudaStream_t s);
+int dcp_counter_advance(void* counter, cudaStream_t s);
+
+/* ---- csrc/symm/symm.cu ---- */
+const char* dcp_last_error();
+void dcp_set_error(const char* fmt, ...);
+// Whether device `device` supports multicast objects (NVLS).
+int dcp_symm_multicast_supported(int device);
+// Create this rank's heap.  mode: 0 = vmm (POSIX FD), 1 = ipc (cudaMalloc).  Returns handle or null.
+void* dcp_symm_create(int rank, int world, int device, size_t bytes, int mode);
+size_t dcp_symm_bytes(void* h);
+void* dcp_symm_local_ptr(void* h);
+void* dcp_symm_peer_ptr(void* h, int r);
+void* dcp_symm_mc_ptr(void* h);
+// vmm: export own heap as a POSIX FD (caller sends it to peers and closes it).
+int dcp_symm_export_fd(void* h);
+// vmm: map peer `r`'s heap from the FD it sent.
+int dcp_symm_import_fd(void* h, int r, int fd);
+// ipc: 64-byte handle of own heap / open a peer's.
+int dcp_symm_ipc_handle(void* h, void* out64);
+int dcp_symm_ipc_open(void* h, int r, const void* in64);
+// NVLS step 1 (rank 0): create the multicast object, returns an FD to distribute (or -1).
+int dcp_symm_mc_create(void* h);
+// NVLS step 1' (other ranks): import the multicast object.
+int dcp_symm_mc_import(void* h, int fd);
+// NVLS step 2 (all ranks): add this device.  Every rank must finish this before anyone binds.
+int dcp_symm_mc_add_device(void* h);
+// NVLS step 3 (all ranks): bind own heap and map the multicast VA.
+int dcp_symm_mc_bind(void* h);
+// Freeze the device context after all peers are mapped.
+int dcp_symm_finalize(void* h, double timeout_s, size_t p2p_slot_bytes, size_t staging_bytes, int allow_nvls);
+size_t dcp_symm_user_offset(void* h);
+size_t dcp_symm_staging_offset(void* h);
+size_t dcp_symm_staging_bytes(void* h);
+int dcp_symm_has_nvls(void* h);
+const struct DcpDevCtx* dcp_symm_ctx(void* h);
+// Non-zero once any kernel's bounded wait expired (a peer died or the ranks diverged).
+int dcp_symm_error_flag(void* h);
+void dcp_symm_clear_error(void* h);
+void dcp_symm_destroy(void* h);
+
+/* ---- hand-maintained additions ---- */
+
+#ifdef __cplusplus
+}  /* extern "C" */
+#endif
