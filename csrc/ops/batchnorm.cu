@@ -193,3 +193,88 @@ int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, con
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// Allocation-free BatchNorm forward (training statistics + normalise), for hosts that cannot give us scratch.
+//
+// Who needs this: dcp_bn_stats / dcp_bn_apply expect the caller to hand in a scratch accumulator (4*C doubles),
+// which our Python layer takes from torch's caching allocator.  Some callers have no allocator to ask:
+//   * a C/C++ program that links libdcp_cuda.so without PyTorch, so there is no caching allocator behind it;
+//   * a process that gave the whole GPU to its own arena at start-up, where a cudaMalloc would fail - and where
+//     cudaMalloc / cudaFree would in any case stall the device, which a latency-bound serving or control loop
+//     cannot afford in the middle of a step.
+// For them the accumulator lives in the library image itself: a file-scope __device__ array of fixed size,
+// created once per GPU when the module is loaded there and kept until the process exits
+// (DCP_BN_NOALLOC_MAX_C channels -> 2 * 2048 * 8 B = 32 KiB per GPU).
+//
+// Rules that follow from sharing one array:
+//   * C above DCP_BN_NOALLOC_MAX_C is refused (-1, message in dcp_last_error()); nothing is launched.
+//   * The array keeps whatever the previous call left in it, so every call first zeroes the 2*C doubles it uses
+//     (stream-ordered memset on the caller's stream) before the statistics kernel adds into them.
+//   * Two calls that can overlap on the GPU (different streams, or different host threads on different streams)
+//     race on the array and corrupt each other's statistics.  Issue them on one stream, or order them with events.
+//   * The first call on each device looks up the array's device address (cudaGetSymbolAddress with that device
+//     current) and caches it; make that first call before starting any stream capture on that device.
+//   * The call itself performs no cudaMalloc / cudaFree and no allocating library call.
+// =====================================================================================================
+#include <mutex>
+
+#define DCP_BN_NOALLOC_MAX_C 2048
+#define DCP_BN_NOALLOC_MAX_DEVICES 64
+
+// In host code this name is only a handle for the runtime (not a device address): never pass it to a kernel.
+static __device__ __align__(256) double g_bn_noalloc_scratch[2 * DCP_BN_NOALLOC_MAX_C];
+
+namespace {
+double* g_bn_noalloc_ptr[DCP_BN_NOALLOC_MAX_DEVICES] = {};
+std::mutex g_bn_noalloc_mu;
+
+// Device address of the scratch array on the current device (resolved once per device).
+int bn_noalloc_scratch(double** out) {
+  int dev = -1;
+  DCP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= DCP_BN_NOALLOC_MAX_DEVICES) { dcp_set_error("bn no-alloc: device index %d out of range", dev); return -1; }
+  std::lock_guard<std::mutex> lock(g_bn_noalloc_mu);
+  if (g_bn_noalloc_ptr[dev] == nullptr) {
+    double* p = nullptr;
+    DCP_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_bn_noalloc_scratch));
+    if (p == nullptr) { dcp_set_error("bn no-alloc: cudaGetSymbolAddress returned a null address"); return -1; }
+    g_bn_noalloc_ptr[dev] = p;
+  }
+  *out = g_bn_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// Training-mode BatchNorm(+ReLU) forward over x[M, C] (row-major, C innermost) without any caller-provided or
+// library-allocated scratch: y = relu?((x - mean) * rstd * gamma + beta); saves mean / rstd for backward and
+// updates running_mean / running_var / num_batches_tracked exactly like dcp_bn_stats + dcp_bn_apply do.
+// gamma, beta, run_mean, run_var, nbt may be null.  C <= DCP_BN_NOALLOC_MAX_C.  See the block comment above for the
+// sharing rules (one call at a time per GPU; first call per device before any stream capture).
+// (declared by hand in include/dcp_b200.h - gen_header: skip)
+int dcp_bn_forward_noalloc(const void* x, void* y, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
+                           float* save_mean, float* save_rstd, long M, int C, float eps, float momentum, int relu, int dtype, cudaStream_t s) {
+  if (C <= 0 || M <= 0) { dcp_set_error("bn no-alloc: empty input (M=%ld, C=%d)", M, C); return -1; }
+  if (C > DCP_BN_NOALLOC_MAX_C) {
+    dcp_set_error("bn no-alloc: C=%d exceeds the built-in scratch (DCP_BN_NOALLOC_MAX_C=%d); use dcp_bn_stats/dcp_bn_apply with your own scratch",
+                  C, DCP_BN_NOALLOC_MAX_C);
+    return -1;
+  }
+  double* scratch = nullptr;
+  if (bn_noalloc_scratch(&scratch) != 0) return -1;
+  // the array still holds the previous call's sums: clear the part this call accumulates into
+  DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * (size_t)C, s));
+  dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);
+  DISPATCH_ACT(dtype, (k_bn_stats<T><<<grid, kRows * kCols, 0, s>>>((const T*)x, scratch, M, C, rpc)));
+  DCP_CUDA_CHECK(cudaGetLastError());
+  const int agrid = grid_1d(M * C, 256, 148 * 8);
+  const size_t smem = sizeof(float) * 2 * C;
+  DISPATCH_ACT(dtype, (k_bn_apply<T><<<agrid, 256, smem, s>>>((const T*)x, (T*)y, scratch, gamma, beta, run_mean, run_var, (long long*)nbt,
+                                                              save_mean, save_rstd, M, C, (double)M, eps, momentum, relu, 1)));
+  DCP_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

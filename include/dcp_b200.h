@@ -209,6 +209,19 @@ void dcp_symm_destroy(void* h);
 
 /* ---- hand-maintained additions ---- */
 
+/* Allocation-free BatchNorm forward.  This entry point has no counterpart in the reference (which never touches
+ * device memory management; ref:main.py only calls nn.BatchNorm1d): it exists for hosts of THIS library that cannot
+ * provide scratch memory - a C/C++ program linking libdcp_cuda.so without PyTorch's caching allocator, or a process
+ * whose own arena already owns the whole GPU so that cudaMalloc would fail (and would stall the device anyway).
+ * The per-channel accumulators live in a 32 KiB __device__ array inside the library (one copy per GPU, kept until
+ * exit), so: C <= DCP_BN_NOALLOC_MAX_C (2048) or the call is refused; the array is shared by every call and
+ * cleared at the start of each, hence calls that may overlap on the GPU race - keep them on one stream; the first
+ * call on a device resolves the array's address (cudaGetSymbolAddress) and should come before any stream capture.
+ * Same results as dcp_bn_stats + dcp_bn_apply(training=1). */
+#define DCP_BN_NOALLOC_MAX_C 2048
+int dcp_bn_forward_noalloc(const void* x, void* y, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
+                           float* save_mean, float* save_rstd, long M, int C, float eps, float momentum, int relu, int dtype, cudaStream_t s);
+
 #ifdef __cplusplus
 }  /* extern "C" */
 #endif
