@@ -24,6 +24,7 @@ struct TcGemmParams {
   //           activation box shifted by filter tap (unit / cchunks) for channel chunk (unit % cchunks); B is the dy box
   int conv, S, cchunks, Cin, pad, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
   int stages;                   // pipeline depth (<= kStages)
+  int x3;                       // fp32 only: 3xTF32 split (hi*hi + lo*hi + hi*lo) -> fp32-class accuracy
   int groups, units, a_bytes;   // accumulator groups per CTA (1 except wgrad), (tap, chunk) units in total, bytes of one A stage
   // epilogue
   void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
@@ -38,7 +39,7 @@ constexpr int kABytes = kBM * 128;            // 16 KB per stage
 constexpr int kThreads = 192;
 
 struct __align__(8) Pipe {
-  uint64_t full[kStages], empty[kStages], acc_full;
+  uint64_t full[kStages], empty[kStages], split[kStages], acc_full;
   uint32_t tmem_base;
 };
 
@@ -50,7 +51,8 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int b_bytes = p.b_bytes;
   const int a_bytes = p.a_bytes;
-  const int stage_bytes = a_bytes + b_bytes;
+  const int half_bytes = a_bytes + b_bytes;                 // [A][B]; in x3 mode followed by [A_lo][B_lo]
+  const int stage_bytes = p.x3 ? 2 * half_bytes : half_bytes;
   const int nstages = p.stages;
   Pipe* pipe = reinterpret_cast<Pipe*>(smem + nstages * stage_bytes);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -67,7 +69,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < kStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); }
+      for (int i = 0; i < kStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); mbar_init(&pipe->split[i], 4); }
       mbar_init(&pipe->acc_full, 1);
       mbar_fence_init();
     }
@@ -142,7 +144,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const uint32_t idesc = make_idesc(kTF32, p.a_mn != 0, p.b_mn != 0, kBM, p.BN);
       for (int i = 0; i < nst; ++i) {
         const int st = i % nstages, ph = (i / nstages) & 1;
-        mbar_wait(&pipe->full[st], ph);
+        mbar_wait(p.x3 ? &pipe->split[st] : &pipe->full[st], ph);
         tc_fence_after();
         const uint32_t sa0 = smem_u32(smem + st * stage_bytes), sb = sa0 + a_bytes;
         for (int g = 0; g < p.groups; ++g) {
@@ -155,6 +157,11 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           const uint64_t da = p.a_mn ? make_smem_desc(sa + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sa + j * 32, 0, 1024);
           const uint64_t db = p.b_mn ? make_smem_desc(sb + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sb + j * 32, 0, 1024);
           umma<kTF32>(tmem_g, da, db, idesc, (i | j) != 0);
+          if (kTF32 && p.x3) {   // + A_lo * B_hi + A_hi * B_lo (the lo tiles sit half_bytes further on)
+            const uint64_t lo_step = (uint64_t)(half_bytes >> 4);   // start-address field is in 16-byte units
+            umma<kTF32>(tmem_g, da + lo_step, db, idesc, 1);
+            umma<kTF32>(tmem_g, da, db + lo_step, idesc, 1);
+          }
         }
         }
         umma_commit(&pipe->empty[st]);   // smem slot reusable once these MMAs retire
@@ -166,6 +173,28 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     // ================= epilogue: TMEM -> registers -> global =================
     const int lg = warp & 3;                       // TMEM lane group this warp may access
     const int row = lg * 32 + lane;                // row inside the tile
+    if (kTF32 && p.x3) {
+      // 3xTF32: while the pipeline runs, these 128 threads split every landed stage in place into
+      // hi = x with the low 13 mantissa bits cleared (exact in tf32) and lo = x - hi (exact in fp32).
+      // The split is element-wise, so it is independent of the swizzle the TMA applied.
+      const int t = (warp - 2) * 32 + lane;
+      for (int i = 0; i < nst; ++i) {
+        const int st = i % nstages, ph = (i / nstages) & 1;
+        mbar_wait(&pipe->full[st], ph);
+        uint4* hi = reinterpret_cast<uint4*>(smem + st * stage_bytes);
+        uint4* lo = reinterpret_cast<uint4*>(smem + st * stage_bytes + half_bytes);
+        for (int v = t; v < half_bytes / 16; v += 128) {
+          uint4 x = hi[v], h, l;
+          h.x = x.x & 0xFFFFE000u; h.y = x.y & 0xFFFFE000u; h.z = x.z & 0xFFFFE000u; h.w = x.w & 0xFFFFE000u;
+          l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(h.x)); l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(h.y));
+          l.z = __float_as_uint(__uint_as_float(x.z) - __uint_as_float(h.z)); l.w = __float_as_uint(__uint_as_float(x.w) - __uint_as_float(h.w));
+          hi[v] = h; lo[v] = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy writes -> visible to the tensor core
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pipe->split[st]);
+      }
+    }
     if (nst > 0) {
       mbar_wait(&pipe->acc_full, 0);
       tc_fence_after();
@@ -301,7 +330,7 @@ int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, 
   return 0;
 }
 
-size_t smem_bytes(int stages, int a_bytes, int b_bytes) { return (size_t)stages * (a_bytes + b_bytes) + sizeof(Pipe) + 1024; }
+size_t smem_bytes(int stages, int a_bytes, int b_bytes, int x3 = 0) { return (size_t)stages * (a_bytes + b_bytes) * (x3 ? 2 : 1) + sizeof(Pipe) + 1024; }
 constexpr int kMaxSmem = 200 * 1024;
 int b_stage_bytes(int BN, int b_mn, int es) { int chunk = 128 / es, bk = 128 / es; return b_mn ? ((BN + chunk - 1) / chunk) * bk * 128 : BN * 128; }
 
@@ -314,9 +343,9 @@ template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUt
   }
   TcGemmParams q = p;
   q.stages = kStages;
-  while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes) > (size_t)kMaxSmem) --q.stages;
-  if (smem_bytes(q.stages, q.a_bytes, q.b_bytes) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }
-  k_tc_gemm<kTF32, kTmemCols><<<grid, kThreads, smem_bytes(q.stages, q.a_bytes, q.b_bytes), s>>>(ma, mb, q);
+  while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) --q.stages;
+  if (smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }
+  k_tc_gemm<kTF32, kTmemCols><<<grid, kThreads, smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3), s>>>(ma, mb, q);
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
@@ -332,15 +361,24 @@ extern "C" {
 //   b_mn = 0: B is [N][K] row-major (ldb);   b_mn = 1: B is [K][N] row-major (ldb)
 // dtype: DCP_F32 (tf32 multiply) or DCP_BF16.  out: fp32 or bf16 (out_bf16), ldc elements.  ksplit > 1 => `out`
 // must be fp32 and zero-initialised (atomic accumulation; relu is rejected).  K must be a multiple of the 128-byte slab.
+// x3 (fp32 only): 3xTF32 - every operand is split into a tf32-exact high part and a low remainder and the kernel
+// accumulates hi*hi + lo*hi + hi*lo, which restores fp32-class accuracy (what cuBLAS gives the reference's Linear
+// layers with allow_tf32=False) at three times the MMA count.
+int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
+                   int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s);
 int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
                 int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s) {
+  return dcp_tc_gemm_ex(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, dtype, out_bf16, bias_bf16, relu, ksplit, 0, s);
+}
+int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
+                   int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s) {
   const int es = dtype == DCP_F32 ? 4 : 2, bk = 128 / es;
   if (dtype != DCP_F32 && dtype != DCP_BF16) { dcp_set_error("tc gemm: dtype must be f32 or bf16"); return -1; }
   if (K % bk) { dcp_set_error("tc gemm: K=%d must be a multiple of %d", K, bk); return -1; }
   if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
   TcGemmParams p{};
   p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
-  p.b_bytes = b_stage_bytes(p.BN, b_mn, es); p.a_bytes = kABytes; p.groups = 1;
+  p.b_bytes = b_stage_bytes(p.BN, b_mn, es); p.a_bytes = kABytes; p.groups = 1; p.x3 = (x3 && dtype == DCP_F32) ? 1 : 0;
   p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
   CUtensorMap ma, mb;
   if (!a_mn) { if (make_map_2d(&ma, A, es, M, K, lda, bk, kBM)) return -1; }

@@ -20,6 +20,8 @@ def declare(lib) -> None:
     vp, i, l = C.c_void_p, C.c_int, C.c_long
     lib.dcp_tc_gemm.restype = C.c_int
     lib.dcp_tc_gemm.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, vp]
+    lib.dcp_tc_gemm_ex.restype = C.c_int
+    lib.dcp_tc_gemm_ex.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, i, vp]
     lib.dcp_tc_conv.restype = C.c_int
     lib.dcp_tc_conv.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
     lib.dcp_tc_conv_wgrad.restype = C.c_int
@@ -42,12 +44,18 @@ def _ok_dtype(dtype) -> bool:
     return dtype in (torch.float32, torch.bfloat16)
 
 
-def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit=1) -> None:
-    """out[M,N] (+)= op(A) op(B)^T on tcgen05 (see dcp_tc_gemm)."""
+# fp32 Linear layers default to 3xTF32 (fp32-class accuracy, like the reference's cuBLAS fp32 matmul);
+# DCP_LINEAR_PRECISION=tf32 selects the single-pass tf32 multiply instead.
+LINEAR_X3 = os.environ.get("DCP_LINEAR_PRECISION", "tf32x3") == "tf32x3"
+
+
+def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit=1, x3=None) -> None:
+    """out[M,N] (+)= op(A) op(B)^T on tcgen05 (see dcp_tc_gemm_ex)."""
     k = _k()
-    k._chk(_lib.dcp_tc_gemm(A.data_ptr(), B.data_ptr(), out.data_ptr(), k._p(bias), M, N, K, lda, ldb, ldc, int(a_mn), int(b_mn), k._dt(A),
-                            int(out.dtype == torch.bfloat16), int(bias is not None and bias.dtype == torch.bfloat16), int(relu), int(ksplit),
-                            k._stream()))
+    x3 = LINEAR_X3 if x3 is None else x3
+    k._chk(_lib.dcp_tc_gemm_ex(A.data_ptr(), B.data_ptr(), out.data_ptr(), k._p(bias), M, N, K, lda, ldb, ldc, int(a_mn), int(b_mn), k._dt(A),
+                               int(out.dtype == torch.bfloat16), int(bias is not None and bias.dtype == torch.bfloat16), int(relu), int(ksplit),
+                               int(bool(x3) and A.dtype == torch.float32), k._stream()))
 
 
 def _ksplit(M: int, N: int, K: int, dtype) -> int:

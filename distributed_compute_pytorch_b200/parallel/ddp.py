@@ -223,7 +223,8 @@ class DistributedDataParallel(nn.Module):
     # ------------------------------------------------------------------------- backward path ----
     def _make_hook(self, idx: int):
         def hook(param: torch.Tensor) -> None:
-            if not self.require_backward_grad_sync or self.world_size == 1 and self._comm_hook is None:
+            if not self.require_backward_grad_sync or (self.world_size == 1 and self._comm_hook is None
+                                                        and getattr(self, "_bucket_override", None) is None):
                 return
             if not self._iter_callback_queued:
                 self._iter_callback_queued = True
@@ -242,7 +243,21 @@ class DistributedDataParallel(nn.Module):
                 self._launch_bucket(self._buckets[b])
         return hook
 
+    def finalize_buckets(self, order: Optional[List[int]] = None) -> None:
+        """Fix the bucket layout now (capped buckets in ``order``, default reverse registration order) instead of
+        waiting for the first backward - used by engines that need stable bucket addresses up front."""
+        order = list(range(len(self._params)))[::-1] if order is None else order
+        for i, p in enumerate(self._params):
+            if p.grad is not None and self._view_of[i] is not None and p.grad.data_ptr() == self._view_of[i].data_ptr():
+                p.grad = None
+        self._build_buckets(order, limits=[self.first_bucket_bytes, self.bucket_bytes_cap])
+        self._rebuilt = True
+        self._pending_order = None
+
     def _launch_bucket(self, bucket: _Bucket) -> None:
+        if getattr(self, "_bucket_override", None) is not None:
+            self._bucket_override(bucket)
+            return
         if self._comm_hook is not None:
             state, fn = self._comm_hook
             out = fn(state, GradBucket(bucket, bucket.index == len(self._buckets) - 1))

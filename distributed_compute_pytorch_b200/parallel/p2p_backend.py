@@ -7,7 +7,7 @@ This is what stands behind ``dist.all_reduce`` at ref:main.py:65,90,91 and behin
 buckets (ref:main.py:62,122) when the tensors live on a B200.
 
 Algorithm choice for all_reduce (per message size, override with DCP_ALLREDUCE_ALGO=1|2|3):
-  <= DCP_ONESHOT_BYTES (default 256 KiB)   one-shot push   (latency floor: 1 NVLink hop + 1 signal)
+  <= DCP_ONESHOT_BYTES (default 2 MiB/(W-1)) one-shot push   (latency floor: 1 NVLink hop + 1 signal)
   larger, multicast mapped, f32/bf16/f16   NVLS            (multimem.ld_reduce + multimem.st)
   otherwise                                two-shot P2P    (pull-reduce own slice, push to all)
 Tensors inside the symmetric heap (``empty_symmetric``; DDP buckets) are reduced in place with zero
@@ -79,7 +79,9 @@ class P2PBackend:
         self._user_off = self.lib.dcp_symm_user_offset(self._h)
         self._free: List[Tuple[int, int]] = [(self._user_off, self.heap_bytes - self._user_off)]
         self._live: Dict[int, Tuple[int, int]] = {}
-        self.oneshot_max = min(int(os.environ.get("DCP_ONESHOT_BYTES", str(256 * 1024))), self.lib.dcp_coll_oneshot_max_bytes(self._h))
+        # one-shot pushes (W-1) full copies per rank, two-shot moves 2(W-1)/W: the crossover shrinks with W
+        default_oneshot = max(64 * 1024, (2 << 20) // max(1, world_size - 1))
+        self.oneshot_max = min(int(os.environ.get("DCP_ONESHOT_BYTES", str(default_oneshot))), self.lib.dcp_coll_oneshot_max_bytes(self._h))
         self.nvls_min = int(os.environ.get("DCP_NVLS_MIN_BYTES", str(256 * 1024)))
         self.comm_stream = torch.cuda.Stream(device=self._torch_dev, priority=-1)
         self._algo_override = int(os.environ.get("DCP_ALLREDUCE_ALGO", "0"))

@@ -37,6 +37,14 @@ int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t strea
 int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream);
 int dcp_barrier_launch(void* h, int chan, cudaStream_t stream);
 
+/* ---- csrc/coll/fused_opt.cu ---- */
+// Elements of the shard rank `rank` owns for a bucket of n elements of `grad_dtype` (state tensors need this many floats).
+size_t dcp_fused_shard_elems(size_t n, int world, int grad_dtype);
+// grads / params: device pointers INSIDE the symmetric heap (same offsets on every rank); the parameter buffer must
+// be padded to a multiple of 8 floats.  s1 / s2: this rank's state shards (dcp_fused_shard_elems floats, or null).
+// kind: 0 Adadelta, 1 SGD, 2 Adam.  hp: device hyper-parameter block (see ops/optim.cu; call dcp_optim_advance first).
+int dcp_fused_rs_opt_ag(void* h, const void* grads, float* params, float* s1, float* s2, size_t n, const float* hp, int kind, int grad_dtype, int use_nvls, int chan, int max_ctas, cudaStream_t stream);
+
 /* ---- csrc/ddp/reducer.cpp ---- */
 // Plan buckets.  `nbytes[i]` / `group_key[i]` describe tensor i in the order given (dtype+device folded
 // into group_key by the caller).  `limits` is the per-group sequence of size limits; the last entry
@@ -135,12 +143,8 @@ int dcp_gap_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, cudaS
 int dcp_correct_count(const void* x, const void* target, void* count, int M, int C, int dtype, cudaStream_t s);
 
 /* ---- csrc/ops/gemm_tc.cu ---- */
-// C[M,N] (+)= op(A) . op(B)^T with fp32 accumulation on tcgen05.
-//   a_mn = 0: A is [M][K] row-major (lda);   a_mn = 1: A is [K][M] row-major (lda)
-//   b_mn = 0: B is [N][K] row-major (ldb);   b_mn = 1: B is [K][N] row-major (ldb)
-// dtype: DCP_F32 (tf32 multiply) or DCP_BF16.  out: fp32 or bf16 (out_bf16), ldc elements.  ksplit > 1 => `out`
-// must be fp32 and zero-initialised (atomic accumulation; relu is rejected).  K must be a multiple of the 128-byte slab.
 int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s);
+int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s);
 // Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
 //   x: channels-last [N,H,W,C]; wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] (fp32 or bf16).
 // C must be a multiple of the 128-byte slab (32 f32 / 64 bf16).  (Wb,Hb,Nb): box of output pixels per CTA, product 128.

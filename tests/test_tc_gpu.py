@@ -30,10 +30,29 @@ def test_gemm_all_majors(dtype, a_mn, b_mn, M, N, K):
     Ast = (A.t().contiguous() if a_mn else A).to(dtype).contiguous()
     Bst = (B.t().contiguous() if b_mn else B).to(dtype).contiguous()
     out = torch.full((M, N), float("nan"), device=DEV)
-    tc.gemm(Ast, Bst, out, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn)
+    tc.gemm(Ast, Bst, out, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn, x3=False)
     torch.cuda.synchronize()
     tol = 2e-3 if dtype == torch.float32 else 1e-5   # tf32 multiplies truncate fp32 inputs; bf16 inputs are exact
     assert _rel_err(out, ref) < tol, (_rel_err(out, ref), dtype, a_mn, b_mn)
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1), (1, 0)])
+@pytest.mark.parametrize("M,N,K,ks", [(128, 128, 9216, 36), (200, 72, 384, 1), (128, 9216, 128, 1)])
+def test_gemm_3xtf32_is_fp32_accurate(a_mn, b_mn, M, N, K, ks):
+    """fp32 Linear layers use the 3xTF32 split: error must be at fp32 level, not tf32 level."""
+    tc = _tc()
+    torch.manual_seed(1)
+    A = torch.randn(M, K, device=DEV); B = torch.randn(N, K, device=DEV)
+    ref = A.double() @ B.double().t()
+    Ast = (A.t().contiguous() if a_mn else A).contiguous(); Bst = (B.t().contiguous() if b_mn else B).contiguous()
+    out = torch.zeros(M, N, device=DEV)
+    tc.gemm(Ast, Bst, out, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn, False, ks, x3=True)
+    e3 = _rel_err(out, ref)
+    out1 = torch.zeros(M, N, device=DEV)
+    tc.gemm(Ast, Bst, out1, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn, False, ks, x3=False)
+    e1 = _rel_err(out1, ref)
+    fp32 = _rel_err(A @ B.t(), ref)      # what cuBLAS fp32 gives
+    assert e3 < 2e-6 and e3 < e1 / 50, (e3, e1, fp32)
 
 
 def test_gemm_splitk_bias_relu_bf16_out():
