@@ -42,9 +42,12 @@ __device__ __forceinline__ uint64_t desc_k128(uint32_t addr, int use_base_offset
   return d;
 }
 
-struct __align__(8) Bars {
+struct __align__(16) Bars {
   uint64_t w_full, full[4], empty[4], acc_full[2], acc_empty[2];
   uint32_t tmem_base;
+  uint32_t adelta[72], wdelta[72];     // per-MMA start-address increments (16-byte units) of the A / W descriptors
+  alignas(16) float bias[64];
+  alignas(16) float stage_out[4][32][36];          // per-epilogue-warp transpose buffer: coalesced 128-byte row stores
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -70,6 +73,14 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
     }
     __syncwarp();
     tmem_alloc<kTmem>(&bars->tmem_base);
+  } else if (warp == 2) {
+    // descriptor increments: MMA m = (tap, channel chunk, k-step)
+    for (int m = lane; m < p.taps * cch * 4; m += 32) {
+      const int j = m & 3, cc = (m >> 2) % cch, t = (m >> 2) / cch;
+      bars->adelta[m] = (uint32_t)(((p.off[t] - p.min_off) * 128 + cc * chunk_bytes + j * 32) >> 4);
+      bars->wdelta[m] = (uint32_t)(((t * cch + cc) * (p.Cout * 128) + j * 32) >> 4);
+    }
+    for (int c = lane; c < p.Cout; c += 32) bars->bias[c] = p.bias ? p.bias[c] : 0.f;
   }
   tc_fence_before();
   __syncthreads();
@@ -101,20 +112,13 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       mbar_wait(&bars->acc_empty[ab], aph ^ 1);     // epilogue drained this accumulator
       mbar_wait(&bars->full[st], ph);
       tc_fence_after();
-      const uint32_t a0 = smem_u32(a_smem + st * stage_bytes), w0 = smem_u32(w_smem);
+      const uint64_t a_base = desc_k128(smem_u32(a_smem + st * stage_bytes), 0), w_base = desc_k128(smem_u32(w_smem), 0);
       const uint32_t tacc = tmem + ab * p.Cout;
-      uint32_t first = 0;
-      for (int t = 0; t < p.taps; ++t) {
-        const uint32_t arow = a0 + (uint32_t)(p.off[t] - p.min_off) * 128;
-        for (int cc = 0; cc < cch; ++cc) {
-          const uint32_t ab_addr = arow + cc * chunk_bytes, wb_addr = w0 + (t * cch + cc) * (p.Cout * 128);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) {
-            umma<true>(tacc, desc_k128(ab_addr + j * 32, p.use_base_offset), desc_k128(wb_addr + j * 32, 0), idesc, first);
-            first = 1;
-          }
-        }
-      }
+      const int nmma = p.taps * cch * 4;
+      // the start-address field (16-byte units, < 2^14) is the only part of the descriptor that changes
+      umma<true>(tacc, a_base + bars->adelta[0], w_base + bars->wdelta[0], idesc, 0);
+#pragma unroll 4
+      for (int m = 1; m < nmma; ++m) umma<true>(tacc, a_base + bars->adelta[m], w_base + bars->wdelta[m], idesc, 1);
       umma_commit(&bars->empty[st]);
       umma_commit(&bars->acc_full[ab]);
     }
@@ -131,37 +135,39 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
         const int q = (int)(pp % p.HW);
         valid = (q / p.W) < p.Hv && (q % p.W) < p.Wv;
       }
+      float (*so)[36] = bars->stage_out[warp - 2];
+      const long tile_row0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM + lg * 32;   // first row this warp owns
       for (int c0 = 0; c0 < p.Cout; c0 += 32) {
         uint32_t r[32];
         tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * p.Cout + c0, r);
         tmem_ld_wait();
-        if (pp < p.P) {
-          float* o = p.out + pp * p.Cout + c0;
+        // lane = row: bias / ReLU / validity here, then transpose through shared memory
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) {
+          float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
           if (p.mode == 0) {
+            const float4 b = *reinterpret_cast<const float4*>(&bars->bias[c0 + j]);
+            v.x = valid ? fmaxf(v.x + b.x, 0.f) : 0.f; v.y = valid ? fmaxf(v.y + b.y, 0.f) : 0.f;
+            v.z = valid ? fmaxf(v.z + b.z, 0.f) : 0.f; v.w = valid ? fmaxf(v.w + b.w, 0.f) : 0.f;
+          }
+          *reinterpret_cast<float4*>(&so[lane][j]) = v;
+        }
+        __syncwarp();
+        // 8 lanes cover one 128-byte output row, 4 rows per instruction: fully coalesced stores (and mask loads)
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 b = *reinterpret_cast<const float4*>(p.bias + c0 + j);
-              float4 v;
-              v.x = valid ? fmaxf(__uint_as_float(r[j]) + b.x, 0.f) : 0.f;
-              v.y = valid ? fmaxf(__uint_as_float(r[j + 1]) + b.y, 0.f) : 0.f;
-              v.z = valid ? fmaxf(__uint_as_float(r[j + 2]) + b.z, 0.f) : 0.f;
-              v.w = valid ? fmaxf(__uint_as_float(r[j + 3]) + b.w, 0.f) : 0.f;
-              *reinterpret_cast<float4*>(o + j) = v;
+        for (int it = 0; it < 8; ++it) {
+          const int rr = it * 4 + (lane >> 3), c4 = (lane & 7) * 4;
+          const long prow = tile_row0 + rr;
+          if (prow < p.P) {
+            float4 v = *reinterpret_cast<const float4*>(&so[rr][c4]);
+            if (p.mode == 1) {
+              const float4 mk = *reinterpret_cast<const float4*>(p.mask + prow * p.Cout + c0 + c4);
+              v.x = mk.x > 0.f ? v.x : 0.f; v.y = mk.y > 0.f ? v.y : 0.f; v.z = mk.z > 0.f ? v.z : 0.f; v.w = mk.w > 0.f ? v.w : 0.f;
             }
-          } else {
-            const float* m = p.mask + pp * p.Cout + c0;
-#pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 mk = *reinterpret_cast<const float4*>(m + j);
-              float4 v;
-              v.x = mk.x > 0.f ? __uint_as_float(r[j]) : 0.f;
-              v.y = mk.y > 0.f ? __uint_as_float(r[j + 1]) : 0.f;
-              v.z = mk.z > 0.f ? __uint_as_float(r[j + 2]) : 0.f;
-              v.w = mk.w > 0.f ? __uint_as_float(r[j + 3]) : 0.f;
-              *reinterpret_cast<float4*>(o + j) = v;
-            }
+            *reinterpret_cast<float4*>(p.out + prow * p.Cout + c0 + c4) = v;
           }
         }
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();

@@ -117,7 +117,8 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float* __restrict__ dpoo
   }
 }
 
-// dz1 [P,32], x [N,28,28] -> dw1[32][9] += , db1[32] +=   (8 pixel lanes x 32 channels per CTA)
+// dz1 [P,32], x [N,28,28] -> dw1[32][9] += , db1[32] +=   (8 pixel lanes x 32 channels per CTA; each lane keeps
+// 4 pixels in flight so the dependent-load chain is short; one atomic per output per CTA)
 __global__ void __launch_bounds__(256) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
                                                      float* __restrict__ db1, long total_pixels) {
   __shared__ float red[8][32][11];
@@ -125,15 +126,26 @@ __global__ void __launch_bounds__(256) k_conv1_wgrad(const float* __restrict__ d
   float acc[10];
 #pragma unroll
   for (int t = 0; t < 10; ++t) acc[t] = 0.f;
-  for (long pix = (long)blockIdx.x * 8 + lane; pix < total_pixels; pix += (long)gridDim.x * 8) {
-    const float g = dz1[pix * 32 + c];
-    const int n = (int)(pix / P1), q = (int)(pix % P1), h = q / HW1, wq = q % HW1;
-    const float* xi = x + (long)n * 784 + h * 28 + wq;
+  const long stride = (long)gridDim.x * 8;
+  for (long p0 = (long)blockIdx.x * 8 + lane; p0 < total_pixels; p0 += 4 * stride) {
+    float g[4]; const float* xi[4];
 #pragma unroll
-    for (int r = 0; r < 3; ++r)
+    for (int u = 0; u < 4; ++u) {
+      const long pix = p0 + u * stride;
+      const bool ok = pix < total_pixels;
+      g[u] = ok ? dz1[pix * 32 + c] : 0.f;
+      const long pc = ok ? pix : 0;
+      const int n = (int)(pc / P1), q = (int)(pc % P1), h = q / HW1, wq = q % HW1;
+      xi[u] = x + (long)n * 784 + h * 28 + wq;
+    }
 #pragma unroll
-      for (int s = 0; s < 3; ++s) acc[r * 3 + s] = fmaf(g, __ldg(xi + r * 28 + s), acc[r * 3 + s]);
-    acc[9] += g;
+    for (int u = 0; u < 4; ++u) {
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int s = 0; s < 3; ++s) acc[r * 3 + s] = fmaf(g[u], __ldg(xi[u] + r * 28 + s), acc[r * 3 + s]);
+      acc[9] += g[u];
+    }
   }
 #pragma unroll
   for (int t = 0; t < 10; ++t) red[lane][c][t] = acc[t];
@@ -168,8 +180,197 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
 }
 // dw1 / db1 are accumulated into: the caller zeroes them (they normally live in the gradient bucket).
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
-  k_conv1_wgrad<<<148 * 4, 256, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
+  k_conv1_wgrad<<<148 * 2, 256, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 
+}  // extern "C"
+
+// =====================================================================================================
+// Head of the network in ONE kernel, forward AND backward (K9-K14 and their gradients, ref:main.py:40-44,61):
+//   h1[N,128] -> BatchNorm1d (batch statistics, running-stat update) -> ReLU -> dropout p2 -> fc2 (128 -> 10)
+//   -> log_softmax + nll (mean) -> d logits -> fc2 weight/bias/data gradients -> dropout / ReLU backward
+//   -> BatchNorm backward -> dh1[N,128], dgamma, dbeta.
+// The whole problem is 16 K activations, so it lives in the shared memory of a single 1024-thread CTA; the
+// 13 launches it replaces cost ~65 us of launch latency and tail effects.  N <= 128 rows.
+// Thread (f = tid % 128, rg = tid / 128) owns feature f of rows rg, rg + 8, ...
+// =====================================================================================================
+namespace {
+constexpr int HF = 128, HC = 10, HRG = 8, HMAXN = 128, HR = HMAXN / HRG;
+
+struct HeadSmem {
+  float xhat[HMAXN][HF];
+  float h3[HMAXN][HF];
+  float w2[HC][HF];
+  float dlog[HMAXN][HC + 2];
+  float red[HRG][HF][HC + 1];
+  float stat[4][HF];      // mean, rstd, dbeta/N, dgamma/N
+  float loss;
+};
+
+__global__ void __launch_bounds__(1024, 1)
+k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ target, const float* __restrict__ gamma, const float* __restrict__ beta,
+               float* __restrict__ run_mean, float* __restrict__ run_var, long long* __restrict__ nbt, const float* __restrict__ w2,
+               const float* __restrict__ b2, float* __restrict__ loss_out, float* __restrict__ logits_out, float* __restrict__ dh1,
+               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2, float* __restrict__ db2, int N, float eps,
+               float momentum, float p2, unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training) {
+  extern __shared__ __align__(16) uint8_t head_raw[];
+  HeadSmem& S = *reinterpret_cast<HeadSmem*>(head_raw);
+  const int tid = threadIdx.x, f = tid & (HF - 1), rg = tid >> 7, warp = tid >> 5, lane = tid & 31;
+  const float invN = 1.f / (float)N;
+  float x[HR];
+  // ---- 1. batch statistics (two-pass, data stays in registers) ----
+  float s = 0.f;
+#pragma unroll
+  for (int i = 0; i < HR; ++i) { const int r = rg + i * HRG; x[i] = r < N ? h1[r * HF + f] : 0.f; s += x[i]; }
+  S.red[rg][f][0] = s;
+  for (int i = tid; i < HC * HF; i += 1024) S.w2[i / HF][i % HF] = w2[i];
+  if (tid == 0) S.loss = 0.f;
+  __syncthreads();
+  if (rg == 0) { float t = 0.f; for (int g = 0; g < HRG; ++g) t += S.red[g][f][0]; S.stat[0][f] = t * invN; }
+  __syncthreads();
+  const float mean = S.stat[0][f];
+  float v = 0.f;
+#pragma unroll
+  for (int i = 0; i < HR; ++i) { const int r = rg + i * HRG; if (r < N) { const float d = x[i] - mean; v += d * d; } }
+  S.red[rg][f][1] = v;
+  __syncthreads();
+  if (rg == 0) {
+    float t = 0.f; for (int g = 0; g < HRG; ++g) t += S.red[g][f][1];
+    const float var = t * invN;
+    S.stat[1][f] = rsqrtf(var + eps);
+    if (training && run_mean) {
+      const float unbiased = N > 1 ? var * (float)N / (float)(N - 1) : var;
+      run_mean[f] = (1.f - momentum) * run_mean[f] + momentum * mean;
+      run_var[f] = (1.f - momentum) * run_var[f] + momentum * unbiased;
+    }
+  }
+  if (tid == 0 && training && nbt) *nbt += 1;
+  __syncthreads();
+  // ---- 2. normalise + affine + ReLU + dropout ----
+  const float rstd = S.stat[1][f], gm = gamma[f], bt = beta[f];
+  const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
+  const float dscale = (training && p2 > 0.f) ? 1.f / (1.f - p2) : 1.f;
+  unsigned keep = 0, pos = 0;   // bit i: dropout kept / ReLU active for row rg + 8 i
+#pragma unroll
+  for (int i = 0; i < HR; ++i) {
+    const int r = rg + i * HRG;
+    float xh = 0.f, h = 0.f;
+    if (r < N) {
+      xh = (x[i] - mean) * rstd;
+      float a = xh * gm + bt;
+      if (a > 0.f) pos |= 1u << i; else a = 0.f;
+      bool k = true;
+      if (training && p2 > 0.f) k = philox_uniform(seed, st, (unsigned long long)(r * HF + f)) >= p2;
+      if (k) keep |= 1u << i;
+      h = k ? a * dscale : 0.f;
+    }
+    S.xhat[r][f] = xh;      // r < HMAXN always: rg < 8, i < 16
+    S.h3[r][f] = h;
+  }
+  __syncthreads();
+  // ---- 3. fc2 + log-softmax + nll + dlogits: one warp per row ----
+  for (int r = warp; r < N; r += 32) {
+    float acc[HC];
+#pragma unroll
+    for (int j = 0; j < HC; ++j) acc[j] = 0.f;
+#pragma unroll
+    for (int q = 0; q < HF / 32; ++q) {
+      const float hv = S.h3[r][lane + 32 * q];
+#pragma unroll
+      for (int j = 0; j < HC; ++j) acc[j] = fmaf(hv, S.w2[j][lane + 32 * q], acc[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < HC; ++j) acc[j] = warp_sum(acc[j]) + b2[j];
+    float m = acc[0];
+#pragma unroll
+    for (int j = 1; j < HC; ++j) m = fmaxf(m, acc[j]);
+    float se = 0.f;
+#pragma unroll
+    for (int j = 0; j < HC; ++j) se += __expf(acc[j] - m);
+    const float lse = m + __logf(se);
+    const int t = (int)target[r];
+    if (lane < HC) {
+      const float pj = __expf(acc[lane] - lse);
+      S.dlog[r][lane] = (pj - (lane == t ? 1.f : 0.f)) * invN;
+      if (logits_out) logits_out[r * HC + lane] = acc[lane] - lse;     // log-probabilities, as the model's forward returns
+    }
+    if (lane == 0 && t >= 0 && t < HC) atomicAdd(&S.loss, (lse - acc[t]) * invN);
+  }
+  __syncthreads();
+  if (tid == 0) *loss_out = S.loss;
+  // ---- 4. fc2 gradients ----
+  float gw[HC];
+#pragma unroll
+  for (int j = 0; j < HC; ++j) gw[j] = 0.f;
+#pragma unroll
+  for (int i = 0; i < HR; ++i) {
+    const int r = rg + i * HRG;
+    if (r < N) {
+      const float hv = S.h3[r][f];
+#pragma unroll
+      for (int j = 0; j < HC; ++j) gw[j] = fmaf(S.dlog[r][j], hv, gw[j]);
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < HC; ++j) S.red[rg][f][j] = gw[j];
+  __syncthreads();
+  for (int i = tid; i < HC * HF; i += 1024) {
+    const int j = i / HF, ff = i % HF;
+    float t = 0.f;
+#pragma unroll
+    for (int g = 0; g < HRG; ++g) t += S.red[g][ff][j];
+    dw2[i] = t;
+  }
+  if (tid < HC) { float t = 0.f; for (int r = 0; r < N; ++r) t += S.dlog[r][tid]; db2[tid] = t; }
+  // ---- 5. dh3 -> dropout / ReLU backward -> BatchNorm backward ----
+  float g[HR];
+  float sb = 0.f, sg = 0.f;
+#pragma unroll
+  for (int i = 0; i < HR; ++i) {
+    const int r = rg + i * HRG;
+    float gv = 0.f;
+    if (r < N && ((keep >> i) & 1u) && ((pos >> i) & 1u)) {
+#pragma unroll
+      for (int j = 0; j < HC; ++j) gv = fmaf(S.dlog[r][j], S.w2[j][f], gv);
+      gv *= dscale;
+    }
+    g[i] = gv;
+    sb += gv;
+    sg += gv * S.xhat[r][f];
+  }
+  __syncthreads();                       // S.red is reused
+  S.red[rg][f][0] = sb; S.red[rg][f][1] = sg;
+  __syncthreads();
+  if (rg == 0) {
+    float tb = 0.f, tg = 0.f;
+    for (int q = 0; q < HRG; ++q) { tb += S.red[q][f][0]; tg += S.red[q][f][1]; }
+    dbeta[f] = tb; dgamma[f] = tg;
+    S.stat[2][f] = tb * invN; S.stat[3][f] = tg * invN;
+  }
+  __syncthreads();
+  const float k1 = gm * rstd, k2 = S.stat[2][f], k3 = S.stat[3][f];
+#pragma unroll
+  for (int i = 0; i < HR; ++i) {
+    const int r = rg + i * HRG;
+    if (r < N) dh1[r * HF + f] = k1 * (g[i] - k2 - S.xhat[r][f] * k3);
+  }
+}
+}  // namespace
+
+extern "C" {
+// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null.  All gradient outputs are
+// fully overwritten.  Training mode only (batch statistics); p2 = dropout probability of the second dropout.
+int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
+                     const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2,
+                     float* db2, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id,
+                     const void* step, int training, cudaStream_t s) {
+  if (N < 1 || N > HMAXN) { dcp_set_error("convnet head: batch %d not in [1, %d]", N, HMAXN); return -1; }
+  static bool attr = false;
+  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_convnet_head, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HeadSmem))); attr = true; }
+  k_convnet_head<<<1, 1024, sizeof(HeadSmem), s>>>(h1, (const long long*)target, gamma, beta, run_mean, run_var, (long long*)nbt, w2, b2, loss,
+                                                   logits_out, dh1, dgamma, dbeta, dw2, db2, N, eps, momentum, p2, seed, stream_id,
+                                                   (const long long*)step, training);
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
 }  // extern "C"

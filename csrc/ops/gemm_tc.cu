@@ -28,6 +28,7 @@ struct TcGemmParams {
   int groups, units, a_bytes;   // accumulator groups per CTA (1 except wgrad), (tap, chunk) units in total, bytes of one A stage
   // epilogue
   void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
+  long partial_stride;      // > 0: split z writes its partial tile to out + z * partial_stride with plain stores (reduced by dcp_splitk_reduce)
 };
 
 namespace {
@@ -147,22 +148,25 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         mbar_wait(p.x3 ? &pipe->split[st] : &pipe->full[st], ph);
         tc_fence_after();
         const uint32_t sa0 = smem_u32(smem + st * stage_bytes), sb = sa0 + a_bytes;
+        // descriptors: only the start-address field (16-byte units) moves between k-steps, so build one base per
+        // operand and stage and add the step (MN-major: k-rows are 128 B apart; tf32 needs the BASE32B layout)
+        constexpr uint32_t kMnSbo = kTF32 ? 512 : 1024, kMnLayout = kTF32 ? 1 : 2;
+        const uint64_t db0 = p.b_mn ? make_smem_desc(sb, kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sb, 0, 1024);
+        const uint64_t step_a = p.a_mn ? (uint64_t)((kUmmaK * 128) >> 4) : 2u, step_b = p.b_mn ? (uint64_t)((kUmmaK * 128) >> 4) : 2u;
+        const uint64_t lo_step = (uint64_t)(half_bytes >> 4);
         for (int g = 0; g < p.groups; ++g) {
-        const uint32_t sa = sa0 + g * kABytes;
-        const uint32_t tmem_g = tmem + g * p.BN;
+          const uint32_t sa = sa0 + g * kABytes;
+          const uint32_t tmem_g = tmem + g * p.BN;
+          const uint64_t da0 = p.a_mn ? make_smem_desc(sa, kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sa, 0, 1024);
 #pragma unroll
-        for (int j = 0; j < kBK / kUmmaK; ++j) {
-          // MN-major: k-rows are 128 B apart (TMA box rows); tf32 needs the BASE32B layout (4-row atoms)
-          constexpr uint32_t kMnSbo = kTF32 ? 512 : 1024, kMnLayout = kTF32 ? 1 : 2;
-          const uint64_t da = p.a_mn ? make_smem_desc(sa + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sa + j * 32, 0, 1024);
-          const uint64_t db = p.b_mn ? make_smem_desc(sb + j * (kUmmaK * 128), kBK * 128, kMnSbo, kMnLayout) : make_smem_desc(sb + j * 32, 0, 1024);
-          umma<kTF32>(tmem_g, da, db, idesc, (i | j) != 0);
-          if (kTF32 && p.x3) {   // + A_lo * B_hi + A_hi * B_lo (the lo tiles sit half_bytes further on)
-            const uint64_t lo_step = (uint64_t)(half_bytes >> 4);   // start-address field is in 16-byte units
-            umma<kTF32>(tmem_g, da + lo_step, db, idesc, 1);
-            umma<kTF32>(tmem_g, da, db + lo_step, idesc, 1);
+          for (int j = 0; j < kBK / kUmmaK; ++j) {
+            const uint64_t da = da0 + j * step_a, db = db0 + j * step_b;
+            umma<kTF32>(tmem_g, da, db, idesc, (i | j) != 0);
+            if (kTF32 && p.x3) {   // + A_lo * B_hi + A_hi * B_lo (the lo tiles sit half_bytes further on)
+              umma<kTF32>(tmem_g, da + lo_step, db, idesc, 1);
+              umma<kTF32>(tmem_g, da, db + lo_step, idesc, 1);
+            }
           }
-        }
         }
         umma_commit(&pipe->empty[st]);   // smem slot reusable once these MMAs retire
       }
@@ -206,11 +210,20 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         const int unit = (m_tile * p.groups + g) * kUnitsPerGroup + row / kChunk;
         const bool valid = unit < p.units;
         const int tap = unit / p.cchunks, cc = unit % p.cchunks;
-        float* orow = (float*)p.out + (long)tap * p.Cin + cc * kChunk + (row % kChunk);
+        float* orow = (float*)p.out + (p.partial_stride ? (long)blockIdx.z * p.partial_stride : 0) + (long)tap * p.Cin + cc * kChunk + (row % kChunk);
         for (int c0 = 0; c0 < p.BN; c0 += 32) {
           uint32_t r[32];
           if (nst > 0) { tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + g * p.BN + c0, r); tmem_ld_wait(); }
-          if (!valid || nst <= 0) continue;
+          if (!valid) continue;
+          if (p.partial_stride) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int k = n_tile * p.BN + c0 + j;
+              if (k < p.N) orow[(long)k * p.ldc] = nst > 0 ? __uint_as_float(r[j]) : 0.f;   // lanes = consecutive c: coalesced 128-B stores
+            }
+            continue;
+          }
+          if (nst <= 0) continue;
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const int k = n_tile * p.BN + c0 + j;
@@ -228,7 +241,8 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const long gm = (long)m_tile * kBM + row;
       if (gm < p.M) out_row = gm;
     }
-    const bool add_bias = p.bias != nullptr && blockIdx.z == 0;
+    const bool add_bias = p.bias != nullptr && blockIdx.z == 0 && p.partial_stride == 0;
+    const long zoff = p.partial_stride ? (long)blockIdx.z * p.partial_stride : 0;
     for (int c0 = 0; c0 < p.BN; c0 += 32) {
       uint32_t r[32];
       if (nst > 0) {
@@ -271,7 +285,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           for (int j = 0; j < ncol; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
         }
       } else {
-        float* o = (float*)p.out + out_row * p.ldc + gn0;
+        float* o = (float*)p.out + zoff + out_row * p.ldc + gn0;
         if (ncol == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
 #pragma unroll
           for (int j = 0; j < 32; j += 4) *reinterpret_cast<uint4*>(o + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
@@ -375,11 +389,16 @@ int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, in
   const int es = dtype == DCP_F32 ? 4 : 2, bk = 128 / es;
   if (dtype != DCP_F32 && dtype != DCP_BF16) { dcp_set_error("tc gemm: dtype must be f32 or bf16"); return -1; }
   if (K % bk) { dcp_set_error("tc gemm: K=%d must be a multiple of %d", K, bk); return -1; }
+  // ksplit < -1: split-K through a scratch buffer: `out` is then a [|ksplit|][M*ldc] fp32 scratch that receives the partial
+  // tiles with plain stores (no atomics); finish with dcp_splitk_reduce (which also adds the bias)
+  const bool partial = ksplit < -1;
+  if (partial) ksplit = -ksplit;
   if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
   TcGemmParams p{};
   p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
   p.b_bytes = b_stage_bytes(p.BN, b_mn, es); p.a_bytes = kABytes; p.groups = 1; p.x3 = (x3 && dtype == DCP_F32) ? 1 : 0;
-  p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
+  p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1 && !partial; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
+  p.partial_stride = partial ? (long)M * ldc : 0;
   CUtensorMap ma, mb;
   if (!a_mn) { if (make_map_2d(&ma, A, es, M, K, lda, bk, kBM)) return -1; }
   else { if (make_map_2d(&ma, A, es, K, M, lda, bk, bk, true)) return -1; }
@@ -432,8 +451,12 @@ int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, 
   p.b_bytes = b_stage_bytes(p.BN, 1, es);
   p.Wb = Wb; p.Hb = Hb; p.Nb = Nb; p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
   p.k_stages = p.tiles_w * p.tiles_h * ((N + Nb - 1) / Nb);
+  // zsplit < -1: partial mode - dw32 is a [|zsplit|][Kout*R*S*C] scratch, finish with dcp_splitk_reduce
+  const bool partial = zsplit < -1;
+  if (partial) zsplit = -zsplit;
   p.out = dw32; p.ldc = (long)R * S * C; p.atomic = 1;
-  DCP_CUDA_CHECK(cudaMemsetAsync(dw32, 0, sizeof(float) * (size_t)Kout * R * S * C, s));
+  p.partial_stride = partial ? (long)Kout * R * S * C : 0;
+  if (!partial) DCP_CUDA_CHECK(cudaMemsetAsync(dw32, 0, sizeof(float) * (size_t)Kout * R * S * C, s));
   CUtensorMap ma, mb;
   if (make_map_4d(&ma, x, es, N, H, W, C, chunk, Wb, Hb, Nb, true)) return -1;
   if (make_map_4d(&mb, dy, es, N, Ho, Wo, Kout, chunk, Wb, Hb, Nb, true)) return -1;
@@ -457,6 +480,40 @@ template <typename T> __global__ void k_flip_weights(const T* __restrict__ w, T*
   }
 }
 }  // namespace
+// out[i] = (bias ? bias[i % ncols] : 0) + sum_z scratch[z][i]   - finishes a split-K done through scratch
+namespace {
+// CTA = 32 float4 columns x 8 split lanes: the (long) chain of dependent loads over the splits is cut 8 ways and the
+// grid stays wide even for a 128 x 128 output
+__global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__ scratch, float* __restrict__ out, const float* __restrict__ bias,
+                                                       int nsplit, long n, int ncols) {
+  __shared__ float4 red[8][33];
+  const int vx = threadIdx.x & 31, zl = threadIdx.x >> 5;
+  const long v = (long)blockIdx.x * 32 + vx, n4 = n / 4;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (v < n4) {
+#pragma unroll 4
+    for (int z = zl; z < nsplit; z += 8) {
+      const float4 x = *reinterpret_cast<const float4*>(scratch + (long)z * n + v * 4);
+      acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+    }
+  }
+  red[zl][vx] = acc;
+  __syncthreads();
+  if (zl == 0 && v < n4) {
+#pragma unroll
+    for (int i = 1; i < 8; ++i) { const float4 x = red[i][vx]; acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w; }
+    if (bias) { const int c = (int)((v * 4) % ncols); acc.x += bias[c]; acc.y += bias[c + 1]; acc.z += bias[c + 2]; acc.w += bias[c + 3]; }
+    *reinterpret_cast<float4*>(out + v * 4) = acc;
+  }
+}
+}  // namespace
+// n and ncols must be multiples of 4.
+extern "C" int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s) {
+  if ((n & 3) || (ncols & 3)) { dcp_set_error("splitk reduce: n and ncols must be multiples of 4"); return -1; }
+  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, bias, nsplit, n, ncols);
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
 extern "C" int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s) {
   long total = (long)K * R * S * C;
   DISPATCH_ACT(dtype, (k_flip_weights<T><<<grid_1d(total, 256), 256, 0, s>>>((const T*)w, (T*)wt, K, R, S, C)));

@@ -26,6 +26,8 @@ def declare(lib) -> None:
     lib.dcp_tc_conv.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
     lib.dcp_tc_conv_wgrad.restype = C.c_int
     lib.dcp_tc_conv_wgrad.argtypes = [vp, vp, vp] + [i] * 15 + [vp]
+    lib.dcp_splitk_reduce.restype = C.c_int
+    lib.dcp_splitk_reduce.argtypes = [vp, vp, vp, i, l, i, vp]
     lib.dcp_flip_weights.restype = C.c_int
     lib.dcp_flip_weights.argtypes = [vp, vp, i, i, i, i, i, vp]
     _lib = lib
@@ -59,11 +61,21 @@ def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit
 
 
 def _ksplit(M: int, N: int, K: int, dtype) -> int:
+    """K splits for skinny problems: enough CTAs to pull the operands at full rate, >= 4 K slabs per CTA."""
     tiles = -(-M // 128) * -(-N // (32 if N <= 32 else 64 if N <= 64 else 128))
     stages = K // _bk(dtype)
     if tiles >= NUM_SMS // 2 or stages < 8:
         return 1
-    return max(1, min(stages // 2, NUM_SMS // tiles))
+    return max(1, min(stages // 4, NUM_SMS // tiles))
+
+
+def gemm_splitk(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, ks, x3=None) -> None:
+    """Split-K GEMM without atomics: partial tiles go to a scratch buffer with plain stores, then one reduce kernel
+    sums them (and adds the bias) into ``out`` (fp32, ldc == N)."""
+    k = _k()
+    scratch = torch.empty(ks * M * N, dtype=torch.float32, device=out.device)
+    gemm(A, B, scratch, None, M, N, K, lda, ldb, N, a_mn, b_mn, False, -ks, x3)
+    k._chk(_lib.dcp_splitk_reduce(scratch.data_ptr(), out.data_ptr(), k._p(bias), ks, M * N, N, k._stream()))
 
 
 def linear_supported(M: int, N: int, K: int, dtype) -> bool:
@@ -76,8 +88,9 @@ def linear_fwd(x2, w, b, y, relu) -> None:
     N = w.shape[0]
     ks = _ksplit(M, N, K, x2.dtype) if (y.dtype == torch.float32 and not relu) else 1
     if ks > 1:
-        y.zero_()
-    gemm(x2, w, y, b, M, N, K, K, K, N, 0, 0, relu, ks)
+        gemm_splitk(x2, w, y, b, M, N, K, K, K, N, 0, 0, ks)
+    else:
+        gemm(x2, w, y, b, M, N, K, K, K, N, 0, 0, relu, 1)
 
 
 def linear_dgrad(dy, w, dx) -> None:
@@ -86,8 +99,9 @@ def linear_dgrad(dy, w, dx) -> None:
     K = w.shape[1]
     ks = _ksplit(M, K, N, dy.dtype) if dx.dtype == torch.float32 else 1
     if ks > 1:
-        dx.zero_()
-    gemm(dy, w, dx, None, M, K, N, N, K, K, 0, 1, False, ks)
+        gemm_splitk(dy, w, dx, None, M, K, N, N, K, K, 0, 1, ks)
+    else:
+        gemm(dy, w, dx, None, M, K, N, N, K, K, 0, 1, False, 1)
 
 
 def linear_wgrad(dy, x2, dw32, db32) -> None:
@@ -96,8 +110,9 @@ def linear_wgrad(dy, x2, dw32, db32) -> None:
     K = x2.shape[1]
     ks = _ksplit(N, K, M, dy.dtype)
     if ks > 1:
-        dw32.zero_()
-    gemm(dy, x2, dw32, None, N, K, M, N, K, K, 1, 1, False, ks)
+        gemm_splitk(dy, x2, dw32, None, N, K, M, N, K, K, 1, 1, ks)
+    else:
+        gemm(dy, x2, dw32, None, N, K, M, N, K, K, 1, 1, False, 1)
     if db32 is not None:
         k = _k()
         k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), M, N, k._dt(dy), k._stream()))
@@ -145,6 +160,20 @@ def conv2d_dgrad(dy, w, dx, p) -> None:
                             wb, hb, nb, k._dt(dy), int(dx.dtype == torch.bfloat16), 0, 0, k._stream()))
 
 
+def conv_wgrad_launch(dy, x, dw32, N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb, zsplit) -> None:
+    """Weight-gradient kernel; with several pixel splits the partial filters meet in a scratch buffer + reduce."""
+    k = _k()
+    if zsplit > 1:
+        n = Kout * R * S * Cc
+        scratch = torch.empty(zsplit * n, dtype=torch.float32, device=dw32.device)
+        k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), scratch.data_ptr(), N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb,
+                                      k._dt(dy), -zsplit, k._stream()))
+        k._chk(_lib.dcp_splitk_reduce(scratch.data_ptr(), dw32.data_ptr(), None, zsplit, n, 4, k._stream()))
+    else:
+        k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb,
+                                      k._dt(dy), 1, k._stream()))
+
+
 def conv_wgrad_supported(p, dtype) -> bool:
     return (_ok_dtype(dtype) and p.stride == 1 and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16
             and os.environ.get("DCP_TC_CONV", "1") == "1")
@@ -161,8 +190,7 @@ def conv2d_wgrad(dy, x, dw32, db32, p) -> None:
     bn = 32 if p.K <= 32 else 64 if p.K <= 64 else 128
     g = max(1, min(3, groups_total, 512 // bn))
     ctas = -(-groups_total // g) * -(-p.K // bn)
-    zsplit = max(1, min(boxes, (2 * NUM_SMS) // ctas if ctas < NUM_SMS else 1))
-    k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo,
-                                  wb, hb, nb, k._dt(dy), zsplit, k._stream()))
+    zsplit = max(1, min(boxes, NUM_SMS // ctas if ctas < NUM_SMS else 1))
+    conv_wgrad_launch(dy, x, dw32, p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo, wb, hb, nb, zsplit)
     if db32 is not None:
         k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), p.N * p.Ho * p.Wo, p.K, k._dt(dy), k._stream()))

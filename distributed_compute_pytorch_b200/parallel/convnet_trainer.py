@@ -88,6 +88,7 @@ class FusedConvNetTrainer:
         if K.graph_step is None:
             K.graph_step = torch.zeros((), dtype=torch.int64, device=dev)
         self.training = True
+        self.fused_head = True
         self.comm_ctas = 16
         self.launches_per_step = 0
         self.graph = None
@@ -109,11 +110,41 @@ class FusedConvNetTrainer:
         ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
                               self.off_fwd, 26, 676, 24, 24, 0, 148, s()))
         ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
-        ks = tc._ksplit(N, 128, 9216, torch.float32)
-        if ks > 1:
-            self.h1.zero_()
-        tc.gemm(self.pooled, p["fc1.weight"], self.h1, p["fc1.bias"], N, 128, 9216, 9216, 9216, 128, 0, 0, False, ks)
+        tc.linear_fwd(self.pooled, p["fc1.weight"], p["fc1.bias"], self.h1, False)
         bn = net.batchnorm
+        if N <= 128 and self.fused_head:
+            # BatchNorm + ReLU + dropout + fc2 + log_softmax/nll and ALL of their gradients: one single-CTA kernel
+            ck(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                                  bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
+                                  self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
+                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), N, bn.eps, bn.momentum,
+                                  net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, tr, s()))
+        else:
+            self._head_unfused(L, ck, s, p, g, bn, N, tr, step_ptr)
+        tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
+        ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
+        ev0 = self._reduce_bucket(0)
+        tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+        # ---- backward: convolutional trunk
+        ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
+                                  self.seed, 1, step_ptr, tr, s()))
+        tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
+        ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
+        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
+        ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
+                              self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
+        g["conv1.weight"].zero_(); g["conv1.bias"].zero_()
+        ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
+        ev1 = self._reduce_bucket(1)
+        for ev in (ev0, ev1):
+            if ev is not None:
+                torch.cuda.current_stream(self.dev).wait_event(ev)
+        self.opt.step()
+
+
+    def _head_unfused(self, L, ck, s, p, g, bn, N, tr, step_ptr) -> None:
+        """Kernel-per-op version of the head (any batch size); numerically the same as dcp_convnet_head."""
+        net = self.net
         ck(L.dcp_bn_stats(self.h1.data_ptr(), self.bn_scratch.data_ptr(), N, 128, 0, s()))
         ck(L.dcp_bn_apply(self.h1.data_ptr(), self.h2.data_ptr(), self.bn_scratch.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
                           bn.running_mean.data_ptr(), bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), self.bn_mean.data_ptr(),
@@ -131,26 +162,17 @@ class FusedConvNetTrainer:
         ck(L.dcp_bn_bwd_apply(self.h1.data_ptr(), self.h2.data_ptr(), self.dh2.data_ptr(), self.dh1.data_ptr(), self.bn_mean.data_ptr(),
                               self.bn_rstd.data_ptr(), bn.weight.data_ptr(), self.bn_scratch.data_ptr(), g["batchnorm.weight"].data_ptr(),
                               g["batchnorm.bias"].data_ptr(), N, 128, float(N), 1, 0, s()))
-        tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
-        ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
-        ev0 = self._reduce_bucket(0)
-        tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
-        # ---- backward: convolutional trunk
-        ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
-                                  self.seed, 1, step_ptr, tr, s()))
-        ck(tc._lib.dcp_tc_conv_wgrad(self.dy2.data_ptr(), self.a1.data_ptr(), g["conv2.weight"].data_ptr(), N, 26, 26, 32, 64, 3, 3, 0, 26, 26,
-                                     8, 4, 1, 0, 148, s()))
-        ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
-        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
-        ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
-                              self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
-        g["conv1.weight"].zero_(); g["conv1.bias"].zero_()
-        ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
-        ev1 = self._reduce_bucket(1)
-        for ev in (ev0, ev1):
-            if ev is not None:
-                torch.cuda.current_stream(self.dev).wait_event(ev)
-        self.opt.step()
+
+    def _issue_head_only(self) -> None:
+        """Just the fused head kernel (used by bench/kernel_bench.py)."""
+        L, net, N, bn = K.lib(), self.net, self.N, self.net.batchnorm
+        p = {n: t for n, t in net.named_parameters()}
+        g = {n: t.grad for n, t in p.items()}
+        K._chk(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                                  bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
+                                  self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
+                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), N, bn.eps, bn.momentum,
+                                  net.dropout2.p, self.seed, 2, K.graph_step.data_ptr(), 1, K._stream()))
 
     def _reduce_bucket(self, idx: int):
         if self.be is None or idx >= len(self.buckets):

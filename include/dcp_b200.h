@@ -130,6 +130,9 @@ int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float
 int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* arg, float* dy2, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
 // dw1 / db1 are accumulated into: the caller zeroes them (they normally live in the gradient bucket).
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s);
+// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null.  All gradient outputs are
+// fully overwritten.  Training mode only (batch statistics); p2 = dropout probability of the second dropout.
+int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
 
 /* ---- csrc/ops/elementwise.cu ---- */
 int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
@@ -156,6 +159,8 @@ int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int 
 // taps, B is the matching box of dy.  gridDim.z splits the pixel boxes; partial sums meet in fp32 atomics, so
 // dw32 ([Kout][R*S*C] fp32) is zeroed here.
 int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
+// n and ncols must be multiples of 4.
+int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s);
 int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s);
 
 /* ---- csrc/ops/loss.cu ---- */

@@ -86,5 +86,33 @@ def test_training_reduces_loss_with_dropout_and_graph():
     assert sum(losses[-8:]) / 8 < 0.7 * sum(losses[:8]) / 8, (losses[:4], losses[-4:])
     # dropout masks change from replay to replay (device-side step counter)
     tr.x.copy_(xs[:N]); tr.y.copy_(ys[:N])
-    tr.graph.replay(); a = tr.h3.clone(); tr.graph.replay(); b = tr.h3.clone()
+    tr.graph.replay(); a = tr.pooled.clone(); tr.graph.replay(); b = tr.pooled.clone()
     assert not torch.equal(a == 0, b == 0)
+
+
+def test_fused_head_kernel_matches_kernel_per_op_head():
+    """dcp_convnet_head (one CTA: BN+ReLU+dropout+fc2+CE forward and backward) vs the separate kernels, with dropout
+    ON: both derive their masks from the same Philox (seed, stream, step, index), so results must agree closely."""
+    N = 128
+    outs = []
+    for fused in (True, False):
+        torch.manual_seed(3)
+        net = dcp.models.ConvNet().to(DEV).train()
+        opt = ops.Adadelta(net.parameters(), lr=0.0)
+        tr = FusedConvNetTrainer(net, opt, N, use_graph=False, seed=1234)
+        tr.fused_head = fused
+        from distributed_compute_pytorch_b200.ops import cuda as K
+        K.graph_step.zero_()
+        g = torch.Generator().manual_seed(9)
+        x = torch.randn(N, 1, 28, 28, generator=g).to(DEV); y = torch.randint(0, 10, (N,), generator=g).to(DEV)
+        loss = tr.step(x, y).clone()
+        torch.cuda.synchronize()
+        outs.append((loss, tr.dh1.clone(), {n: p.grad.clone() for n, p in net.named_parameters()},
+                     net.batchnorm.running_mean.clone(), net.batchnorm.running_var.clone()))
+    (l0, d0, g0, rm0, rv0), (l1, d1, g1, rm1, rv1) = outs
+    assert abs(l0.item() - l1.item()) < 1e-4
+    assert _relerr(d0, d1) < 1e-3
+    assert _relerr(rm0, rm1) < 1e-5 and _relerr(rv0, rv1) < 1e-4
+    for n in g0:
+        if n != "fc1.bias":
+            assert _relerr(g0[n], g1[n]) < 2e-3, (n, _relerr(g0[n], g1[n]))

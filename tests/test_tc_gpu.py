@@ -52,7 +52,7 @@ def test_gemm_3xtf32_is_fp32_accurate(a_mn, b_mn, M, N, K, ks):
     tc.gemm(Ast, Bst, out1, None, M, N, K, Ast.shape[1], Bst.shape[1], N, a_mn, b_mn, False, ks, x3=False)
     e1 = _rel_err(out1, ref)
     fp32 = _rel_err(A @ B.t(), ref)      # what cuBLAS fp32 gives
-    assert e3 < 2e-6 and e3 < e1 / 50, (e3, e1, fp32)
+    assert e3 < 1e-5 and e3 < e1 / 50, (e3, e1, fp32)
 
 
 def test_gemm_splitk_bias_relu_bf16_out():
@@ -63,8 +63,12 @@ def test_gemm_splitk_bias_relu_bf16_out():
     ref = A.double() @ B.double().t() + bias.double()
     for ks in (1, 4, 144):
         out = torch.zeros(M, N, device=DEV)
-        tc.gemm(A, B, out, bias, M, N, K, K, K, N, 0, 0, False, ks)
+        tc.gemm(A, B, out, bias, M, N, K, K, K, N, 0, 0, False, ks, x3=False)
         assert _rel_err(out, ref) < 2e-3, ks
+        if ks > 1:   # the same split through scratch + reduce (no atomics, nothing to pre-zero)
+            out2 = torch.full((M, N), float("nan"), device=DEV)
+            tc.gemm_splitk(A, B, out2, bias, M, N, K, K, K, N, 0, 0, ks, x3=False)
+            assert _rel_err(out2, ref) < 2e-3, ks
     out = torch.empty(M, N, device=DEV)
     tc.gemm(A, B, out, bias, M, N, K, K, K, N, 0, 0, True, 1)
     assert _rel_err(out, ref.clamp(min=0)) < 2e-3
