@@ -29,11 +29,12 @@ struct FlatConvParams {
   float* out; const float* bias; const float* mask;
   int tiles;
   int use_base_offset;
+  long long* dbg;         // optional: per-CTA clock64 trace (CTA 0 only), see scratch/dbg_flat_trace.py
 };
 
 namespace {
 using namespace tc;
-constexpr int kBM = 128, kThreads = 192, kTmem = 128;
+constexpr int kBM = 128, kThreads = 320, kTmem = 128;   // warps: 0 TMA, 1 MMA, 2-9 epilogue (4 lane groups x 2 column chunks)
 
 __device__ __forceinline__ uint64_t desc_k128(uint32_t addr, int use_base_offset) {
   // K-major, 128-byte swizzle, SBO = 1024 B; optional base_offset = row phase of the start address inside its 1024-B atom
@@ -47,13 +48,14 @@ struct __align__(16) Bars {
   uint32_t tmem_base;
   uint32_t adelta[72], wdelta[72];     // per-MMA start-address increments (16-byte units) of the A / W descriptors
   alignas(16) float bias[64];
-  alignas(16) float stage_out[4][32][36];          // per-epilogue-warp transpose buffer: coalesced 128-byte row stores
+  alignas(16) float stage_out[8][32][36];          // per-epilogue-warp transpose buffer: coalesced 128-byte row stores
 };
 
+template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
 k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_w, const FlatConvParams p, int stages, int halo_rows) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   const int cch = p.Cin / 32;
   const int w_bytes = p.taps * cch * p.Cout * 128;          // all taps resident
   const int chunk_bytes = halo_rows * 128;                   // one channel chunk of a haloed tile (multiple of 1024)
@@ -61,14 +63,14 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   uint8_t* w_smem = smem;
   uint8_t* a_smem = smem + ((w_bytes + 1023) & ~1023);
   Bars* bars = reinterpret_cast<Bars*>(a_smem + stages * stage_bytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
 
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_in); tma_prefetch_desc(&map_w); }
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(&bars->w_full, 1);
       for (int i = 0; i < 4; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
-      for (int i = 0; i < 2; ++i) { mbar_init(&bars->acc_full[i], 1); mbar_init(&bars->acc_empty[i], 4); }
+      for (int i = 0; i < 2; ++i) { mbar_init(&bars->acc_full[i], 1); mbar_init(&bars->acc_empty[i], 4 * (p.Cout / 32)); }
       mbar_fence_init();
     }
     __syncwarp();
@@ -86,6 +88,8 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *((volatile uint32_t*)&bars->tmem_base);
+  long long* dbg = (p.dbg && blockIdx.x == 0) ? p.dbg : nullptr;
+  if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   const int my_tiles = (p.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
@@ -102,80 +106,107 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       for (int cc = 0; cc < cch; ++cc)
         tma_load_2d(a_smem + st * stage_bytes + cc * chunk_bytes, &map_in, &bars->full[st], cc * 32, (int)(p0 + p.min_off));
     }
-  } else if (warp == 1 && lane == 0) {
-    // ---- MMA issuer ----
+  } else if (warp == 1) {
+    // ---- MMA issuer: the whole warp runs the (uniform) loop, one elected lane issues ----
     const uint32_t idesc = make_idesc(true, false, false, kBM, p.Cout);
+    const uint32_t w0 = smem_u32(w_smem);
     mbar_wait(&bars->w_full, 0);
+    if (dbg && lane == 0) dbg[1] = clock64();
     for (int i = 0; i < my_tiles; ++i) {
       const int st = i % stages, ph = (i / stages) & 1;
       const int ab = i & 1, aph = (i >> 1) & 1;
       mbar_wait(&bars->acc_empty[ab], aph ^ 1);     // epilogue drained this accumulator
+      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 0] = clock64();
       mbar_wait(&bars->full[st], ph);
+      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 1] = clock64();
       tc_fence_after();
-      const uint64_t a_base = desc_k128(smem_u32(a_smem + st * stage_bytes), 0), w_base = desc_k128(smem_u32(w_smem), 0);
+      const uint32_t a0 = smem_u32(a_smem + st * stage_bytes);
       const uint32_t tacc = tmem + ab * p.Cout;
-      const int nmma = p.taps * cch * 4;
-      // the start-address field (16-byte units, < 2^14) is the only part of the descriptor that changes
-      umma<true>(tacc, a_base + bars->adelta[0], w_base + bars->wdelta[0], idesc, 0);
-#pragma unroll 4
-      for (int m = 1; m < nmma; ++m) umma<true>(tacc, a_base + bars->adelta[m], w_base + bars->wdelta[m], idesc, 1);
-      umma_commit(&bars->empty[st]);
-      umma_commit(&bars->acc_full[ab]);
+      if (elect_one()) {
+        // descriptor = constant high word | (address >> 4): everything below is computed from kernel parameters
+        constexpr uint64_t kDescHi = ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+        uint32_t acc = 0;
+        for (int t = 0; t < p.taps; ++t) {
+          const uint32_t arow = a0 + (uint32_t)(p.off[t] - p.min_off) * 128;
+          for (int cc = 0; cc < cch; ++cc) {
+            const uint32_t aa = arow + cc * chunk_bytes, wa = w0 + (t * cch + cc) * (p.Cout * 128);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              umma<true>(tacc, kDescHi | (uint64_t)(((aa + j * 32) >> 4) & 0x3FFF), kDescHi | (uint64_t)(((wa + j * 32) >> 4) & 0x3FFF), idesc, acc);
+              acc = 1;
+            }
+          }
+        }
+        umma_commit(&bars->empty[st]);
+        umma_commit(&bars->acc_full[ab]);
+      }
+      __syncwarp();
+      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 2] = clock64();
     }
-  } else if (warp >= 2) {
-    // ---- epilogue ----
-    const int lg = warp & 3, row = lg * 32 + lane;
+  } else if (warp >= 2 && (warp - 2) / 4 < p.Cout / 32) {
+    // ---- epilogue: warp = (lane group lg, 32-column chunk) ----
+    const int lg = warp & 3, row = lg * 32 + lane, c0 = ((warp - 2) >> 2) * 32;
+    float (*so)[36] = bars->stage_out[warp - 2];
+    float4 bias4[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) bias4[j] = *reinterpret_cast<const float4*>(&bars->bias[c0 + 4 * j]);
     for (int i = 0; i < my_tiles; ++i) {
       const int ab = i & 1, aph = (i >> 1) & 1;
-      const long pp = (long)(blockIdx.x + (long)i * gridDim.x) * kBM + row;
+      const long tile0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM;
+      float vm = 1.f;
+      if (kMode == 0) {
+        const int q = (int)((tile0 + row) % p.HW);
+        vm = ((q / p.W) < p.Hv && (q % p.W) < p.Wv) ? 1.f : 0.f;
+      }
       mbar_wait(&bars->acc_full[ab], aph);
+      if (dbg && i < 8 && warp == 2 && lane == 0) dbg[8 + i * 8 + 3] = clock64();
       tc_fence_after();
-      bool valid = true;
-      if (p.mode == 0) {
-        const int q = (int)(pp % p.HW);
-        valid = (q / p.W) < p.Hv && (q % p.W) < p.Wv;
-      }
-      float (*so)[36] = bars->stage_out[warp - 2];
-      const long tile_row0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM + lg * 32;   // first row this warp owns
-      for (int c0 = 0; c0 < p.Cout; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * p.Cout + c0, r);
-        tmem_ld_wait();
-        // lane = row: bias / ReLU / validity here, then transpose through shared memory
-#pragma unroll
-        for (int j = 0; j < 32; j += 4) {
-          float4 v = make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-          if (p.mode == 0) {
-            const float4 b = *reinterpret_cast<const float4*>(&bars->bias[c0 + j]);
-            v.x = valid ? fmaxf(v.x + b.x, 0.f) : 0.f; v.y = valid ? fmaxf(v.y + b.y, 0.f) : 0.f;
-            v.z = valid ? fmaxf(v.z + b.z, 0.f) : 0.f; v.w = valid ? fmaxf(v.w + b.w, 0.f) : 0.f;
-          }
-          *reinterpret_cast<float4*>(&so[lane][j]) = v;
-        }
-        __syncwarp();
-        // 8 lanes cover one 128-byte output row, 4 rows per instruction: fully coalesced stores (and mask loads)
-#pragma unroll
-        for (int it = 0; it < 8; ++it) {
-          const int rr = it * 4 + (lane >> 3), c4 = (lane & 7) * 4;
-          const long prow = tile_row0 + rr;
-          if (prow < p.P) {
-            float4 v = *reinterpret_cast<const float4*>(&so[rr][c4]);
-            if (p.mode == 1) {
-              const float4 mk = *reinterpret_cast<const float4*>(p.mask + prow * p.Cout + c0 + c4);
-              v.x = mk.x > 0.f ? v.x : 0.f; v.y = mk.y > 0.f ? v.y : 0.f; v.z = mk.z > 0.f ? v.z : 0.f; v.w = mk.w > 0.f ? v.w : 0.f;
-            }
-            *reinterpret_cast<float4*>(p.out + prow * p.Cout + c0 + c4) = v;
-          }
-        }
-        __syncwarp();
-      }
+      uint32_t r[32];
+      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * p.Cout + c0, r);
+      tmem_ld_wait();
+      // the accumulator is in registers: hand the TMEM buffer back before the (long) store phase
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&bars->acc_empty[ab]);   // 4 epilogue warps -> count 4
+      if (lane == 0) mbar_arrive(&bars->acc_empty[ab]);
+      if (dbg && i < 8 && warp == 2 && lane == 0) dbg[8 + i * 8 + 5] = clock64();
+      // lane = row: bias / ReLU / validity, then transpose through shared memory
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        if (kMode == 0) {
+          v.x = fmaxf(v.x + bias4[j].x, 0.f) * vm; v.y = fmaxf(v.y + bias4[j].y, 0.f) * vm;
+          v.z = fmaxf(v.z + bias4[j].z, 0.f) * vm; v.w = fmaxf(v.w + bias4[j].w, 0.f) * vm;
+        }
+        *reinterpret_cast<float4*>(&so[lane][4 * j]) = v;
+      }
+      __syncwarp();
+      if (dbg && i < 8 && warp == 2 && lane == 0) dbg[8 + i * 8 + 6] = clock64();
+      // 8 lanes cover one 128-byte output row, 4 rows per instruction: coalesced stores (and mask loads)
+      const long row0 = tile0 + lg * 32;
+      const int c4 = (lane & 7) * 4, rsub = lane >> 3;
+      float4 mk[8];
+      if (kMode == 1) {
+#pragma unroll
+        for (int it = 0; it < 8; ++it) {
+          const long prow = row0 + it * 4 + rsub;
+          mk[it] = prow < p.P ? *reinterpret_cast<const float4*>(p.mask + prow * p.Cout + c0 + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rr = it * 4 + rsub;
+        const long prow = row0 + rr;
+        float4 v = *reinterpret_cast<const float4*>(&so[rr][c4]);
+        if (kMode == 1) { v.x = mk[it].x > 0.f ? v.x : 0.f; v.y = mk[it].y > 0.f ? v.y : 0.f; v.z = mk[it].z > 0.f ? v.z : 0.f; v.w = mk[it].w > 0.f ? v.w : 0.f; }
+        if (prow < p.P) *reinterpret_cast<float4*>(p.out + prow * p.Cout + c0 + c4) = v;
+      }
+      __syncwarp();
+      if (dbg && i < 8 && warp == 2 && lane == 0) { dbg[8 + i * 8 + 7] = clock64(); dbg[8 + i * 8 + 4] = clock64(); }
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (dbg && threadIdx.x == 0) dbg[2] = clock64();
   if (warp == 1) tmem_dealloc<kTmem>(tmem);
 }
 
@@ -216,24 +247,30 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   p.min_off = mn; p.span = mx - mn;
   p.tiles = (int)((P + kBM - 1) / kBM);
   { const char* e = getenv("DCP_FLAT_BASEOFF"); p.use_base_offset = e ? atoi(e) : 0; }
+  { const char* e = getenv("DCP_FLAT_DBG_PTR"); p.dbg = e ? (long long*)strtoull(e, nullptr, 0) : nullptr; }
   const int halo_rows = (kBM + p.span + 7) / 8 * 8;
   if (halo_rows > 256) { dcp_set_error("flat conv: halo of %d rows exceeds one TMA box", halo_rows); return -1; }
   const int cch = Cin / 32;
   const int w_bytes = ((taps * cch * Cout * 128) + 1023) & ~1023;
   const int stage_bytes = cch * halo_rows * 128;
   int stages = 4;
-  const int budget = 200 * 1024;
+  const int budget = 222 * 1024;
   while (stages > 1 && w_bytes + stages * stage_bytes + (int)sizeof(Bars) + 1024 > budget) --stages;
   const size_t smem = (size_t)w_bytes + (size_t)stages * stage_bytes + sizeof(Bars) + 1024;
   if (smem > (size_t)budget) { dcp_set_error("flat conv: needs %zu bytes of shared memory", smem); return -1; }
   static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat, cudaFuncAttributeMaxDynamicSharedMemorySize, budget)); attr = true; }
+  if (!attr) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
+    attr = true;
+  }
   CUtensorMap mi, mw;
   if (map2d(&mi, in, P, Cin, 32, halo_rows)) return -1;
   if (map2d(&mw, wmat, Cout, (long)taps * Cin, 32, Cout)) return -1;
   if (num_ctas <= 0) num_ctas = 148;
   if (num_ctas > p.tiles) num_ctas = p.tiles;
-  k_conv_flat<<<num_ctas, kThreads, smem, s>>>(mi, mw, p, stages, halo_rows);
+  if (mode == 0) k_conv_flat<0><<<num_ctas, kThreads, smem, s>>>(mi, mw, p, stages, halo_rows);
+  else k_conv_flat<1><<<num_ctas, kThreads, smem, s>>>(mi, mw, p, stages, halo_rows);
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -49,14 +49,14 @@ __global__ void __launch_bounds__(kThreads, 1)
 k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const TcGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment is required by the 128-byte swizzle atoms
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = align_smem_1024(smem_raw);
   const int b_bytes = p.b_bytes;
   const int a_bytes = p.a_bytes;
   const int half_bytes = a_bytes + b_bytes;                 // [A][B]; in x3 mode followed by [A_lo][B_lo]
   const int stage_bytes = p.x3 ? 2 * half_bytes : half_bytes;
   const int nstages = p.stages;
   Pipe* pipe = reinterpret_cast<Pipe*>(smem + nstages * stage_bytes);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
   constexpr int kElem = kTF32 ? 4 : 2;
   constexpr int kBK = 128 / kElem;             // elements per K slab
   constexpr int kUmmaK = 32 / kElem;           // elements per MMA
@@ -140,14 +140,15 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
             tma_load_2d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, kb);
         }
       }
-    } else if (warp == 1 && lane == 0) {
-      // ================= MMA issuer =================
+    } else if (warp == 1) {
+      // ================= MMA issuer (uniform loop, one elected lane issues) =================
       const uint32_t idesc = make_idesc(kTF32, p.a_mn != 0, p.b_mn != 0, kBM, p.BN);
       for (int i = 0; i < nst; ++i) {
         const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(p.x3 ? &pipe->split[st] : &pipe->full[st], ph);
         tc_fence_after();
         const uint32_t sa0 = smem_u32(smem + st * stage_bytes), sb = sa0 + a_bytes;
+        if (elect_one()) {
         // descriptors: only the start-address field (16-byte units) moves between k-steps, so build one base per
         // operand and stage and add the step (MN-major: k-rows are 128 B apart; tf32 needs the BASE32B layout)
         constexpr uint32_t kMnSbo = kTF32 ? 512 : 1024, kMnLayout = kTF32 ? 1 : 2;
@@ -169,8 +170,10 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           }
         }
         umma_commit(&pipe->empty[st]);   // smem slot reusable once these MMAs retire
+        if (i == nst - 1) umma_commit(&pipe->acc_full);      // accumulator complete
+        }
+        __syncwarp();
       }
-      umma_commit(&pipe->acc_full);      // accumulator complete
     }
   }
   if (warp >= 2) {

@@ -8,6 +8,17 @@
 namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+// Warp index the compiler can prove warp-uniform (keeps role dispatch and descriptor math on the uniform datapath).
+__device__ __forceinline__ int warp_idx_uniform() { return __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0); }
+// One elected lane of a fully active warp (elect.sync): the single-thread issue idiom for TMA / tcgen05.mma.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n.reg .pred p;\nelect.sync _|p, 0xffffffff;\nselp.u32 %0, 1, 0, p;\n}\n" : "=r"(pred));
+  return pred != 0;
+}
+// 1024-byte aligned view of the dynamic shared memory that keeps the shared address space visible to the compiler
+// (pointer + offset, no integer round trip), so accesses compile to LDS/STS instead of generic LD/ST.
+__device__ __forceinline__ uint8_t* align_smem_1024(uint8_t* raw) { return raw + ((1024u - (smem_u32(raw) & 1023u)) & 1023u); }
 
 // ---- mbarrier -------------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
