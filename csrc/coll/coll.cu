@@ -170,6 +170,19 @@ __device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nb
   const uintptr_t mis = reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src);
   const bool al16 = (mis & 15) == 0, al4 = (mis & 3) == 0;
   const size_t nchunk = (nbytes + 15) / 16;
+  if (al16) {
+    // bulk: 4 independent 16-byte loads in flight per thread (same chunk -> thread mapping as the generic loop)
+    const size_t nfull = nbytes / 16;
+    size_t c = tid;
+    for (; c + 3 * stride < nfull; c += 4 * stride) {
+      uint4 x0 = ld16(src + c * 16), x1 = ld16(src + (c + stride) * 16), x2 = ld16(src + (c + 2 * stride) * 16), x3 = ld16(src + (c + 3 * stride) * 16);
+      if (stream_store) { st16_stream(dst + c * 16, x0); st16_stream(dst + (c + stride) * 16, x1); st16_stream(dst + (c + 2 * stride) * 16, x2); st16_stream(dst + (c + 3 * stride) * 16, x3); }
+      else { st16(dst + c * 16, x0); st16(dst + (c + stride) * 16, x1); st16(dst + (c + 2 * stride) * 16, x2); st16(dst + (c + 3 * stride) * 16, x3); }
+    }
+    for (; c < nfull; c += stride) { uint4 x = ld16(src + c * 16); if (stream_store) st16_stream(dst + c * 16, x); else st16(dst + c * 16, x); }
+    if (nfull < nchunk && (nfull % stride) == tid) for (size_t j = nfull * 16; j < nbytes; ++j) dst[j] = src[j];
+    return;
+  }
   for (size_t c = tid; c < nchunk; c += stride) {
     const size_t b = c * 16;
     const size_t len = nbytes - b < 16 ? nbytes - b : 16;
@@ -184,6 +197,21 @@ __device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nb
   }
 }
 
+// One multimem.st per 16 bytes reaches every rank's copy of heap offset `off` (NVSwitch replicates the store);
+// the < 16-byte tail goes point to point.  Same chunk -> thread mapping as copy_bytes.
+__device__ __forceinline__ void push_all_nvls(const DcpDevCtx& c, size_t off, const char* src, size_t nbytes, size_t tid, size_t stride) {
+  const size_t nfull = nbytes / 16;
+  const bool al = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
+  for (size_t v = tid; v < nfull; v += stride) {
+    uint4 x;
+    if (al) x = ld16(src + v * 16);
+    else { unsigned char* b = reinterpret_cast<unsigned char*>(&x); for (int j = 0; j < 16; ++j) b[j] = (unsigned char)src[v * 16 + j]; }
+    multimem_st16(c.mc + off + v * 16, x);
+  }
+  if ((nfull % stride) == tid)
+    for (size_t j = nfull * 16; j < nbytes; ++j) { const char x = src[j]; for (int p = 0; p < c.world; ++p) c.peer[p][off + j] = x; }
+}
+
 // Rank `root` pushes nbytes to every rank's buffer at `off` (+ parity half when staged), everyone
 // copies out.  sym: buffer is the user's symmetric tensor (in place on root, leading barrier needed).
 __global__ void __launch_bounds__(kThreads) k_broadcast(DcpDevCtx c, char* __restrict__ data, size_t off, size_t half_bytes, size_t nbytes,
@@ -193,8 +221,8 @@ __global__ void __launch_bounds__(kThreads) k_broadcast(DcpDevCtx c, char* __res
   else dcp_barrier(c, chan);  // peers may still be reading their copy of the tensor
   if (c.rank == root) {
     const char* src = sym ? c.peer[root] + off : data;
-    if (c.nvls && !sym && (nbytes % 16 == 0) && ((reinterpret_cast<uintptr_t>(src) & 15) == 0)) {
-      for (size_t v = tid; v < nbytes / 16; v += stride) multimem_st16(c.mc + off + v * 16, ld16(src + v * 16));
+    if (c.nvls && (off % 16 == 0)) {
+      push_all_nvls(c, off, src, nbytes, tid, stride);   // in place on the root for a symmetric tensor: rewrites its own bytes with the same values
     } else {
       for (int p = 0; p < c.world; ++p) {
         if (sym && p == root) continue;
@@ -218,9 +246,13 @@ __global__ void __launch_bounds__(kThreads) k_allgather(DcpDevCtx c, const char*
   if (!sym) off += (size_t)call_parity(c, chan) * half_bytes;
   else dcp_barrier(c, chan);
   const size_t my = off + (size_t)c.rank * slot_stride;
-  for (int p = 0; p < c.world; ++p) {
-    if (root >= 0 && p != root) continue;
-    copy_bytes(c.peer[p] + my, in, nbytes, tid, stride, true);
+  if (c.nvls && root < 0 && (my % 16 == 0)) {
+    push_all_nvls(c, my, in, nbytes, tid, stride);        // one store per 16 bytes instead of W: egress drops W-fold
+  } else {
+    for (int p = 0; p < c.world; ++p) {
+      if (root >= 0 && p != root) continue;
+      copy_bytes(c.peer[p] + my, in, nbytes, tid, stride, true);
+    }
   }
   dcp_barrier(c, chan);
   if (!sym) {
@@ -267,7 +299,18 @@ __global__ void __launch_bounds__(kThreads) k_reduce_scatter(DcpDevCtx c, const 
     const size_t soff = off + first * sizeof(T);
     const bool al = ((soff | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
     const size_t nvec = al ? n_out / V : 0;
-    for (size_t v = tid; v < nvec; v += stride) {
+    bool done_nvls = false;
+    if constexpr (NvlsOk<T>::value) {
+      if (c.nvls && (op == DCP_SUM || op == DCP_AVG) && nvec > 0) {
+        for (size_t v = tid; v < nvec; v += stride) {
+          uint4 r = multimem_ld_reduce_add<T>(c.mc + soff + v * 16);      // in-switch reduction of the W copies
+          if (op == DCP_AVG) r = vec_scale<T>(r, scale);
+          st16(out + v * V, r);
+        }
+        done_nvls = true;
+      }
+    }
+    for (size_t v = done_nvls ? nvec : tid; v < nvec; v += stride) {
       Acc acc[V]; Vec<T> x;
       uint4 raw[DCP_MAX_RANKS];
 #pragma unroll
@@ -307,10 +350,11 @@ __global__ void __launch_bounds__(kThreads) k_send(DcpDevCtx c, const char* __re
   const int b = blockIdx.x;
   volatile uint32_t* seqp = p2p_word(me, DcpHeapLayout::kSendSeqOff, dst, b);
   const uint32_t seq = *seqp + 1;
-  // the slot is free once the receiver acknowledged the previous message
-  if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PAckOff, dst, b), seq - 1);
+  // two half-slots per (source, destination): message seq uses half (seq & 1), which is free once the receiver
+  // acknowledged message seq - 2 - so a stream of chunks pipelines instead of ping-ponging on acks
+  if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PAckOff, dst, b), seq - 2);
   __syncthreads();
-  char* slot = c.peer[dst] + c.p2p_slot_off + (size_t)c.rank * c.p2p_slot_bytes;
+  char* slot = c.peer[dst] + c.p2p_slot_off + (size_t)c.rank * c.p2p_slot_bytes + (size_t)(seq & 1) * (c.p2p_slot_bytes / 2);
   // contiguous share per block so that flags cover disjoint ranges
   size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
   size_t lo = per * b; if (lo > nbytes) lo = nbytes;
@@ -331,7 +375,7 @@ __global__ void __launch_bounds__(kThreads) k_recv(DcpDevCtx c, char* __restrict
   const uint32_t seq = *seqp + 1;
   if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PFlagOff, src, b), seq);
   __syncthreads();
-  const char* slot = me + c.p2p_slot_off + (size_t)src * c.p2p_slot_bytes;
+  const char* slot = me + c.p2p_slot_off + (size_t)src * c.p2p_slot_bytes + (size_t)(seq & 1) * (c.p2p_slot_bytes / 2);
   size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
   size_t lo = per * b; if (lo > nbytes) lo = nbytes;
   size_t hi = lo + per; if (hi > nbytes) hi = nbytes;
@@ -508,8 +552,9 @@ int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dty
 
 int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t stream) {
   const DcpDevCtx& c = *dcp_symm_ctx(h);
-  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += c.p2p_slot_bytes) {
-    size_t m = nbytes - done < c.p2p_slot_bytes ? nbytes - done : c.p2p_slot_bytes;
+  const size_t half = c.p2p_slot_bytes / 2;
+  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += half) {
+    size_t m = nbytes - done < half ? nbytes - done : half;
     k_send<<<DCP_P2P_BLOCKS, kThreads, 0, stream>>>(c, (const char*)in + done, m, dst);
     if (nbytes == 0) break;
   }
@@ -519,8 +564,9 @@ int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t strea
 
 int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream) {
   const DcpDevCtx& c = *dcp_symm_ctx(h);
-  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += c.p2p_slot_bytes) {
-    size_t m = nbytes - done < c.p2p_slot_bytes ? nbytes - done : c.p2p_slot_bytes;
+  const size_t half = c.p2p_slot_bytes / 2;
+  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += half) {
+    size_t m = nbytes - done < half ? nbytes - done : half;
     k_recv<<<DCP_P2P_BLOCKS, kThreads, 0, stream>>>(c, (char*)out + done, m, src);
     if (nbytes == 0) break;
   }

@@ -87,8 +87,12 @@ template <> struct NvlsOk<__half> { static constexpr bool value = true; };
 
 // scale a 16-byte vector of T in fp32
 template <typename T> __device__ __forceinline__ uint4 vec_scale(uint4 raw, float s) {
-  Vec<T> v; v.u = raw;
+  if constexpr (ElemTraits<T>::kFloat) {
+    Vec<T> v; v.u = raw;
 #pragma unroll
-  for (int i = 0; i < Vec<T>::N; ++i) v.e[i] = ElemTraits<T>::down(ElemTraits<T>::up(v.e[i]) * (typename ElemTraits<T>::Acc)s);
-  return v.u;
+    for (int i = 0; i < Vec<T>::N; ++i) v.e[i] = ElemTraits<T>::down(ElemTraits<T>::up(v.e[i]) * (typename ElemTraits<T>::Acc)s);
+    return v.u;
+  } else {
+    return raw;
+  }
 }

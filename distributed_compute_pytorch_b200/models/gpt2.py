@@ -22,14 +22,21 @@ class GPT2Config:
     n_layer: int = 12
     n_head: int = 12
 
+    @property
+    def padded_vocab(self) -> int:
+        """Vocabulary rounded up to a multiple of 128 so the LM-head GEMMs tile on tensor cores; the extra logits are
+        never targets (124,439,808 parameters are counted on the unpadded 50257 x 768 embedding)."""
+        return -(-self.vocab_size // 128) * 128
+
 
 class Block(nn.Module):
     def __init__(self, cfg: GPT2Config):
         super().__init__()
-        self.ln_1 = nn.LayerNorm(cfg.n_embd)
+        self.ln_1 = ops.LayerNorm(cfg.n_embd)
         self.attn_qkv = ops.Linear(cfg.n_embd, 3 * cfg.n_embd)
         self.attn_proj = ops.Linear(cfg.n_embd, cfg.n_embd)
-        self.ln_2 = nn.LayerNorm(cfg.n_embd)
+        self.ln_2 = ops.LayerNorm(cfg.n_embd)
+        self.act = ops.GELU()
         self.mlp_fc = ops.Linear(cfg.n_embd, 4 * cfg.n_embd)
         self.mlp_proj = ops.Linear(4 * cfg.n_embd, cfg.n_embd)
         self.n_head = cfg.n_head
@@ -41,7 +48,7 @@ class Block(nn.Module):
         y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
         y = y.transpose(1, 2).reshape(B * T, C)
         x = x + self.attn_proj(y).view(B, T, C)
-        h = F.gelu(self.mlp_fc(self.ln_2(x).view(B * T, C)), approximate="tanh")
+        h = self.act(self.mlp_fc(self.ln_2(x).view(B * T, C)))
         return x + self.mlp_proj(h).view(B, T, C)
 
 
@@ -49,10 +56,11 @@ class GPT2(nn.Module):
     def __init__(self, cfg: GPT2Config = GPT2Config()):
         super().__init__()
         self.cfg = cfg
-        self.wte = nn.Embedding(cfg.vocab_size, cfg.n_embd)
+        self.wte = nn.Embedding(cfg.padded_vocab, cfg.n_embd)
         self.wpe = nn.Embedding(cfg.n_positions, cfg.n_embd)
         self.h = nn.ModuleList(Block(cfg) for _ in range(cfg.n_layer))
-        self.ln_f = nn.LayerNorm(cfg.n_embd)
+        self.ln_f = ops.LayerNorm(cfg.n_embd)
+        self.compute_dtype = None   # torch.bfloat16: bf16 activations / GEMMs with fp32 master weights
         self.apply(self._init)
         for n, p in self.named_parameters():
             if n.endswith("proj.weight"):
@@ -69,6 +77,8 @@ class GPT2(nn.Module):
         B, T = idx.shape
         pos = torch.arange(T, device=idx.device)
         x = self.wte(idx) + self.wpe(pos)
+        if self.compute_dtype is not None:
+            x = x.to(self.compute_dtype)
         for blk in self.h:
             x = blk(x)
         x = self.ln_f(x)

@@ -71,6 +71,7 @@ class ResNet(nn.Module):
     def __init__(self, block: Type[nn.Module], layers: List[int], num_classes: int = 1000, sync_bn: bool = False):
         super().__init__()
         self.inplanes, self.sync_bn = 64, sync_bn
+        self.compute_dtype = None   # torch.bfloat16: bf16 activations / convs with fp32 master weights and fp32 BN parameters
         self.conv1 = ops.Conv2d(3, 64, 7, 2, 3, bias=False)
         self.bn1 = _bn(64, True, sync_bn)
         self.maxpool = ops.MaxPool2d(3, 2, 1)
@@ -94,6 +95,8 @@ class ResNet(nn.Module):
         return nn.Sequential(*blocks)
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if self.compute_dtype is not None:
+            x = x.to(self.compute_dtype)
         x = x.contiguous(memory_format=torch.channels_last)
         x = self.maxpool(self.bn1(self.conv1(x)))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))

@@ -58,6 +58,9 @@ def lib():
             "dcp_linear_wgrad_simt": [vp, vp, vp, vp, i, i, i, i, vp],
             "dcp_colsum": [vp, vp, l, i, i, vp], "dcp_cast_from_f32": [vp, vp, l, i, vp],
             "dcp_counter_advance": [vp, vp],
+            "dcp_layernorm_fwd": [vp, vp, vp, vp, vp, vp, i, i, f, i, vp],
+            "dcp_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
+            "dcp_gelu_fwd": [vp, vp, l, i, vp], "dcp_gelu_bwd": [vp, vp, vp, l, i, vp],
             "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
             "dcp_convnet_conv1_fwd": [vp, vp, vp, vp, i, vp],
             "dcp_convnet_pool_fwd": [vp, vp, vp, i, f, ull, ull, vp, i, vp],
@@ -424,6 +427,10 @@ class _Conv2d(Function):
         from . import tc
         x = _nhwc(x)
         w = _nhwc(w)
+        ctx.w_dtype = w.dtype
+        if w.dtype != x.dtype:      # fp32 master weights, bf16 compute (autocast-style): cast per call, grads come back fp32
+            w = _cast(w, x.dtype) if w.dtype == torch.float32 else w.to(x.dtype)
+            b = None if b is None else (_cast(b, x.dtype) if b.dtype == torch.float32 else b.to(x.dtype))
         p = _convp(x.shape, w.shape, stride, pad)
         y = torch.empty((p.N, p.K, p.Ho, p.Wo), dtype=x.dtype, device=x.device, memory_format=CL)
         if USE_TC and tc.conv_fwd_supported(p, x.dtype):
@@ -458,9 +465,9 @@ class _Conv2d(Function):
                 tc.conv2d_wgrad(dy, x, dw32, db32, p)
             else:
                 _chk(lib().dcp_conv2d_wgrad_simt(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), _p(db32), p, _dt(x), _stream()))
-            dw = dw32 if w.dtype == torch.float32 else _cast(dw32, w.dtype)
+            dw = dw32 if ctx.w_dtype == torch.float32 else _cast(dw32, ctx.w_dtype)
             if has_b:
-                db = db32 if w.dtype == torch.float32 else _cast(db32, w.dtype)
+                db = db32 if ctx.w_dtype == torch.float32 else _cast(db32, ctx.w_dtype)
         return dx, dw, db, None, None, None
 
 
@@ -484,6 +491,10 @@ class _Linear(Function):
         x2 = x.reshape(-1, shape[-1])
         x2 = x2 if x2.is_contiguous() else x2.contiguous()
         w = w if w.is_contiguous() else w.contiguous()
+        ctx.w_dtype = w.dtype
+        if w.dtype != x2.dtype:     # fp32 master weights, bf16 compute
+            w = _cast(w, x2.dtype) if w.dtype == torch.float32 else w.to(x2.dtype)
+            b = None if b is None else (_cast(b, x2.dtype) if b.dtype == torch.float32 else b.to(x2.dtype))
         M, K = x2.shape
         N = w.shape[0]
         y = torch.empty((M, N), dtype=x.dtype, device=x.device)
@@ -523,14 +534,71 @@ class _Linear(Function):
                 tc.linear_wgrad(dy, x2, dw32, db32)
             else:
                 _chk(lib().dcp_linear_wgrad_simt(dy.data_ptr(), x2.data_ptr(), dw32.data_ptr(), _p(db32), M, N, K, _dt(x2), _stream()))
-            dw = dw32 if w.dtype == torch.float32 else _cast(dw32, w.dtype)
+            dw = dw32 if ctx.w_dtype == torch.float32 else _cast(dw32, ctx.w_dtype)
             if has_b:
-                db = db32 if w.dtype == torch.float32 else _cast(db32, w.dtype)
+                db = db32 if ctx.w_dtype == torch.float32 else _cast(db32, ctx.w_dtype)
         return dx, dw, db, None
 
 
 def linear(x, w, b, relu: bool = False):
     return _Linear.apply(x, w, b, bool(relu))
+
+
+# ------------------------------------------------------------------------------------ transformer --
+class _LayerNorm(Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, eps):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        rows, Cc = x2.shape
+        y = torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        _chk(lib().dcp_layernorm_fwd(x2.data_ptr(), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(), rstd.data_ptr(), rows, Cc,
+                                     float(eps), _dt(x2), _stream()))
+        ctx.save_for_backward(x2, gamma, mean, rstd)
+        ctx.shape = shape
+        return y.view(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, gamma, mean, rstd = ctx.saved_tensors
+        rows, Cc = x2.shape
+        dy = dy.reshape(rows, Cc)
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        dx = torch.empty_like(x2)
+        dg = torch.empty(Cc, dtype=torch.float32, device=x2.device)
+        db = torch.empty(Cc, dtype=torch.float32, device=x2.device)
+        _chk(lib().dcp_layernorm_bwd(x2.data_ptr(), dy.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(), dg.data_ptr(),
+                                     db.data_ptr(), rows, Cc, _dt(x2), _stream()))
+        return dx.view(ctx.shape), dg, db, None
+
+
+def layer_norm(x, gamma, beta, eps: float = 1e-5):
+    return _LayerNorm.apply(x, gamma, beta, eps)
+
+
+class _GELU(Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = x if x.is_contiguous() else x.contiguous()
+        y = torch.empty_like(x)
+        _chk(lib().dcp_gelu_fwd(x.data_ptr(), y.data_ptr(), x.numel(), _dt(x), _stream()))
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        dx = torch.empty_like(x)
+        _chk(lib().dcp_gelu_bwd(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), _dt(x), _stream()))
+        return dx
+
+
+def gelu(x):
+    return _GELU.apply(x)
 
 
 # -------------------------------------------------------------------------------------- optimizer --

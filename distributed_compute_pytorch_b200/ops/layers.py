@@ -135,6 +135,22 @@ def _sync_bn_cpu(bn: _BatchNorm, x: torch.Tensor) -> torch.Tensor:
     return y
 
 
+class LayerNorm(nn.LayerNorm):
+    """LayerNorm over the last dimension (fp32 parameters, f32/bf16 activations)."""
+
+    def forward(self, x):
+        if x.is_cuda and len(self.normalized_shape) == 1 and self.elementwise_affine and self.bias is not None:
+            return _k().layer_norm(x, self.weight, self.bias, self.eps)
+        return F.layer_norm(x.float(), self.normalized_shape, self.weight, self.bias, self.eps).to(x.dtype)
+
+
+class GELU(nn.Module):
+    """tanh-approximated GELU (the GPT-2 activation)."""
+
+    def forward(self, x):
+        return _k().gelu(x) if x.is_cuda else F.gelu(x, approximate="tanh")
+
+
 class ReLU(nn.Module):
     def forward(self, x):
         return _k().relu(x) if x.is_cuda else F.relu(x)

@@ -7,7 +7,7 @@ This is what stands behind ``dist.all_reduce`` at ref:main.py:65,90,91 and behin
 buckets (ref:main.py:62,122) when the tensors live on a B200.
 
 Algorithm choice for all_reduce (per message size, override with DCP_ALLREDUCE_ALGO=1|2|3):
-  <= DCP_ONESHOT_BYTES (default 2 MiB/(W-1)) one-shot push   (latency floor: 1 NVLink hop + 1 signal)
+  <= DCP_ONESHOT_BYTES (default 512 KiB/(W-1)^2) one-shot push   (latency floor: 1 NVLink hop + 1 signal)
   larger, multicast mapped, f32/bf16/f16   NVLS            (multimem.ld_reduce + multimem.st)
   otherwise                                two-shot P2P    (pull-reduce own slice, push to all)
 Tensors inside the symmetric heap (``empty_symmetric``; DDP buckets) are reduced in place with zero
@@ -50,7 +50,7 @@ class P2PBackend:
         self.timeout = float(os.environ.get("DCP_COLL_TIMEOUT_S", min(timeout, 120.0)))
         heap_mb = int(os.environ.get("DCP_HEAP_MB", "2048"))
         staging_mb = int(os.environ.get("DCP_STAGING_MB", "288"))
-        p2p_slot = int(os.environ.get("DCP_P2P_SLOT_MB", "8")) << 20
+        p2p_slot = int(os.environ.get("DCP_P2P_SLOT_MB", "16")) << 20   # two 8 MiB halves per (src, dst) pair
         mode_env = os.environ.get("DCP_SYMM", "vmm")
         self._torch_dev = torch.device("cuda", self.device)
         with torch.cuda.device(self._torch_dev):
@@ -80,7 +80,8 @@ class P2PBackend:
         self._free: List[Tuple[int, int]] = [(self._user_off, self.heap_bytes - self._user_off)]
         self._live: Dict[int, Tuple[int, int]] = {}
         # one-shot pushes (W-1) full copies per rank, two-shot moves 2(W-1)/W: the crossover shrinks with W
-        default_oneshot = max(64 * 1024, (2 << 20) // max(1, world_size - 1))
+        # measured crossovers (profiles/coll_sweep_*): ~512 KiB at W=2, ~10 KiB at W=8
+        default_oneshot = max(8 * 1024, (512 << 10) // max(1, (world_size - 1) ** 2))
         self.oneshot_max = min(int(os.environ.get("DCP_ONESHOT_BYTES", str(default_oneshot))), self.lib.dcp_coll_oneshot_max_bytes(self._h))
         self.nvls_min = int(os.environ.get("DCP_NVLS_MIN_BYTES", str(256 * 1024)))
         self.comm_stream = torch.cuda.Stream(device=self._torch_dev, priority=-1)
@@ -275,7 +276,7 @@ class P2PBackend:
         nbytes = t.numel() * t.element_size()
         algo = algo or self.pick_allreduce_algo(t, op, nbytes)
         if max_ctas <= 0:
-            max_ctas = 16 if nbytes <= (1 << 20) else (64 if nbytes <= (64 << 20) else 128)
+            max_ctas = 16 if nbytes <= (1 << 20) else (64 if nbytes <= (32 << 20) else 148)
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_all_reduce(self._h, t.data_ptr(), t.numel(), self._code(t), int(op), algo, chan, max_ctas, self._stream(stream))
         self._check(rc, "all_reduce")

@@ -178,6 +178,13 @@ int dcp_optim_advance(float* hp, cudaStream_t s);
 int dcp_optim_step(const void* table, int ntensors, long long max_numel, const float* hp, int kind, int grad_dtype, cudaStream_t s);
 int dcp_counter_advance(void* counter, cudaStream_t s);
 
+/* ---- csrc/ops/transformer.cu ---- */
+int dcp_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, float* mean, float* rstd, int rows, int C, float eps, int dtype, cudaStream_t s);
+// dgamma / dbeta: fp32 [C], zeroed here.
+int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const float* mean, const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int C, int dtype, cudaStream_t s);
+int dcp_gelu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
+int dcp_gelu_bwd(const void* x, const void* dy, void* dx, long n, int dtype, cudaStream_t s);
+
 /* ---- csrc/symm/symm.cu ---- */
 const char* dcp_last_error();
 void dcp_set_error(const char* fmt, ...);
