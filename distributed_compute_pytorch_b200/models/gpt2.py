@@ -82,7 +82,7 @@ class GPT2(nn.Module):
         for blk in self.h:
             x = blk(x)
         x = self.ln_f(x)
-        if x.is_cuda:
+        if ops.layers.use_kernels(x):
             from ..ops import cuda
             logits = cuda.linear(x.view(B * T, -1), self.wte.weight, None, False)
         else:

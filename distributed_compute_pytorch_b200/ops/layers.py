@@ -4,6 +4,7 @@ backward run the hand-written sm_100a kernels (``ops/cuda.py`` -> csrc/ops), the
 plain PyTorch op and only exists for the no-GPU plumbing configuration."""
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -14,6 +15,12 @@ from torch import nn
 def _k():
     from . import cuda
     return cuda
+
+
+def use_kernels(x: torch.Tensor) -> bool:
+    """True when ``x`` should go to the hand-written kernels: a CUDA tensor, unless DCP_FORCE_TORCH_OPS=1 (the
+    stock-PyTorch baseline arm of bench/train_models.py runs the very same module definitions that way)."""
+    return x.is_cuda and os.environ.get("DCP_FORCE_TORCH_OPS") != "1"
 
 
 class Conv2d(nn.Conv2d):
@@ -34,7 +41,7 @@ class Conv2d(nn.Conv2d):
         return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if x.is_cuda:
+        if use_kernels(x):
             return _k().conv2d(x, self.weight, self.bias, self.stride, self.padding, self.fuse_relu)
         y = F.conv2d(x, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
         return F.relu(y) if self.fuse_relu else y
@@ -46,7 +53,7 @@ class Linear(nn.Linear):
         self.fuse_relu = fuse_relu
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if x.is_cuda:
+        if use_kernels(x):
             return _k().linear(x, self.weight, self.bias, self.fuse_relu)
         y = F.linear(x, self.weight, self.bias)
         return F.relu(y) if self.fuse_relu else y
@@ -66,7 +73,7 @@ class _BatchNorm(nn.modules.batchnorm._BatchNorm):
             raise ValueError(f"expected 2D, 3D or 4D input (got {input.dim()}D input)")
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if x.is_cuda and x.dim() in (2, 4):
+        if use_kernels(x) and x.dim() in (2, 4):
             return _k().batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.num_batches_tracked,
                                    self.training or not self.track_running_stats, self.momentum, self.eps, self.fuse_relu,
                                    self._sync)
@@ -139,21 +146,21 @@ class LayerNorm(nn.LayerNorm):
     """LayerNorm over the last dimension (fp32 parameters, f32/bf16 activations)."""
 
     def forward(self, x):
-        if x.is_cuda and len(self.normalized_shape) == 1 and self.elementwise_affine and self.bias is not None:
+        if use_kernels(x) and len(self.normalized_shape) == 1 and self.elementwise_affine and self.bias is not None:
             return _k().layer_norm(x, self.weight, self.bias, self.eps)
-        return F.layer_norm(x.float(), self.normalized_shape, self.weight, self.bias, self.eps).to(x.dtype)
+        return F.layer_norm(x, self.normalized_shape, self.weight, self.bias, self.eps)
 
 
 class GELU(nn.Module):
     """tanh-approximated GELU (the GPT-2 activation)."""
 
     def forward(self, x):
-        return _k().gelu(x) if x.is_cuda else F.gelu(x, approximate="tanh")
+        return _k().gelu(x) if use_kernels(x) else F.gelu(x, approximate="tanh")
 
 
 class ReLU(nn.Module):
     def forward(self, x):
-        return _k().relu(x) if x.is_cuda else F.relu(x)
+        return _k().relu(x) if use_kernels(x) else F.relu(x)
 
 
 class MaxPool2d(nn.Module):
@@ -211,7 +218,7 @@ def nll_loss(logp: torch.Tensor, target: torch.Tensor, reduction: str = "mean") 
 
 def cross_entropy(logits: torch.Tensor, target: torch.Tensor, reduction: str = "mean") -> torch.Tensor:
     """Fused log_softmax + nll (forward) and (softmax - onehot)/N (backward)."""
-    if logits.is_cuda and logits.dim() == 2:
+    if use_kernels(logits) and logits.dim() == 2:
         return _k().cross_entropy(logits, target, reduction)
     return F.cross_entropy(logits, target, reduction=reduction)
 
