@@ -34,7 +34,8 @@ struct FlatConvParams {
 
 namespace {
 using namespace tc;
-constexpr int kBM = 128, kThreads = 320, kTmem = 128;   // warps: 0 TMA, 1 MMA, 2-9 epilogue (4 lane groups x 2 column chunks)
+constexpr int kIssuers = 3;                                  // MMA-issuing warps (1, 10, 11): the filter taps are split between them
+constexpr int kBM = 128, kThreads = 32 * (9 + kIssuers), kTmem = 512;   // warps: 0 TMA, 1/10/11 MMA issuers, 2-9 epilogue (4 lane groups x 2 column chunks)
 
 __device__ __forceinline__ uint64_t desc_k128(uint32_t addr, int use_base_offset) {
   // K-major, 128-byte swizzle, SBO = 1024 B; optional base_offset = row phase of the start address inside its 1024-B atom
@@ -69,8 +70,8 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   if (warp == 1) {
     if (lane == 0) {
       mbar_init(&bars->w_full, 1);
-      for (int i = 0; i < 4; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 1); }
-      for (int i = 0; i < 2; ++i) { mbar_init(&bars->acc_full[i], 1); mbar_init(&bars->acc_empty[i], 4 * (p.Cout / 32)); }
+      for (int i = 0; i < 4; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], kIssuers); }
+      for (int i = 0; i < 2; ++i) { mbar_init(&bars->acc_full[i], kIssuers); mbar_init(&bars->acc_empty[i], 4 * (p.Cout / 32)); }
       mbar_fence_init();
     }
     __syncwarp();
@@ -106,27 +107,32 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       for (int cc = 0; cc < cch; ++cc)
         tma_load_2d(a_smem + st * stage_bytes + cc * chunk_bytes, &map_in, &bars->full[st], cc * 32, (int)(p0 + p.min_off));
     }
-  } else if (warp == 1) {
-    // ---- MMA issuer: the whole warp runs the (uniform) loop, one elected lane issues ----
+  } else if (warp == 1 || warp >= 10) {
+    // ---- two MMA issuers (the single-thread issue rate, ~120 cycles per 128x64x8 instruction, is what bounds this
+    //      kernel): warp 1 takes the first half of the filter taps, warp 10 the rest, each into its own TMEM
+    //      accumulator; the epilogue adds the two.  Each warp runs the (uniform) loop, one elected lane issues.
+    const int half = warp == 1 ? 0 : warp - 9;                        // issuer index 0 .. kIssuers-1
+    const int per = (p.taps + kIssuers - 1) / kIssuers;
+    const int t_begin = min(p.taps, half * per), t_end = min(p.taps, t_begin + per);
     const uint32_t idesc = make_idesc(true, false, false, kBM, p.Cout);
     const uint32_t w0 = smem_u32(w_smem);
     mbar_wait(&bars->w_full, 0);
-    if (dbg && lane == 0) dbg[1] = clock64();
+    if (dbg && lane == 0 && half == 0) dbg[1] = clock64();
     for (int i = 0; i < my_tiles; ++i) {
       const int st = i % stages, ph = (i / stages) & 1;
       const int ab = i & 1, aph = (i >> 1) & 1;
       mbar_wait(&bars->acc_empty[ab], aph ^ 1);     // epilogue drained this accumulator
-      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 0] = clock64();
+      if (dbg && i < 8 && lane == 0 && half == 0) dbg[8 + i * 8 + 0] = clock64();
       mbar_wait(&bars->full[st], ph);
-      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 1] = clock64();
+      if (dbg && i < 8 && lane == 0 && half == 0) dbg[8 + i * 8 + 1] = clock64();
       tc_fence_after();
       const uint32_t a0 = smem_u32(a_smem + st * stage_bytes);
-      const uint32_t tacc = tmem + ab * p.Cout;
+      const uint32_t tacc = tmem + (ab * kIssuers + half) * p.Cout;
       if (elect_one()) {
         // descriptor = constant high word | (address >> 4): everything below is computed from kernel parameters
         constexpr uint64_t kDescHi = ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
         uint32_t acc = 0;
-        for (int t = 0; t < p.taps; ++t) {
+        for (int t = t_begin; t < t_end; ++t) {
           const uint32_t arow = a0 + (uint32_t)(p.off[t] - p.min_off) * 128;
           for (int cc = 0; cc < cch; ++cc) {
             const uint32_t aa = arow + cc * chunk_bytes, wa = w0 + (t * cch + cc) * (p.Cout * 128);
@@ -141,9 +147,9 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
         umma_commit(&bars->acc_full[ab]);
       }
       __syncwarp();
-      if (dbg && i < 8 && lane == 0) dbg[8 + i * 8 + 2] = clock64();
+      if (dbg && i < 8 && lane == 0 && half == 0) dbg[8 + i * 8 + 2] = clock64();
     }
-  } else if (warp >= 2 && (warp - 2) / 4 < p.Cout / 32) {
+  } else if (warp >= 2 && warp < 10 && (warp - 2) / 4 < p.Cout / 32) {
     // ---- epilogue: warp = (lane group lg, 32-column chunk) ----
     const int lg = warp & 3, row = lg * 32 + lane, c0 = ((warp - 2) >> 2) * 32;
     float (*so)[36] = bars->stage_out[warp - 2];
@@ -162,7 +168,15 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       if (dbg && i < 8 && warp == 2 && lane == 0) dbg[8 + i * 8 + 3] = clock64();
       tc_fence_after();
       uint32_t r[32];
-      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * p.Cout + c0, r);
+      tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + (ab * kIssuers) * p.Cout + c0, r);
+#pragma unroll
+      for (int h = 1; h < kIssuers; ++h) {      // add the partial accumulators of the other issuers
+        uint32_t r2[32];
+        tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + (ab * kIssuers + h) * p.Cout + c0, r2);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 32; ++j) r[j] = __float_as_uint(__uint_as_float(r[j]) + __uint_as_float(r2[j]));
+      }
       tmem_ld_wait();
       // the accumulator is in registers: hand the TMEM buffer back before the (long) store phase
       tc_fence_before();
@@ -239,6 +253,7 @@ extern "C" {
 int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps,
                      const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, cudaStream_t s) {
   if ((Cin != 32 && Cin != 64) || (Cout != 32 && Cout != 64) || taps < 1 || taps > 9) { dcp_set_error("flat conv: unsupported Cin/Cout/taps %d/%d/%d", Cin, Cout, taps); return -1; }
+  if (taps < kIssuers) { dcp_set_error("flat conv: needs at least %d filter taps (one per issuing warp)", kIssuers); return -1; }
   FlatConvParams p{};
   p.P = P; p.Cin = Cin; p.Cout = Cout; p.taps = taps; p.W = W; p.HW = HW; p.Hv = Hv; p.Wv = Wv; p.mode = mode;
   p.out = out; p.bias = bias; p.mask = mask;
