@@ -17,6 +17,7 @@ weights (tests/test_convnet_trainer_gpu.py checks gradients against the layer-by
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
@@ -82,6 +83,9 @@ class FusedConvNetTrainer:
         self.dh1 = torch.empty(N, 128, **f32); self.dpooled = torch.empty(N, 9216, **f32)
         self.dy2 = torch.empty(P, 64, **f32); self.dz1 = torch.empty(P, 32, **f32)
         self.wt2 = torch.empty(32 * 9 * 64, **f32)
+        self.wg_parts = min(148, -(-P // 128))
+        self.wg_scratch = torch.empty(self.wg_parts * 64 * 288, **f32)
+        self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
         self.off_bwd = (C.c_int * 9)(*[-((2 - r) * 26 + (2 - s)) for r in range(3) for s in range(3)])
         self.seed = int(torch.initial_seed() if seed is None else seed) & 0xFFFFFFFFFFFFFFFF
@@ -128,7 +132,11 @@ class FusedConvNetTrainer:
         # ---- backward: convolutional trunk
         ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
                                   self.seed, 1, step_ptr, tr, s()))
-        tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
+        if self.flat_wgrad:
+            ck(L.dcp_conv_wgrad_flat_tc(self.a1.data_ptr(), self.dy2.data_ptr(), self.wg_scratch.data_ptr(), N * 676, 64, 26, self.wg_parts, s()))
+            ck(tc._lib.dcp_splitk_reduce(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), None, self.wg_parts, 64 * 288, 4, s()))
+        else:
+            tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
         ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
         ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,

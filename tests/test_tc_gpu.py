@@ -114,3 +114,32 @@ def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
         F.conv2d(x.double(), wr, br, 1, pad).backward(dy.double())
         assert _rel_err(dw32, wr.grad) < tol, _rel_err(dw32, wr.grad)
         assert _rel_err(db32, br.grad) < tol
+
+
+@pytest.mark.parametrize("N,Cout,W", [(4, 64, 26), (37, 64, 26), (16, 32, 26), (8, 64, 14)])
+def test_conv_wgrad_flat(N, Cout, W):
+    """Flat-shift weight gradient (dcp_conv_wgrad_flat_tc + dcp_splitk_reduce) vs F.conv2d's fp32 weight gradient."""
+    from distributed_compute_pytorch_b200.ops import cuda
+    tc = _tc()
+    L = cuda.lib()
+    torch.manual_seed(N * Cout)
+    H = W
+    x = torch.randn(N, 32, H, W, device=DEV)
+    dy_valid = torch.randn(N, Cout, H - 2, W - 2, device=DEV)
+    # reference in fp64 on tf32-rounded... plain fp32 inputs; tf32 multiply tolerance below
+    w = torch.zeros(Cout, 32, 3, 3, device=DEV, dtype=torch.float64, requires_grad=True)
+    F.conv2d(x.double(), w).backward(dy_valid.double())
+    ref = w.grad.permute(0, 2, 3, 1).contiguous()                    # [K, R, S, C]
+    xf = x.permute(0, 2, 3, 1).contiguous().view(N * H * W, 32)
+    dyf = torch.zeros(N, H, W, Cout, device=DEV)
+    dyf[:, :H - 2, :W - 2, :] = dy_valid.permute(0, 2, 3, 1)
+    dyf = dyf.view(N * H * W, Cout)
+    P = N * H * W
+    for parts in (min(148, -(-P // 128)), 3):
+        scratch = torch.full((parts * Cout * 288,), float("nan"), device=DEV)
+        dw = torch.empty(Cout, 3, 3, 32, device=DEV)
+        cuda._chk(L.dcp_conv_wgrad_flat_tc(xf.data_ptr(), dyf.data_ptr(), scratch.data_ptr(), P, Cout, W, parts, cuda._stream()))
+        cuda._chk(tc._lib.dcp_splitk_reduce(scratch.data_ptr(), dw.data_ptr(), None, parts, Cout * 288, 4, cuda._stream()))
+        torch.cuda.synchronize()
+        err = ((dw.double() - ref).norm() / ref.norm()).item()
+        assert err < 2e-3, (parts, err)
