@@ -8,7 +8,7 @@
 //                  dropout p (Philox, regenerated in backward) and the argmax byte     (K5-K7, ref:main.py:36-38)
 //   pool_bwd       dpooled -> dy2[N*676, 64]: routes the gradient to the argmax position, applies the dropout
 //                  mask and the ReLU mask (pooled > 0), zero elsewhere                 (backward of K4-K6)
-//   conv1_wgrad    dz1[N*676, 32], x -> dw1[32, 9], db1[32] (fp32 atomics; caller zeroes)   (backward of K1)
+//   conv1_wgrad    dz1[N*676, 32], x -> dw1[32, 9], db1[32] (per-CTA partials, last CTA sums)  (backward of K1)
 #include "ops/ops_common.cuh"
 
 namespace {
@@ -117,20 +117,27 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float* __restrict__ dpoo
   }
 }
 
-// dz1 [P,32], x [N,28,28] -> dw1[32][9] += , db1[32] +=   (8 pixel lanes x 32 channels per CTA; each lane keeps
-// 4 pixels in flight so the dependent-load chain is short; one atomic per output per CTA)
-__global__ void __launch_bounds__(256) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
-                                                     float* __restrict__ db1, long total_pixels) {
-  __shared__ float red[8][32][11];
+// dz1 [P,32], x [N,28,28] -> dw1[32][9], db1[32].  16 pixel lanes x 32 channels per CTA, each lane keeps 8 pixels in
+// flight.  Every CTA leaves its partial sums in a device-resident table and takes a ticket; the CTA that draws the last
+// ticket adds the table up and OVERWRITES dw1 / db1 (no atomics on the outputs, nothing to zero beforehand), then
+// resets the ticket counter for the next launch.
+constexpr int kC1Blocks = 148, kC1Lanes = 16, kC1Fly = 8;
+static __device__ float g_c1w_part[kC1Blocks][320];
+static __device__ unsigned g_c1w_ticket;
+
+__global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
+                                                               float* __restrict__ db1, long total_pixels) {
+  __shared__ float red[kC1Lanes][32][11];
+  __shared__ bool last;
   const int c = threadIdx.x & 31, lane = threadIdx.x >> 5;
   float acc[10];
 #pragma unroll
   for (int t = 0; t < 10; ++t) acc[t] = 0.f;
-  const long stride = (long)gridDim.x * 8;
-  for (long p0 = (long)blockIdx.x * 8 + lane; p0 < total_pixels; p0 += 4 * stride) {
-    float g[4]; const float* xi[4];
+  const long stride = (long)gridDim.x * kC1Lanes;
+  for (long p0 = (long)blockIdx.x * kC1Lanes + lane; p0 < total_pixels; p0 += kC1Fly * stride) {
+    float g[kC1Fly]; const float* xi[kC1Fly];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kC1Fly; ++u) {
       const long pix = p0 + u * stride;
       const bool ok = pix < total_pixels;
       g[u] = ok ? dz1[pix * 32 + c] : 0.f;
@@ -139,7 +146,7 @@ __global__ void __launch_bounds__(256) k_conv1_wgrad(const float* __restrict__ d
       xi[u] = x + (long)n * 784 + h * 28 + wq;
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < kC1Fly; ++u) {
 #pragma unroll
       for (int r = 0; r < 3; ++r)
 #pragma unroll
@@ -150,13 +157,42 @@ __global__ void __launch_bounds__(256) k_conv1_wgrad(const float* __restrict__ d
 #pragma unroll
   for (int t = 0; t < 10; ++t) red[lane][c][t] = acc[t];
   __syncthreads();
-  for (int i = threadIdx.x; i < 32 * 10; i += blockDim.x) {
-    const int cc = i / 10, t = i % 10;
+  if (threadIdx.x < 320) {
+    const int cc = threadIdx.x / 10, t = threadIdx.x % 10;
     float s = 0.f;
 #pragma unroll
-    for (int l = 0; l < 8; ++l) s += red[l][cc][t];
-    if (t < 9) atomicAdd(&dw1[cc * 9 + t], s); else atomicAdd(&db1[cc], s);
+    for (int l = 0; l < kC1Lanes; ++l) s += red[l][cc][t];
+    g_c1w_part[blockIdx.x][threadIdx.x] = s;
+    __threadfence();
   }
+  __syncthreads();
+  if (threadIdx.x == 0) last = atomicAdd(&g_c1w_ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  // warp w sums the tables of CTAs w, w + 16, ... (10 coalesced loads per table, all independent), then the 16 warp
+  // sums meet in shared memory
+  float t10[10];
+#pragma unroll
+  for (int k = 0; k < 10; ++k) t10[k] = 0.f;
+#pragma unroll 2
+  for (int b = lane; b < (int)gridDim.x; b += kC1Lanes) {
+    const float* part = &g_c1w_part[b][c];
+#pragma unroll
+    for (int k = 0; k < 10; ++k) t10[k] += __ldcg(part + 32 * k);
+  }
+  float* red2 = &red[0][0][0];                 // [16][320]
+#pragma unroll
+  for (int k = 0; k < 10; ++k) red2[lane * 320 + c + 32 * k] = t10[k];
+  __syncthreads();
+  if (threadIdx.x < 320) {
+    const int cc = threadIdx.x / 10, t = threadIdx.x % 10;
+    float tot = 0.f;
+#pragma unroll
+    for (int l = 0; l < kC1Lanes; ++l) tot += red2[l * 320 + threadIdx.x];
+    if (t < 9) dw1[cc * 9 + t] = tot; else db1[cc] = tot;
+  }
+  if (threadIdx.x == 0) g_c1w_ticket = 0;
 }
 
 }  // namespace
@@ -178,9 +214,10 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
   k_pool_bwd<<<dim3(HP + 1, N), 256, 0, s>>>(dpooled, pooled, (const uint8_t*)arg, dy2, p, seed, stream, (const long long*)step, training);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
-// dw1 / db1 are accumulated into: the caller zeroes them (they normally live in the gradient bucket).
+// dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
+// (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
-  k_conv1_wgrad<<<148 * 2, 256, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
+  k_conv1_wgrad<<<kC1Blocks, kC1Lanes * 32, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 
@@ -191,97 +228,135 @@ int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float*
 //   h1[N,128] -> BatchNorm1d (batch statistics, running-stat update) -> ReLU -> dropout p2 -> fc2 (128 -> 10)
 //   -> log_softmax + nll (mean) -> d logits -> fc2 weight/bias/data gradients -> dropout / ReLU backward
 //   -> BatchNorm backward -> dh1[N,128], dgamma, dbeta.
-// The whole problem is 16 K activations, so it lives in the shared memory of a single 1024-thread CTA; the
-// 13 launches it replaces cost ~65 us of launch latency and tail effects.  N <= 128 rows.
-// Thread (f = tid % 128, rg = tid / 128) owns feature f of rows rg, rg + 8, ...
+// The whole problem is 16 K activations.  BatchNorm, ReLU and dropout are independent per feature, only fc2 mixes
+// features: ONE thread-block cluster of 8 CTAs splits the 128 features 16 per CTA, each CTA computes its partial
+// logits, and the partials meet through distributed shared memory (every CTA reads the other seven, then finishes the
+// softmax redundantly so no second exchange is needed).  Two cluster barriers in total.  N <= 128 rows.
+// Thread (fl = tid % 16, rg = tid / 16) owns feature f0 + fl of rows rg, rg + 32, rg + 64, rg + 96.
 // =====================================================================================================
+#include <cooperative_groups.h>
 namespace {
-constexpr int HF = 128, HC = 10, HRG = 8, HMAXN = 128, HR = HMAXN / HRG;
+namespace cg = cooperative_groups;
+constexpr int HF = 128, HC = 10, HMAXN = 128;
+constexpr int HCL = 8, HFL = HF / HCL;          // cluster size, features per CTA
+constexpr int HT = 512, HRG = HT / HFL, HR = HMAXN / HRG;   // threads, row groups (32), rows per thread (4)
 
 struct HeadSmem {
-  float xhat[HMAXN][HF];
-  float h3[HMAXN][HF];
-  float w2[HC][HF];
+  float xhat[HMAXN][HFL + 1];
+  float h3[HMAXN][HFL + 1];
+  float w2[HC][HFL];
+  float part[HMAXN][HC];          // this CTA's partial logits (read by the whole cluster)
   float dlog[HMAXN][HC + 2];
-  float red[HRG][HF][HC + 1];
-  float stat[4][HF];      // mean, rstd, dbeta/N, dgamma/N
+  float red[HRG / 2][HFL][HC + 1];
+  float stat[4][HFL];             // mean, rstd, dbeta/N, dgamma/N
   float loss;
 };
 
-__global__ void __launch_bounds__(1024, 1)
+// sum over the 32 row groups of a per-thread value: the two row groups of a warp by shuffle, the 16 warps through smem
+__device__ __forceinline__ float head_colsum(HeadSmem& S, float v, int slot, int fl, int warp) {
+  v += __shfl_xor_sync(0xffffffffu, v, 16);
+  S.red[warp][fl][slot] = v;
+  return v;
+}
+
+__global__ void __cluster_dims__(HCL, 1, 1) __launch_bounds__(HT, 1)
 k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ target, const float* __restrict__ gamma, const float* __restrict__ beta,
                float* __restrict__ run_mean, float* __restrict__ run_var, long long* __restrict__ nbt, const float* __restrict__ w2,
                const float* __restrict__ b2, float* __restrict__ loss_out, float* __restrict__ logits_out, float* __restrict__ dh1,
                float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2, float* __restrict__ db2, int N, float eps,
                float momentum, float p2, unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training) {
-  extern __shared__ __align__(16) uint8_t head_raw[];
-  HeadSmem& S = *reinterpret_cast<HeadSmem*>(head_raw);
-  const int tid = threadIdx.x, f = tid & (HF - 1), rg = tid >> 7, warp = tid >> 5, lane = tid & 31;
+  __shared__ HeadSmem S;
+  cg::cluster_group cluster = cg::this_cluster();
+  const int rank = (int)cluster.block_rank();
+  const int tid = threadIdx.x, fl = tid & (HFL - 1), rg = tid >> 4, warp = tid >> 5, lane = tid & 31;
+  const int f0 = rank * HFL, f = f0 + fl;
   const float invN = 1.f / (float)N;
   float x[HR];
   // ---- 1. batch statistics (two-pass, data stays in registers) ----
   float s = 0.f;
 #pragma unroll
   for (int i = 0; i < HR; ++i) { const int r = rg + i * HRG; x[i] = r < N ? h1[r * HF + f] : 0.f; s += x[i]; }
-  S.red[rg][f][0] = s;
-  for (int i = tid; i < HC * HF; i += 1024) S.w2[i / HF][i % HF] = w2[i];
+  head_colsum(S, s, 0, fl, warp);
+  if (tid < HC * HFL) S.w2[tid / HFL][tid % HFL] = w2[(tid / HFL) * HF + f0 + tid % HFL];
   if (tid == 0) S.loss = 0.f;
   __syncthreads();
-  if (rg == 0) { float t = 0.f; for (int g = 0; g < HRG; ++g) t += S.red[g][f][0]; S.stat[0][f] = t * invN; }
+  if (tid < HFL) { float t = 0.f; for (int g = 0; g < HRG / 2; ++g) t += S.red[g][tid][0]; S.stat[0][tid] = t * invN; }
   __syncthreads();
-  const float mean = S.stat[0][f];
+  const float mean = S.stat[0][fl];
   float v = 0.f;
 #pragma unroll
   for (int i = 0; i < HR; ++i) { const int r = rg + i * HRG; if (r < N) { const float d = x[i] - mean; v += d * d; } }
-  S.red[rg][f][1] = v;
+  head_colsum(S, v, 1, fl, warp);
   __syncthreads();
-  if (rg == 0) {
-    float t = 0.f; for (int g = 0; g < HRG; ++g) t += S.red[g][f][1];
-    const float var = t * invN;
-    S.stat[1][f] = rsqrtf(var + eps);
+  if (tid < HFL) {
+    float t = 0.f; for (int g = 0; g < HRG / 2; ++g) t += S.red[g][tid][1];
+    const float var = t * invN, mu = S.stat[0][tid];
+    S.stat[1][tid] = rsqrtf(var + eps);
     if (training && run_mean) {
       const float unbiased = N > 1 ? var * (float)N / (float)(N - 1) : var;
-      run_mean[f] = (1.f - momentum) * run_mean[f] + momentum * mean;
-      run_var[f] = (1.f - momentum) * run_var[f] + momentum * unbiased;
+      run_mean[f0 + tid] = (1.f - momentum) * run_mean[f0 + tid] + momentum * mu;
+      run_var[f0 + tid] = (1.f - momentum) * run_var[f0 + tid] + momentum * unbiased;
     }
   }
-  if (tid == 0 && training && nbt) *nbt += 1;
+  if (rank == 0 && tid == 0 && training && nbt) *nbt += 1;
   __syncthreads();
   // ---- 2. normalise + affine + ReLU + dropout ----
-  const float rstd = S.stat[1][f], gm = gamma[f], bt = beta[f];
+  const float rstd = S.stat[1][fl], gm = gamma[f], bt = beta[f];
   const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
-  const float dscale = (training && p2 > 0.f) ? 1.f / (1.f - p2) : 1.f;
-  unsigned keep = 0, pos = 0;   // bit i: dropout kept / ReLU active for row rg + 8 i
+  const bool drop = training && p2 > 0.f;
+  const float dscale = drop ? 1.f / (1.f - p2) : 1.f;
+  // one Philox call yields the uniforms of 4 consecutive features of a row: lane q of a feature quad generates row q of
+  // its four rows and the quad trades the words by shuffle (same element -> same number as philox_uniform(idx))
+  uint4 rnd = make_uint4(0, 0, 0, 0);
+  if (drop) { Philox ph(seed); rnd = ph((unsigned long long)(((rg + (fl & 3) * HRG) * HF + f) >> 2), st); }
+  unsigned keep = 0, pos = 0;   // bit i: dropout kept / ReLU active for row rg + 32 i
 #pragma unroll
   for (int i = 0; i < HR; ++i) {
     const int r = rg + i * HRG;
+    const int src = (lane & ~3) | i;
+    const uint32_t wx = __shfl_sync(0xffffffffu, rnd.x, src), wy = __shfl_sync(0xffffffffu, rnd.y, src);
+    const uint32_t wz = __shfl_sync(0xffffffffu, rnd.z, src), ww = __shfl_sync(0xffffffffu, rnd.w, src);
+    const uint32_t wsel = (fl & 3) == 0 ? wx : (fl & 3) == 1 ? wy : (fl & 3) == 2 ? wz : ww;
     float xh = 0.f, h = 0.f;
     if (r < N) {
       xh = (x[i] - mean) * rstd;
       float a = xh * gm + bt;
       if (a > 0.f) pos |= 1u << i; else a = 0.f;
-      bool k = true;
-      if (training && p2 > 0.f) k = philox_uniform(seed, st, (unsigned long long)(r * HF + f)) >= p2;
+      const bool k = !drop || (float)(wsel >> 8) * (1.0f / 16777216.0f) >= p2;
       if (k) keep |= 1u << i;
       h = k ? a * dscale : 0.f;
     }
-    S.xhat[r][f] = xh;      // r < HMAXN always: rg < 8, i < 16
-    S.h3[r][f] = h;
+    S.xhat[r][fl] = xh;
+    S.h3[r][fl] = h;
   }
   __syncthreads();
-  // ---- 3. fc2 + log-softmax + nll + dlogits: one warp per row ----
-  for (int r = warp; r < N; r += 32) {
+  // ---- 3a. partial logits over this CTA's 16 features ----
+  for (int o = tid; o < HMAXN * HC; o += HT) {
+    const int r = o / HC, j = o % HC;
+    float acc = 0.f;
+#pragma unroll
+    for (int q = 0; q < HFL; ++q) acc = fmaf(S.h3[r][q], S.w2[j][q], acc);
+    S.part[r][j] = acc;
+  }
+  cluster.sync();
+  // ---- 3b. every CTA: sum the 8 partials (4 threads per row, 2 source CTAs each), log-softmax + nll + dlogits ----
+  {
+    const int r = tid >> 2, q = tid & 3;
     float acc[HC];
 #pragma unroll
     for (int j = 0; j < HC; ++j) acc[j] = 0.f;
 #pragma unroll
-    for (int q = 0; q < HF / 32; ++q) {
-      const float hv = S.h3[r][lane + 32 * q];
+    for (int c = 0; c < 2; ++c) {
+      const float2* rp = reinterpret_cast<const float2*>(cluster.map_shared_rank(&S.part[r][0], q * 2 + c));
 #pragma unroll
-      for (int j = 0; j < HC; ++j) acc[j] = fmaf(hv, S.w2[j][lane + 32 * q], acc[j]);
+      for (int j = 0; j < HC / 2; ++j) { const float2 t = rp[j]; acc[2 * j] += t.x; acc[2 * j + 1] += t.y; }
     }
 #pragma unroll
-    for (int j = 0; j < HC; ++j) acc[j] = warp_sum(acc[j]) + b2[j];
+    for (int j = 0; j < HC; ++j) {
+      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
+      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
+      acc[j] += b2[j];
+    }
     float m = acc[0];
 #pragma unroll
     for (int j = 1; j < HC; ++j) m = fmaxf(m, acc[j]);
@@ -289,40 +364,38 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
 #pragma unroll
     for (int j = 0; j < HC; ++j) se += __expf(acc[j] - m);
     const float lse = m + __logf(se);
-    const int t = (int)target[r];
-    if (lane < HC) {
-      const float pj = __expf(acc[lane] - lse);
-      S.dlog[r][lane] = (pj - (lane == t ? 1.f : 0.f)) * invN;
-      if (logits_out) logits_out[r * HC + lane] = acc[lane] - lse;     // log-probabilities, as the model's forward returns
+    const int t = r < N ? (int)target[r] : -1;
+    // thread q of the row writes columns q, q + 4, q + 8
+#pragma unroll
+    for (int j = 0; j < HC; ++j) {
+      if ((j & 3) == q) {
+        const float pj = __expf(acc[j] - lse);
+        S.dlog[r][j] = r < N ? (pj - (j == t ? 1.f : 0.f)) * invN : 0.f;
+        if (rank == 0 && logits_out && r < N) logits_out[r * HC + j] = acc[j] - lse;   // log-probabilities, as the model's forward returns
+      }
     }
-    if (lane == 0 && t >= 0 && t < HC) atomicAdd(&S.loss, (lse - acc[t]) * invN);
+    if (rank == 0 && q == 0 && t >= 0 && t < HC) {
+      float at = acc[0];
+#pragma unroll
+      for (int j = 1; j < HC; ++j) at = j == t ? acc[j] : at;
+      atomicAdd(&S.loss, (lse - at) * invN);
+    }
   }
   __syncthreads();
-  if (tid == 0) *loss_out = S.loss;
-  // ---- 4. fc2 gradients ----
+  if (rank == 0 && tid == 0) *loss_out = S.loss;
+  // ---- 4. fc2 gradients (this CTA's 16 columns of dw2; db2 on CTA 0) ----
   float gw[HC];
 #pragma unroll
   for (int j = 0; j < HC; ++j) gw[j] = 0.f;
 #pragma unroll
   for (int i = 0; i < HR; ++i) {
     const int r = rg + i * HRG;
-    if (r < N) {
-      const float hv = S.h3[r][f];
+    const float hv = S.h3[r][fl];                     // rows >= N hold zeros
 #pragma unroll
-      for (int j = 0; j < HC; ++j) gw[j] = fmaf(S.dlog[r][j], hv, gw[j]);
-    }
+    for (int j = 0; j < HC; ++j) gw[j] = fmaf(S.dlog[r][j], hv, gw[j]);
   }
 #pragma unroll
-  for (int j = 0; j < HC; ++j) S.red[rg][f][j] = gw[j];
-  __syncthreads();
-  for (int i = tid; i < HC * HF; i += 1024) {
-    const int j = i / HF, ff = i % HF;
-    float t = 0.f;
-#pragma unroll
-    for (int g = 0; g < HRG; ++g) t += S.red[g][ff][j];
-    dw2[i] = t;
-  }
-  if (tid < HC) { float t = 0.f; for (int r = 0; r < N; ++r) t += S.dlog[r][tid]; db2[tid] = t; }
+  for (int j = 0; j < HC; ++j) head_colsum(S, gw[j], j, fl, warp);
   // ---- 5. dh3 -> dropout / ReLU backward -> BatchNorm backward ----
   float g[HR];
   float sb = 0.f, sg = 0.f;
@@ -332,29 +405,40 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     float gv = 0.f;
     if (r < N && ((keep >> i) & 1u) && ((pos >> i) & 1u)) {
 #pragma unroll
-      for (int j = 0; j < HC; ++j) gv = fmaf(S.dlog[r][j], S.w2[j][f], gv);
+      for (int j = 0; j < HC; ++j) gv = fmaf(S.dlog[r][j], S.w2[j][fl], gv);
       gv *= dscale;
     }
     g[i] = gv;
     sb += gv;
-    sg += gv * S.xhat[r][f];
+    sg += gv * S.xhat[r][fl];
   }
+  __syncthreads();
+  if (tid < HC * HFL) {
+    const int j = tid / HFL, ff = tid % HFL;
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < HRG / 2; ++w) t += S.red[w][ff][j];
+    dw2[j * HF + f0 + ff] = t;
+  }
+  if (rank == 0 && tid >= HT - HC) { const int j = tid - (HT - HC); float t = 0.f; for (int r = 0; r < N; ++r) t += S.dlog[r][j]; db2[j] = t; }
   __syncthreads();                       // S.red is reused
-  S.red[rg][f][0] = sb; S.red[rg][f][1] = sg;
+  head_colsum(S, sb, 0, fl, warp);
+  head_colsum(S, sg, 1, fl, warp);
   __syncthreads();
-  if (rg == 0) {
+  if (tid < HFL) {
     float tb = 0.f, tg = 0.f;
-    for (int q = 0; q < HRG; ++q) { tb += S.red[q][f][0]; tg += S.red[q][f][1]; }
-    dbeta[f] = tb; dgamma[f] = tg;
-    S.stat[2][f] = tb * invN; S.stat[3][f] = tg * invN;
+    for (int w = 0; w < HRG / 2; ++w) { tb += S.red[w][tid][0]; tg += S.red[w][tid][1]; }
+    dbeta[f0 + tid] = tb; dgamma[f0 + tid] = tg;
+    S.stat[2][tid] = tb * invN; S.stat[3][tid] = tg * invN;
   }
   __syncthreads();
-  const float k1 = gm * rstd, k2 = S.stat[2][f], k3 = S.stat[3][f];
+  const float k1 = gm * rstd, k2 = S.stat[2][fl], k3 = S.stat[3][fl];
 #pragma unroll
   for (int i = 0; i < HR; ++i) {
     const int r = rg + i * HRG;
-    if (r < N) dh1[r * HF + f] = k1 * (g[i] - k2 - S.xhat[r][f] * k3);
+    if (r < N) dh1[r * HF + f] = k1 * (g[i] - k2 - S.xhat[r][fl] * k3);
   }
+  cluster.sync();                        // nobody leaves while a peer may still read its partial logits
 }
 }  // namespace
 
@@ -366,11 +450,9 @@ int dcp_convnet_head(const float* h1, const void* target, const float* gamma, co
                      float* db2, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id,
                      const void* step, int training, cudaStream_t s) {
   if (N < 1 || N > HMAXN) { dcp_set_error("convnet head: batch %d not in [1, %d]", N, HMAXN); return -1; }
-  static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_convnet_head, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(HeadSmem))); attr = true; }
-  k_convnet_head<<<1, 1024, sizeof(HeadSmem), s>>>(h1, (const long long*)target, gamma, beta, run_mean, run_var, (long long*)nbt, w2, b2, loss,
-                                                   logits_out, dh1, dgamma, dbeta, dw2, db2, N, eps, momentum, p2, seed, stream_id,
-                                                   (const long long*)step, training);
+  k_convnet_head<<<HCL, HT, 0, s>>>(h1, (const long long*)target, gamma, beta, run_mean, run_var, (long long*)nbt, w2, b2, loss,
+                                    logits_out, dh1, dgamma, dbeta, dw2, db2, N, eps, momentum, p2, seed, stream_id,
+                                    (const long long*)step, training);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 }  // extern "C"

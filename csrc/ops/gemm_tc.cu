@@ -11,6 +11,8 @@
 // 64 bf16 elements).  gridDim.z splits K (fp32 atomics epilogue).
 #include <cudaTypedefs.h>
 
+#include <cstdlib>
+
 #include "ops/tc_common.cuh"
 
 struct TcGemmParams {
@@ -29,6 +31,7 @@ struct TcGemmParams {
   // epilogue
   void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
   long partial_stride;      // > 0: split z writes its partial tile to out + z * partial_stride with plain stores (reduced by dcp_splitk_reduce)
+  long long* dbg;           // optional clock64 trace of CTA (0,0,0) (env DCP_GEMM_DBG_PTR, see scratch/dbg_gemm_trace.py)
 };
 
 namespace {
@@ -37,7 +40,8 @@ using namespace tc;
 constexpr int kBM = 128, kStages = 4, kMaxBN = 128;
 constexpr int kMaxGroups = 3;                 // wgrad: up to 3 accumulator groups (3 x 16 KB of A per stage)
 constexpr int kABytes = kBM * 128;            // 16 KB per stage
-constexpr int kThreads = 192;
+constexpr int kThreads = 320;                // warp 0 TMA, warp 1 MMA, warps 2-9 operand split (3xTF32) + epilogue
+constexpr int kEpiWarps = 8;
 
 struct __align__(8) Pipe {
   uint64_t full[kStages], empty[kStages], split[kStages], acc_full;
@@ -57,6 +61,8 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int nstages = p.stages;
   Pipe* pipe = reinterpret_cast<Pipe*>(smem + nstages * stage_bytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
+  long long* dbg = (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg : nullptr;
+  if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   constexpr int kElem = kTF32 ? 4 : 2;
   constexpr int kBK = 128 / kElem;             // elements per K slab
   constexpr int kUmmaK = 32 / kElem;           // elements per MMA
@@ -70,7 +76,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < kStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); mbar_init(&pipe->split[i], 4); }
+      for (int i = 0; i < kStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); mbar_init(&pipe->split[i], kEpiWarps); }
       mbar_init(&pipe->acc_full, 1);
       mbar_fence_init();
     }
@@ -81,6 +87,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *((volatile uint32_t*)&pipe->tmem_base);
+  if (dbg && threadIdx.x == 0) dbg[1] = clock64();
 
   const int m_tile = blockIdx.x, n_tile = blockIdx.y;
   // conv: decode the tile into (image group, box row, box col)
@@ -139,6 +146,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           for (int j = 0; j < (p.BN + kChunk - 1) / kChunk; ++j)
             tma_load_2d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, kb);
         }
+        if (dbg && i < 8) dbg[8 + i * 4 + 0] = clock64();
       }
     } else if (warp == 1) {
       // ================= MMA issuer (uniform loop, one elected lane issues) =================
@@ -147,6 +155,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(p.x3 ? &pipe->split[st] : &pipe->full[st], ph);
         tc_fence_after();
+        if (dbg && i < 8 && lane == 0) dbg[8 + i * 4 + 1] = clock64();
         const uint32_t sa0 = smem_u32(smem + st * stage_bytes), sb = sa0 + a_bytes;
         if (elect_one()) {
         // descriptors: only the start-address field (16-byte units) moves between k-steps, so build one base per
@@ -173,6 +182,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         if (i == nst - 1) umma_commit(&pipe->acc_full);      // accumulator complete
         }
         __syncwarp();
+        if (dbg && i < 8 && lane == 0) dbg[8 + i * 4 + 2] = clock64();
       }
     }
   }
@@ -181,16 +191,18 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
     const int lg = warp & 3;                       // TMEM lane group this warp may access
     const int row = lg * 32 + lane;                // row inside the tile
     if (kTF32 && p.x3) {
-      // 3xTF32: while the pipeline runs, these 128 threads split every landed stage in place into
+      // 3xTF32: while the pipeline runs, these 256 threads split every landed stage in place into
       // hi = x with the low 13 mantissa bits cleared (exact in tf32) and lo = x - hi (exact in fp32).
       // The split is element-wise, so it is independent of the swizzle the TMA applied.
       const int t = (warp - 2) * 32 + lane;
       for (int i = 0; i < nst; ++i) {
         const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(&pipe->full[st], ph);
+        if (dbg && i < 8 && t == 0) dbg[8 + i * 4 + 3] = clock64();
         uint4* hi = reinterpret_cast<uint4*>(smem + st * stage_bytes);
         uint4* lo = reinterpret_cast<uint4*>(smem + st * stage_bytes + half_bytes);
-        for (int v = t; v < half_bytes / 16; v += 128) {
+#pragma unroll 4
+        for (int v = t; v < half_bytes / 16; v += kEpiWarps * 32) {
           uint4 x = hi[v], h, l;
           h.x = x.x & 0xFFFFE000u; h.y = x.y & 0xFFFFE000u; h.z = x.z & 0xFFFFE000u; h.w = x.w & 0xFFFFE000u;
           l.x = __float_as_uint(__uint_as_float(x.x) - __uint_as_float(h.x)); l.y = __float_as_uint(__uint_as_float(x.y) - __uint_as_float(h.y));
@@ -206,7 +218,8 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       mbar_wait(&pipe->acc_full, 0);
       tc_fence_after();
     }
-    if (p.conv == 2) {
+    if (dbg && warp == 2 && lane == 0) dbg[3] = clock64();
+    if (p.conv == 2 && warp < 6) {
       // weight-grad: row = (unit-in-group, channel-in-chunk), column = output channel; dw[k][tap][c] += acc
       constexpr int kUnitsPerGroup = kBM / kChunk;
       for (int g = 0; g < p.groups; ++g) {
@@ -234,7 +247,13 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
           }
         }
       }
-    } else {
+    } else if (p.conv != 2) {
+    // Every MMA has retired (acc_full), so the operand stages are dead: reuse them as the transpose buffer that turns
+    // "one thread = one output row" (what tcgen05.ld delivers) into coalesced stores - 8 lanes x 16 B cover the 32
+    // columns of a row, 4 rows per store instruction.  Warps 2-5 take the first half of the BN columns, 6-9 the second.
+    const int ew = warp - 2;
+    float* stg = reinterpret_cast<float*>(smem) + ew * (32 * 36 + 64);
+    long* srow = reinterpret_cast<long*>(stg + 32 * 36);
     long out_row = -1;
     if (p.conv) {
       const int nl = row / (p.Hb * p.Wb), hl = (row / p.Wb) % p.Hb, wl = row % p.Wb;
@@ -244,9 +263,12 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
       const long gm = (long)m_tile * kBM + row;
       if (gm < p.M) out_row = gm;
     }
+    srow[lane] = out_row;
     const bool add_bias = p.bias != nullptr && blockIdx.z == 0 && p.partial_stride == 0;
     const long zoff = p.partial_stride ? (long)blockIdx.z * p.partial_stride : 0;
-    for (int c0 = 0; c0 < p.BN; c0 += 32) {
+    const int cpw = p.BN >= 64 ? p.BN / 2 : 32;             // columns per warp set
+    const int cbeg = (ew >> 2) * cpw, cend = min(p.BN, cbeg + cpw);
+    for (int c0 = cbeg; c0 < cend; c0 += 32) {
       uint32_t r[32];
       if (nst > 0) {
         tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + c0, r);
@@ -255,53 +277,56 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
 #pragma unroll
         for (int j = 0; j < 32; ++j) r[j] = 0;
       }
-      if (out_row < 0) continue;
       const int gn0 = n_tile * p.BN + c0;
-#pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int gn = gn0 + j;
-        if (gn >= p.N) break;
-        float v = __uint_as_float(r[j]);
-        if (add_bias) v += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn]) : ((const float*)p.bias)[gn];
-        if (p.relu) v = fmaxf(v, 0.f);
-        r[j] = __float_as_uint(v);
-      }
       const int ncol = min(32, p.N - gn0);
-      if (p.atomic) {
-        float* o = (float*)p.out + out_row * p.ldc + gn0;
-        for (int j = 0; j < ncol; ++j) atomicAdd(o + j, __uint_as_float(r[j]));
-      } else if (p.out_bf16) {
-        __nv_bfloat16* o = (__nv_bfloat16*)p.out + out_row * p.ldc + gn0;
-        if (ncol == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
+      if (ncol <= 0) break;
+      if (add_bias || p.relu) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            uint4 v;
-            __nv_bfloat162 t0 = __floats2bfloat162_rn(__uint_as_float(r[j]), __uint_as_float(r[j + 1]));
-            __nv_bfloat162 t1 = __floats2bfloat162_rn(__uint_as_float(r[j + 2]), __uint_as_float(r[j + 3]));
-            __nv_bfloat162 t2 = __floats2bfloat162_rn(__uint_as_float(r[j + 4]), __uint_as_float(r[j + 5]));
-            __nv_bfloat162 t3 = __floats2bfloat162_rn(__uint_as_float(r[j + 6]), __uint_as_float(r[j + 7]));
-            v.x = *reinterpret_cast<uint32_t*>(&t0); v.y = *reinterpret_cast<uint32_t*>(&t1);
-            v.z = *reinterpret_cast<uint32_t*>(&t2); v.w = *reinterpret_cast<uint32_t*>(&t3);
-            *reinterpret_cast<uint4*>(o + j) = v;
+        for (int j = 0; j < 32; ++j) {
+          const int gn = gn0 + j;
+          float v = __uint_as_float(r[j]);
+          if (add_bias && gn < p.N) v += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn]) : ((const float*)p.bias)[gn];
+          if (p.relu) v = fmaxf(v, 0.f);
+          r[j] = __float_as_uint(v);
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(stg + lane * 36 + j * 4) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+      __syncwarp();
+      const int c4 = (lane & 7) * 4, nv = min(4, ncol - c4);
+#pragma unroll
+      for (int it = 0; it < 8; ++it) {
+        const int rl = it * 4 + (lane >> 3);
+        const long orow = srow[rl];
+        if (orow < 0 || nv <= 0) continue;
+        const float4 v = *reinterpret_cast<const float4*>(stg + rl * 36 + c4);
+        const float ve[4] = {v.x, v.y, v.z, v.w};
+        if (p.atomic) {
+          float* o = (float*)p.out + orow * p.ldc + gn0 + c4;
+          for (int e = 0; e < nv; ++e) atomicAdd(o + e, ve[e]);
+        } else if (p.out_bf16) {
+          __nv_bfloat16* o = (__nv_bfloat16*)p.out + orow * p.ldc + gn0 + c4;
+          if (nv == 4 && (reinterpret_cast<uintptr_t>(o) & 7) == 0) {
+            const __nv_bfloat162 t0 = __floats2bfloat162_rn(v.x, v.y), t1 = __floats2bfloat162_rn(v.z, v.w);
+            *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&t0), *reinterpret_cast<const uint32_t*>(&t1));
+          } else {
+            for (int e = 0; e < nv; ++e) o[e] = __float2bfloat16_rn(ve[e]);
           }
         } else {
-          for (int j = 0; j < ncol; ++j) o[j] = __float2bfloat16_rn(__uint_as_float(r[j]));
-        }
-      } else {
-        float* o = (float*)p.out + zoff + out_row * p.ldc + gn0;
-        if (ncol == 32 && ((reinterpret_cast<uintptr_t>(o) & 15) == 0)) {
-#pragma unroll
-          for (int j = 0; j < 32; j += 4) *reinterpret_cast<uint4*>(o + j) = make_uint4(r[j], r[j + 1], r[j + 2], r[j + 3]);
-        } else {
-          for (int j = 0; j < ncol; ++j) o[j] = __uint_as_float(r[j]);
+          float* o = (float*)p.out + zoff + orow * p.ldc + gn0 + c4;
+          if (nv == 4 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) *reinterpret_cast<float4*>(o) = v;
+          else for (int e = 0; e < nv; ++e) o[e] = ve[e];
         }
       }
+      __syncwarp();
     }
     }
   }
+  if (dbg && warp == 2 && lane == 0) dbg[4] = clock64();
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc<kTmemCols>(tmem);
+  if (dbg && threadIdx.x == 0) dbg[2] = clock64();
 }
 
 // ---- host: tensor maps ------------------------------------------------------------------------------
@@ -348,7 +373,7 @@ int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, 
 }
 
 size_t smem_bytes(int stages, int a_bytes, int b_bytes, int x3 = 0) { return (size_t)stages * (a_bytes + b_bytes) * (x3 ? 2 : 1) + sizeof(Pipe) + 1024; }
-constexpr int kMaxSmem = 200 * 1024;
+constexpr int kMaxSmem = 200 * 1024;    // >= 8 x 4864 B of epilogue staging, which reuses the (dead) operand stages
 int b_stage_bytes(int BN, int b_mn, int es) { int chunk = 128 / es, bk = 128 / es; return b_mn ? ((BN + chunk - 1) / chunk) * bk * 128 : BN * 128; }
 
 template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUtensorMap& mb, const TcGemmParams& p, dim3 grid, cudaStream_t s) {
@@ -359,6 +384,7 @@ template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUt
     attr_set = true;
   }
   TcGemmParams q = p;
+  { const char* e = getenv("DCP_GEMM_DBG_PTR"); q.dbg = e ? (long long*)strtoull(e, nullptr, 0) : nullptr; }
   q.stages = kStages;
   while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) --q.stages;
   if (smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }

@@ -11,12 +11,40 @@ struct DcpOptEntry { float* p; const void* g; float* s1; float* s2; long long n;
 
 namespace {
 constexpr int kT = 256;
+template <typename G> struct GVec4;
+template <> struct GVec4<float> { using type = float4; };
+template <> struct GVec4<__nv_bfloat16> { using type = uint2; };
+__device__ __forceinline__ void unpack4(const float4& v, float* o) { o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+__device__ __forceinline__ void unpack4(const uint2& v, float* o) {
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&v.x), b = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+  o[0] = __low2float(a); o[1] = __high2float(a); o[2] = __low2float(b); o[3] = __high2float(b);
+}
+
 template <int KIND, typename G>
 __global__ void __launch_bounds__(kT) k_opt(const DcpOptEntry* __restrict__ table, const float* __restrict__ hp) {
   const DcpOptEntry e = table[blockIdx.y];
   const float step = hp[6], gs = hp[7];
   const G* g = static_cast<const G*>(e.g);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < e.n; i += (long long)gridDim.x * blockDim.x) {
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
+  // 16-byte path: four elements per thread and iteration (parameter views inside the flat buckets are 16-byte aligned
+  // whenever their offset is a multiple of four elements)
+  using GV = typename GVec4<G>::type;
+  const bool vec = (((uintptr_t)e.p | (uintptr_t)e.s1 | (uintptr_t)e.s2) & 15) == 0 && ((uintptr_t)e.g & (sizeof(GV) - 1)) == 0;
+  const long long n4 = vec ? e.n / 4 : 0;
+  for (long long i = tid; i < n4; i += nthr) {
+    float4 p4 = reinterpret_cast<float4*>(e.p)[i];
+    float4 a4 = e.s1 ? reinterpret_cast<float4*>(e.s1)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 b4 = e.s2 ? reinterpret_cast<float4*>(e.s2)[i] : make_float4(0.f, 0.f, 0.f, 0.f);
+    float gv[4];
+    unpack4(reinterpret_cast<const GV*>(g)[i], gv);
+    float* pp = reinterpret_cast<float*>(&p4); float* pa = reinterpret_cast<float*>(&a4); float* pb = reinterpret_cast<float*>(&b4);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) opt_update<KIND, float>(pp[j], gv[j] * gs, pa[j], pb[j], hp, step);
+    reinterpret_cast<float4*>(e.p)[i] = p4;
+    if (e.s1) reinterpret_cast<float4*>(e.s1)[i] = a4;
+    if (e.s2) reinterpret_cast<float4*>(e.s2)[i] = b4;
+  }
+  for (long long i = n4 * 4 + tid; i < e.n; i += nthr) {
     float p = e.p[i], s1 = e.s1 ? e.s1[i] : 0.f, s2 = e.s2 ? e.s2[i] : 0.f;
     opt_update<KIND, G>(p, to_f(g[i]) * gs, s1, s2, hp, step);
     e.p[i] = p;

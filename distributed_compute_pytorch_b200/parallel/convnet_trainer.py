@@ -141,7 +141,6 @@ class FusedConvNetTrainer:
         ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
-        g["conv1.weight"].zero_(); g["conv1.bias"].zero_()
         ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
         ev1 = self._reduce_bucket(1)
         for ev in (ev0, ev1):
