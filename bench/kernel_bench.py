@@ -44,8 +44,8 @@ def main():
         "fc1_dgrad tcgen05 3xTF32": (lambda: tc.gemm(tr.dh1, p["fc1.weight"], tr.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1), 3 * 2 * N * 128 * 9216, (N + 128) * 9216 * 4),
         "pool_bwd (+relu/dropout bwd)": (lambda: L.dcp_convnet_pool_bwd(tr.dpooled.data_ptr(), tr.pooled.data_ptr(), tr.arg.data_ptr(), tr.dy2.data_ptr(), N, 0.25, tr.seed, 1, step_ptr, 1, s()), 0, P * 64 * 4 + N * 9216 * 9),
         "conv2_wgrad tcgen05 (tf32) + reduce": (lambda: tc.conv_wgrad_launch(tr.dy2, tr.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148), 2 * P * 64 * 288, P * 96 * 4),
-        "conv2_wgrad FLAT tcgen05 (tf32) + reduce": (lambda: (L.dcp_conv_wgrad_flat_tc(tr.a1.data_ptr(), tr.dy2.data_ptr(), tr.wg_scratch.data_ptr(), P, 64, 26, tr.wg_parts, s()),
-                                                              tc._lib.dcp_splitk_reduce(tr.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), None, tr.wg_parts, 64 * 288, 4, s())), 2 * P * 64 * 288, P * 96 * 4),
+        "conv2_wgrad+bias_grad FLAT tcgen05 (tf32) + reduce": (lambda: (L.dcp_conv_wgrad_flat_tc(tr.a1.data_ptr(), tr.dy2.data_ptr(), tr.wg_scratch.data_ptr(), P, 64, 26, tr.wg_parts, s()),
+                                                              tc._lib.dcp_splitk_reduce2(tr.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), g["conv2.bias"].data_ptr(), 64 * 288, tr.wg_parts, 64 * 289, s())), 2 * P * 64 * 288, P * 96 * 4),
         "conv2_bias_grad colsum": (lambda: L.dcp_colsum(tr.dy2.data_ptr(), g["conv2.bias"].data_ptr(), P, 64, 0, s()), 0, P * 64 * 4),
         "conv2_dgrad flat tcgen05 (tf32)": (lambda: L.dcp_conv_flat_tc(tr.dy2.data_ptr(), tr.wt2.data_ptr(), tr.dz1.data_ptr(), None, tr.a1.data_ptr(), P, 64, 32, 9, tr.off_bwd, 26, 676, 26, 26, 1, 148, s()),
                                             2 * P * 32 * 576, P * 64 * 4 + P * 32 * 8),

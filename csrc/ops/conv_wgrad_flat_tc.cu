@@ -9,7 +9,10 @@
 // (128 lanes = 4 chunks of 32 channels, chunk s = tap (r, s); chunk 3 is padding): its A operand is the x tile
 // shifted by r*W rows whose 128-byte M-chunks are ONE row apart (LBO = 128 B) - the three horizontal taps are
 // overlapping windows of the same shared-memory tile, so x is loaded once instead of 9 times.
-// Partial filters of the CTAs go to a scratch buffer [CTA][Cout][9*32] and are summed by dcp_splitk_reduce.
+// While the tensor core works, the four epilogue warps add up the columns of the dy tile in shared memory: that is the
+// BIAS gradient db[k] = sum_p dy[p][k], which so costs no extra pass over dy.
+// Partial filters and bias gradients of the CTAs go to a scratch buffer [CTA][Cout*288 + Cout] and are summed by
+// dcp_splitk_reduce2.
 #include <cudaTypedefs.h>
 
 #include "ops/tc_common.cuh"
@@ -18,7 +21,7 @@ struct WgradFlatParams {
   long P;
   int Cout, W;              // Cout in {32, 64}; row pitch of the frame
   int stages_total;         // ceil(P / 128)
-  float* scratch;           // [gridDim.x][Cout][288]
+  float* scratch;           // [gridDim.x][Cout*288 + Cout]
 };
 
 namespace {
@@ -48,7 +51,7 @@ k_wgrad_flat(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_dy); }
   if (warp == 1) {
     if (lane == 0) {
-      for (int i = 0; i < 3; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 3); }
+      for (int i = 0; i < 3; ++i) { mbar_init(&bars->full[i], 1); mbar_init(&bars->empty[i], 3 + 4); }
       mbar_init(&bars->acc_full, 3);
       mbar_fence_init();
     }
@@ -95,10 +98,37 @@ k_wgrad_flat(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
       __syncwarp();
     }
   } else if (warp >= 4) {
-    // epilogue (once): accumulator r, lane = s*32 + c, column = k  ->  scratch[cta][k][(r*3+s)*32 + c]
+    // ---- during the main loop: column sums of the dy tiles (bias gradient).  Thread = (16-byte unit u of the row,
+    // row group rg); the TMA wrote the tile with the 32-byte-atom swizzle: physical unit = u ^ ((row & 3) << 1)
+    const int t = (warp - 4) * 32 + lane;
+    const int upr = p.Cout / 4, u = t % upr, rg = t / upr, nrg = 128 / upr;
+    float4 bsum = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int i = 0; i < n; ++i) {
+      const int st = i % nstages, ph = (i / nstages) & 1;
+      mbar_wait(&bars->full[st], ph);
+      const uint8_t* base = smem + st * stage_bytes + x_bytes + (u >> 3) * (kBK * 128);
+#pragma unroll 4
+      for (int row = rg; row < kBK; row += nrg) {
+        const float4 v = *reinterpret_cast<const float4*>(base + row * 128 + (((u & 7) ^ ((row & 3) << 1)) << 4));
+        bsum.x += v.x; bsum.y += v.y; bsum.z += v.z; bsum.w += v.w;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bars->empty[st]);
+    }
+    // ---- epilogue (once): accumulator r, lane = s*32 + c, column = k  ->  scratch[cta][k][(r*3+s)*32 + c]
     const int lg = warp & 3;                                   // lanes lg*32 .. +31  <=>  tap column s = lg, channel c = lane
-    float* out = p.scratch + (size_t)blockIdx.x * p.Cout * 288;
+    float* out = p.scratch + (size_t)blockIdx.x * p.Cout * 289;
     if (n > 0) { mbar_wait(&bars->acc_full, 0); tc_fence_after(); }
+    // all MMAs have retired: the stages are free, use stage 0 to add the row groups of the bias sums
+    float4* red = reinterpret_cast<float4*>(smem);
+    red[rg * upr + u] = bsum;
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    if (t < p.Cout) {
+      const float* rf = reinterpret_cast<const float*>(smem);
+      float sum = 0.f;
+      for (int g = 0; g < nrg; ++g) sum += rf[g * p.Cout + t];
+      out[p.Cout * 288 + t] = sum;
+    }
     if (lg < 3) {
       for (int r = 0; r < 3; ++r) {
         for (int c0 = 0; c0 < p.Cout; c0 += 32) {
@@ -144,8 +174,9 @@ int wg_map(CUtensorMap* m, const void* base, long rows, long cols, int box_cols,
 
 extern "C" {
 
-// x: [P, 32] fp32 flat pixels (pitch W); dy: [P, Cout] fp32 in the same frame; scratch: [num_ctas][Cout][288] fp32 partial
-// filters (finish with dcp_splitk_reduce(scratch, dw, nullptr, num_ctas, Cout*288, 4)).  3x3 filters, Cin = 32.
+// x: [P, 32] fp32 flat pixels (pitch W); dy: [P, Cout] fp32 in the same frame; scratch: [num_ctas][Cout*288 + Cout] fp32 partial
+// filters followed by partial bias gradients (finish with dcp_splitk_reduce2(scratch, dw, db, Cout*288, num_ctas, Cout*289)).
+// 3x3 filters, Cin = 32.
 // Exactly num_ctas partials are written (CTAs without pixels write zeros).
 int dcp_conv_wgrad_flat_tc(const float* x, const float* dy, float* scratch, long P, int Cout, int W, int num_ctas, cudaStream_t s) {
   if (Cout != 32 && Cout != 64) { dcp_set_error("flat wgrad: Cout must be 32 or 64"); return -1; }

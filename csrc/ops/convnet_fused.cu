@@ -52,8 +52,17 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float* __restrict__ a2, 
                                                   unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training) {
   __shared__ float sv[HP][65];
   __shared__ uint8_t sa[HP][65];
+  __shared__ float keep[64];          // dropout factor of channel c of this image: 0 or 1/(1-p)
   const int ph = blockIdx.x, n = blockIdx.y;
   const float* base = a2 + ((long)n * P1 + (long)(2 * ph) * HW1) * 64;
+  if (threadIdx.x < 64) {
+    float k = 1.f;
+    if (training && p > 0.f) {
+      const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
+      k = philox_uniform(seed, st, (unsigned long long)(n * 64 + threadIdx.x)) >= p ? 1.f / (1.f - p) : 0.f;
+    }
+    keep[threadIdx.x] = k;
+  }
   for (int i = threadIdx.x; i < HP * 64; i += blockDim.x) {
     const int c = i & 63, pw = i >> 6;
     const float* q = base + (2 * pw) * 64 + c;
@@ -65,17 +74,10 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float* __restrict__ a2, 
     sv[pw][c] = m; sa[pw][c] = (uint8_t)a;
   }
   __syncthreads();
-  const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
-  const float scale = 1.f / (1.f - p);
   for (int i = threadIdx.x; i < 64 * HP; i += blockDim.x) {
     const int pw = i % HP, c = i / HP;
-    float m = sv[pw][c];
-    if (training && p > 0.f) {
-      float u = philox_uniform(seed, st, (unsigned long long)(n * 64 + c));
-      m = u >= p ? m * scale : 0.f;
-    }
     const long o = (((long)n * 64 + c) * HP + ph) * HP + pw;
-    pooled[o] = m;
+    pooled[o] = sv[pw][c] * keep[c];
     arg[o] = sa[pw][c];
   }
 }
@@ -117,8 +119,8 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float* __restrict__ dpoo
   }
 }
 
-// dz1 [P,32], x [N,28,28] -> dw1[32][9], db1[32].  16 pixel lanes x 32 channels per CTA, each lane keeps 8 pixels in
-// flight.  Every CTA leaves its partial sums in a device-resident table and takes a ticket; the CTA that draws the last
+// dz1 [P,32], x [N,28,28] -> dw1[32][9], db1[32].  16 pixel lanes (warps) x 32 channels per CTA, one image per CTA
+// iteration, 8 gradient rows in flight per warp.  Every CTA leaves its partial sums in a device-resident table and takes a ticket; the CTA that draws the last
 // ticket adds the table up and OVERWRITES dw1 / db1 (no atomics on the outputs, nothing to zero beforehand), then
 // resets the ticket counter for the next launch.
 constexpr int kC1Blocks = 148, kC1Lanes = 16, kC1Fly = 8;
@@ -128,30 +130,34 @@ static __device__ unsigned g_c1w_ticket;
 __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
                                                                float* __restrict__ db1, long total_pixels) {
   __shared__ float red[kC1Lanes][32][11];
+  __shared__ float sx[784];
   __shared__ bool last;
   const int c = threadIdx.x & 31, lane = threadIdx.x >> 5;
   float acc[10];
 #pragma unroll
   for (int t = 0; t < 10; ++t) acc[t] = 0.f;
-  const long stride = (long)gridDim.x * kC1Lanes;
-  for (long p0 = (long)blockIdx.x * kC1Lanes + lane; p0 < total_pixels; p0 += kC1Fly * stride) {
-    float g[kC1Fly]; const float* xi[kC1Fly];
+  // one image at a time: its 28x28 input sits in shared memory (the 9 taps are broadcast reads), warp `lane` takes
+  // output pixels lane, lane + 16, ... of the 26x26 frame with kC1Fly gradient rows in flight
+  const int nimg = (int)(total_pixels / P1);
+  for (int n = blockIdx.x; n < nimg; n += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 784; i += blockDim.x) sx[i] = x[(long)n * 784 + i];
+    __syncthreads();
+    const float* dz = dz1 + (long)n * P1 * 32 + c;
+    for (int q0 = lane; q0 < P1; q0 += kC1Lanes * kC1Fly) {
+      float g[kC1Fly];
 #pragma unroll
-    for (int u = 0; u < kC1Fly; ++u) {
-      const long pix = p0 + u * stride;
-      const bool ok = pix < total_pixels;
-      g[u] = ok ? dz1[pix * 32 + c] : 0.f;
-      const long pc = ok ? pix : 0;
-      const int n = (int)(pc / P1), q = (int)(pc % P1), h = q / HW1, wq = q % HW1;
-      xi[u] = x + (long)n * 784 + h * 28 + wq;
-    }
+      for (int u = 0; u < kC1Fly; ++u) { const int q = q0 + u * kC1Lanes; g[u] = q < P1 ? dz[q * 32] : 0.f; }
 #pragma unroll
-    for (int u = 0; u < kC1Fly; ++u) {
+      for (int u = 0; u < kC1Fly; ++u) {
+        const int q = min(q0 + u * kC1Lanes, P1 - 1), h = q / HW1, wq = q % HW1;
+        const float* xi = sx + h * 28 + wq;
 #pragma unroll
-      for (int r = 0; r < 3; ++r)
+        for (int r = 0; r < 3; ++r)
 #pragma unroll
-        for (int s = 0; s < 3; ++s) acc[r * 3 + s] = fmaf(g[u], __ldg(xi[u] + r * 28 + s), acc[r * 3 + s]);
-      acc[9] += g[u];
+          for (int s = 0; s < 3; ++s) acc[r * 3 + s] = fmaf(g[u], xi[r * 28 + s], acc[r * 3 + s]);
+        acc[9] += g[u];
+      }
     }
   }
 #pragma unroll
@@ -217,7 +223,7 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
 // dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
 // (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
-  k_conv1_wgrad<<<kC1Blocks, kC1Lanes * 32, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
+  k_conv1_wgrad<<<N < kC1Blocks ? N : kC1Blocks, kC1Lanes * 32, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 

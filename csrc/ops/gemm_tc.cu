@@ -514,7 +514,7 @@ namespace {
 // CTA = 32 float4 columns x 8 split lanes: the (long) chain of dependent loads over the splits is cut 8 ways and the
 // grid stays wide even for a 128 x 128 output
 __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__ scratch, float* __restrict__ out, const float* __restrict__ bias,
-                                                       int nsplit, long n, int ncols) {
+                                                       int nsplit, long n, int ncols, float* __restrict__ out2, long n1) {
   __shared__ float4 red[8][33];
   const int vx = threadIdx.x & 31, zl = threadIdx.x >> 5;
   const long v = (long)blockIdx.x * 32 + vx, n4 = n / 4;
@@ -532,14 +532,20 @@ __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__
 #pragma unroll
     for (int i = 1; i < 8; ++i) { const float4 x = red[i][vx]; acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w; }
     if (bias) { const int c = (int)((v * 4) % ncols); acc.x += bias[c]; acc.y += bias[c + 1]; acc.z += bias[c + 2]; acc.w += bias[c + 3]; }
-    *reinterpret_cast<float4*>(out + v * 4) = acc;
+    *reinterpret_cast<float4*>(v * 4 < n1 ? out + v * 4 : out2 + (v * 4 - n1)) = acc;
   }
 }
 }  // namespace
 // n and ncols must be multiples of 4.
 extern "C" int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s) {
   if ((n & 3) || (ncols & 3)) { dcp_set_error("splitk reduce: n and ncols must be multiples of 4"); return -1; }
-  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, bias, nsplit, n, ncols);
+  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, bias, nsplit, n, ncols, nullptr, n);
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+// Same reduction with the summed vector going to two places: elements [0, n1) to `out`, [n1, n) to `out2` (n1 % 4 == 0).
+extern "C" int dcp_splitk_reduce2(const float* scratch, float* out, float* out2, long n1, int nsplit, long n, cudaStream_t s) {
+  if ((n & 3) || (n1 & 3) || n1 > n) { dcp_set_error("splitk reduce2: n and n1 must be multiples of 4, n1 <= n"); return -1; }
+  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, nullptr, nsplit, n, 4, out2, n1);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 

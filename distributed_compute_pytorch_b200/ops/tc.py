@@ -28,6 +28,8 @@ def declare(lib) -> None:
     lib.dcp_tc_conv_wgrad.argtypes = [vp, vp, vp] + [i] * 15 + [vp]
     lib.dcp_splitk_reduce.restype = C.c_int
     lib.dcp_splitk_reduce.argtypes = [vp, vp, vp, i, l, i, vp]
+    lib.dcp_splitk_reduce2.restype = C.c_int
+    lib.dcp_splitk_reduce2.argtypes = [vp, vp, vp, l, i, l, vp]
     lib.dcp_flip_weights.restype = C.c_int
     lib.dcp_flip_weights.argtypes = [vp, vp, i, i, i, i, i, vp]
     _lib = lib

@@ -84,7 +84,7 @@ class FusedConvNetTrainer:
         self.dy2 = torch.empty(P, 64, **f32); self.dz1 = torch.empty(P, 32, **f32)
         self.wt2 = torch.empty(32 * 9 * 64, **f32)
         self.wg_parts = min(148, -(-P // 128))
-        self.wg_scratch = torch.empty(self.wg_parts * 64 * 288, **f32)
+        self.wg_scratch = torch.empty(self.wg_parts * 64 * 289, **f32)
         self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
         self.off_bwd = (C.c_int * 9)(*[-((2 - r) * 26 + (2 - s)) for r in range(3) for s in range(3)])
@@ -134,10 +134,11 @@ class FusedConvNetTrainer:
                                   self.seed, 1, step_ptr, tr, s()))
         if self.flat_wgrad:
             ck(L.dcp_conv_wgrad_flat_tc(self.a1.data_ptr(), self.dy2.data_ptr(), self.wg_scratch.data_ptr(), N * 676, 64, 26, self.wg_parts, s()))
-            ck(tc._lib.dcp_splitk_reduce(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), None, self.wg_parts, 64 * 288, 4, s()))
+            ck(tc._lib.dcp_splitk_reduce2(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), g["conv2.bias"].data_ptr(), 64 * 288,
+                                          self.wg_parts, 64 * 289, s()))
         else:
             tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
-        ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
+            ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
         ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))

@@ -136,10 +136,13 @@ def test_conv_wgrad_flat(N, Cout, W):
     dyf = dyf.view(N * H * W, Cout)
     P = N * H * W
     for parts in (min(148, -(-P // 128)), 3):
-        scratch = torch.full((parts * Cout * 288,), float("nan"), device=DEV)
+        scratch = torch.full((parts * Cout * 289,), float("nan"), device=DEV)
         dw = torch.empty(Cout, 3, 3, 32, device=DEV)
+        db = torch.empty(Cout, device=DEV)
         cuda._chk(L.dcp_conv_wgrad_flat_tc(xf.data_ptr(), dyf.data_ptr(), scratch.data_ptr(), P, Cout, W, parts, cuda._stream()))
-        cuda._chk(tc._lib.dcp_splitk_reduce(scratch.data_ptr(), dw.data_ptr(), None, parts, Cout * 288, 4, cuda._stream()))
+        cuda._chk(tc._lib.dcp_splitk_reduce2(scratch.data_ptr(), dw.data_ptr(), db.data_ptr(), Cout * 288, parts, Cout * 289, cuda._stream()))
         torch.cuda.synchronize()
         err = ((dw.double() - ref).norm() / ref.norm()).item()
         assert err < 2e-3, (parts, err)
+        db_ref = dy_valid.double().sum((0, 2, 3))            # bias gradient = column sums of dy (fp32 adds, no tensor core)
+        assert ((db.double() - db_ref).norm() / db_ref.norm()).item() < 1e-5
