@@ -31,6 +31,32 @@ void dcp_set_error(const char* fmt, ...);
   } while (0)
 
 // ------------------------------------------------------------------------------------------------
+// Programmatic dependent launch (PDL).  A kernel launched with dcp_launch_pdl may become resident while its
+// predecessors in the stream are still draining: its prologue (barrier init, TMEM allocation, descriptor prefetch)
+// then overlaps their tails and the launch latency disappears.  The contract inside such a kernel:
+//   * griddep_launch() early lets the NEXT kernel in the stream start its own prologue;
+//   * griddep_wait() must come before the first access to global memory that any earlier kernel wrote or will
+//     still read - it returns once every prerequisite grid has completed and its writes are visible.
+// Launched without the attribute (DCP_PDL=0, or after a kernel that knows nothing of this) both are no-ops and the
+// stream order is the usual full serialisation.
+// ------------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void griddep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void griddep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool dcp_pdl_enabled();
+template <typename... P, typename... A>
+inline cudaError_t dcp_launch_pdl(void (*kern)(P...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, A... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = dcp_pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<P>(args)...);
+}
+#endif
+
+// ------------------------------------------------------------------------------------------------
 // Symmetric heap layout (identical offsets on every rank).  All sizes in bytes.
 // ------------------------------------------------------------------------------------------------
 struct DcpHeapLayout {

@@ -66,6 +66,7 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   Bars* bars = reinterpret_cast<Bars*>(a_smem + stages * stage_bytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
 
+  griddep_launch();                    // the next kernel may start its prologue (see common.cuh)
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_in); tma_prefetch_desc(&map_w); }
   if (warp == 1) {
     if (lane == 0) {
@@ -83,8 +84,10 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       bars->adelta[m] = (uint32_t)(((p.off[t] - p.min_off) * 128 + cc * chunk_bytes + j * 32) >> 4);
       bars->wdelta[m] = (uint32_t)(((t * cch + cc) * (p.Cout * 128) + j * 32) >> 4);
     }
-    for (int c = lane; c < p.Cout; c += 32) bars->bias[c] = p.bias ? p.bias[c] : 0.f;
   }
+  griddep_wait();                      // everything above touched only shared memory / TMEM / kernel parameters
+  if (warp == 2)
+    for (int c = lane; c < p.Cout; c += 32) bars->bias[c] = p.bias ? p.bias[c] : 0.f;
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -284,8 +287,8 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   if (map2d(&mw, wmat, Cout, (long)taps * Cin, 32, Cout)) return -1;
   if (num_ctas <= 0) num_ctas = 148;
   if (num_ctas > p.tiles) num_ctas = p.tiles;
-  if (mode == 0) k_conv_flat<0><<<num_ctas, kThreads, smem, s>>>(mi, mw, p, stages, halo_rows);
-  else k_conv_flat<1><<<num_ctas, kThreads, smem, s>>>(mi, mw, p, stages, halo_rows);
+  if (mode == 0) DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<0>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
+  else DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<1>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

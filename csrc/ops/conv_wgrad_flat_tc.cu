@@ -48,6 +48,7 @@ k_wgrad_flat(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   WBars* bars = reinterpret_cast<WBars*>(smem + nstages * stage_bytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
 
+  griddep_launch();
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_x); tma_prefetch_desc(&map_dy); }
   if (warp == 1) {
     if (lane == 0) {
@@ -61,6 +62,7 @@ k_wgrad_flat(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  griddep_wait();                      // prologue done; from here on global memory of earlier kernels is read
   const uint32_t tmem = *((volatile uint32_t*)&bars->tmem_base);
   // contiguous range of stages for this CTA
   const int per = (p.stages_total + gridDim.x - 1) / gridDim.x;
@@ -196,8 +198,7 @@ int dcp_conv_wgrad_flat_tc(const float* x, const float* dy, float* scratch, long
   if (wg_map(&mx, x, P, 32, 32, halo_rows)) return -1;
   if (wg_map(&mdy, dy, P, Cout, 32, kBK)) return -1;
   if (num_ctas <= 0) { dcp_set_error("flat wgrad: num_ctas must be positive"); return -1; }
-  k_wgrad_flat<<<num_ctas, kThreads, smem, s>>>(mx, mdy, p, nstages, halo_rows);
-  DCP_CUDA_CHECK(cudaGetLastError());
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_wgrad_flat, dim3(num_ctas), dim3(kThreads), smem, s, mx, mdy, p, nstages, halo_rows));
   return 0;
 }
 

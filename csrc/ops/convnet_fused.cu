@@ -9,6 +9,8 @@
 //   pool_bwd       dpooled -> dy2[N*676, 64]: routes the gradient to the argmax position, applies the dropout
 //                  mask and the ReLU mask (pooled > 0), zero elsewhere                 (backward of K4-K6)
 //   conv1_wgrad    dz1[N*676, 32], x -> dw1[32, 9], db1[32] (per-CTA partials, last CTA sums)  (backward of K1)
+#include <cstdlib>
+
 #include "ops/ops_common.cuh"
 
 namespace {
@@ -19,6 +21,8 @@ constexpr int HP = 12;              // pooled extent
 __global__ void __launch_bounds__(256) k_conv1_fwd(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ b,
                                                    float* __restrict__ a1, long total_pixels) {
   __shared__ float sw[32 * 9], sb[32];
+  griddep_launch();
+  griddep_wait();
   for (int i = threadIdx.x; i < 32 * 9; i += blockDim.x) sw[i] = w[i];
   if (threadIdx.x < 32) sb[threadIdx.x] = b[threadIdx.x];
   __syncthreads();
@@ -53,6 +57,8 @@ __global__ void __launch_bounds__(256) k_pool_fwd(const float* __restrict__ a2, 
   __shared__ float sv[HP][65];
   __shared__ uint8_t sa[HP][65];
   __shared__ float keep[64];          // dropout factor of channel c of this image: 0 or 1/(1-p)
+  griddep_launch();
+  griddep_wait();
   const int ph = blockIdx.x, n = blockIdx.y;
   const float* base = a2 + ((long)n * P1 + (long)(2 * ph) * HW1) * 64;
   if (threadIdx.x < 64) {
@@ -88,6 +94,8 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float* __restrict__ dpoo
                                                   const long long* __restrict__ step, int training) {
   __shared__ float sg[HP][65];
   __shared__ uint8_t sa[HP][65];
+  griddep_launch();
+  griddep_wait();
   const int ph = blockIdx.x, n = blockIdx.y;
   float* out = dy2 + ((long)n * P1 + (long)(2 * ph) * HW1) * 64;
   if (ph == HP) {
@@ -123,7 +131,7 @@ __global__ void __launch_bounds__(256) k_pool_bwd(const float* __restrict__ dpoo
 // iteration, 8 gradient rows in flight per warp.  Every CTA leaves its partial sums in a device-resident table and takes a ticket; the CTA that draws the last
 // ticket adds the table up and OVERWRITES dw1 / db1 (no atomics on the outputs, nothing to zero beforehand), then
 // resets the ticket counter for the next launch.
-constexpr int kC1Blocks = 148, kC1Lanes = 16, kC1Fly = 8;
+constexpr int kC1Blocks = 148, kC1Lanes = 16, kC1Fly = 6;
 static __device__ float g_c1w_part[kC1Blocks][320];
 static __device__ unsigned g_c1w_ticket;
 
@@ -132,36 +140,55 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
   __shared__ float red[kC1Lanes][32][11];
   __shared__ float sx[784];
   __shared__ bool last;
-  const int c = threadIdx.x & 31, lane = threadIdx.x >> 5;
-  float acc[10];
+  griddep_launch();
+  griddep_wait();
+  const int c = threadIdx.x & 31, lane = threadIdx.x >> 5;       // c: lane in warp, lane: warp index ("pixel lane")
+  // main loop: a thread owns 4 channels (16-byte loads, 8 threads cover the 32 channels of a pixel) of every 4th
+  // pixel its warp takes; one warp instruction brings 4 pixels, kC1Fly of them are in flight
+  const int c4 = c & 7, sub = c >> 3;
+  float acc[4][10];
 #pragma unroll
-  for (int t = 0; t < 10; ++t) acc[t] = 0.f;
-  // one image at a time: its 28x28 input sits in shared memory (the 9 taps are broadcast reads), warp `lane` takes
-  // output pixels lane, lane + 16, ... of the 26x26 frame with kC1Fly gradient rows in flight
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int t = 0; t < 10; ++t) acc[j][t] = 0.f;
   const int nimg = (int)(total_pixels / P1);
   for (int n = blockIdx.x; n < nimg; n += gridDim.x) {
     __syncthreads();
     for (int i = threadIdx.x; i < 784; i += blockDim.x) sx[i] = x[(long)n * 784 + i];
     __syncthreads();
-    const float* dz = dz1 + (long)n * P1 * 32 + c;
-    for (int q0 = lane; q0 < P1; q0 += kC1Lanes * kC1Fly) {
-      float g[kC1Fly];
+    const float4* dz = reinterpret_cast<const float4*>(dz1 + (long)n * P1 * 32) + c4;
+    for (int q0 = lane * 4 + sub; q0 < P1; q0 += kC1Lanes * 4 * kC1Fly) {
+      float4 g[kC1Fly];
 #pragma unroll
-      for (int u = 0; u < kC1Fly; ++u) { const int q = q0 + u * kC1Lanes; g[u] = q < P1 ? dz[q * 32] : 0.f; }
+      for (int u = 0; u < kC1Fly; ++u) { const int q = q0 + u * kC1Lanes * 4; g[u] = q < P1 ? dz[q * 8] : make_float4(0.f, 0.f, 0.f, 0.f); }
 #pragma unroll
       for (int u = 0; u < kC1Fly; ++u) {
-        const int q = min(q0 + u * kC1Lanes, P1 - 1), h = q / HW1, wq = q % HW1;
+        const int q = min(q0 + u * kC1Lanes * 4, P1 - 1), h = q / HW1, wq = q % HW1;
         const float* xi = sx + h * 28 + wq;
+        const float gv[4] = {g[u].x, g[u].y, g[u].z, g[u].w};
 #pragma unroll
         for (int r = 0; r < 3; ++r)
 #pragma unroll
-          for (int s = 0; s < 3; ++s) acc[r * 3 + s] = fmaf(g[u], xi[r * 28 + s], acc[r * 3 + s]);
-        acc[9] += g[u];
+          for (int s = 0; s < 3; ++s) {
+            const float xv = xi[r * 28 + s];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) acc[j][r * 3 + s] = fmaf(gv[j], xv, acc[j][r * 3 + s]);
+          }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[j][9] += gv[j];
       }
     }
   }
+  // the 4 pixel sub-lanes of the warp hold sums for the same channels: fold them, lanes 0-7 then own channel 4*c4 + j
 #pragma unroll
-  for (int t = 0; t < 10; ++t) red[lane][c][t] = acc[t];
+  for (int j = 0; j < 4; ++j)
+#pragma unroll
+    for (int t = 0; t < 10; ++t) {
+      float v = acc[j][t];
+      v += __shfl_xor_sync(0xffffffffu, v, 8);
+      v += __shfl_xor_sync(0xffffffffu, v, 16);
+      if (sub == 0) red[lane][c4 * 4 + j][t] = v;
+    }
   __syncthreads();
   if (threadIdx.x < 320) {
     const int cc = threadIdx.x / 10, t = threadIdx.x % 10;
@@ -181,7 +208,7 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
   float t10[10];
 #pragma unroll
   for (int k = 0; k < 10; ++k) t10[k] = 0.f;
-#pragma unroll 2
+#pragma unroll 5
   for (int b = lane; b < (int)gridDim.x; b += kC1Lanes) {
     const float* part = &g_c1w_part[b][c];
 #pragma unroll
@@ -207,24 +234,20 @@ extern "C" {
 
 int dcp_convnet_conv1_fwd(const float* x, const float* w, const float* b, float* a1, int N, cudaStream_t s) {
   const long pixels = (long)N * P1;
-  k_conv1_fwd<<<(unsigned)((pixels * 4 + 255) / 256), 256, 0, s>>>(x, w, b, a1, pixels);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_fwd, dim3((unsigned)((pixels * 4 + 255) / 256)), dim3(256), 0, s, x, w, b, a1, pixels)); return 0;
 }
 int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float p, unsigned long long seed, unsigned long long stream,
                          const void* step, int training, cudaStream_t s) {
-  k_pool_fwd<<<dim3(HP, N), 256, 0, s>>>(a2, pooled, (uint8_t*)arg, p, seed, stream, (const long long*)step, training);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_pool_fwd, dim3(HP, N), dim3(256), 0, s, a2, pooled, (uint8_t*)arg, p, seed, stream, (const long long*)step, training)); return 0;
 }
 int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* arg, float* dy2, int N, float p, unsigned long long seed,
                          unsigned long long stream, const void* step, int training, cudaStream_t s) {
-  k_pool_bwd<<<dim3(HP + 1, N), 256, 0, s>>>(dpooled, pooled, (const uint8_t*)arg, dy2, p, seed, stream, (const long long*)step, training);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_pool_bwd, dim3(HP + 1, N), dim3(256), 0, s, dpooled, pooled, (const uint8_t*)arg, dy2, p, seed, stream, (const long long*)step, training)); return 0;
 }
 // dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
 // (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
-  k_conv1_wgrad<<<N < kC1Blocks ? N : kC1Blocks, kC1Lanes * 32, 0, s>>>(dz1, x, dw1, db1, (long)N * P1);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1)); return 0;
 }
 
 }  // extern "C"
@@ -247,11 +270,13 @@ constexpr int HF = 128, HC = 10, HMAXN = 128;
 constexpr int HCL = 8, HFL = HF / HCL;          // cluster size, features per CTA
 constexpr int HT = 512, HRG = HT / HFL, HR = HMAXN / HRG;   // threads, row groups (32), rows per thread (4)
 
-struct HeadSmem {
+struct __align__(16) HeadSmem {
   float xhat[HMAXN][HFL + 1];
   float h3[HMAXN][HFL + 1];
   float w2[HC][HFL];
-  float part[HMAXN][HC];          // this CTA's partial logits (read by the whole cluster)
+  float part[HMAXN][HC];          // this CTA's partial logits (read by the whole cluster); 16-byte aligned offset
+  float logit[HMAXN][HC];         // sum of the 8 partial logits
+  float w2t[HFL][HC + 1];         // w2 slice transposed (conflict-free in the partial-logit loop)
   float dlog[HMAXN][HC + 2];
   float red[HRG / 2][HFL][HC + 1];
   float stat[4][HFL];             // mean, rstd, dbeta/N, dgamma/N
@@ -265,13 +290,23 @@ __device__ __forceinline__ float head_colsum(HeadSmem& S, float v, int slot, int
   return v;
 }
 
+// optional globaltimer trace of CTA 0 / thread 0 (env DCP_HEAD_DBG_PTR, scratch/dbg_head_trace.py)
+__device__ unsigned long long* g_head_dbg = nullptr;
+__device__ __forceinline__ void head_mark(int i) {
+  if (g_head_dbg && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); g_head_dbg[i] = t; }
+}
+
 __global__ void __cluster_dims__(HCL, 1, 1) __launch_bounds__(HT, 1)
 k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ target, const float* __restrict__ gamma, const float* __restrict__ beta,
                float* __restrict__ run_mean, float* __restrict__ run_var, long long* __restrict__ nbt, const float* __restrict__ w2,
                const float* __restrict__ b2, float* __restrict__ loss_out, float* __restrict__ logits_out, float* __restrict__ dh1,
-               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2, float* __restrict__ db2, int N, float eps,
+               float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2, float* __restrict__ db2,
+               float* __restrict__ dbias1, int N, float eps,
                float momentum, float p2, unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training) {
   __shared__ HeadSmem S;
+  griddep_launch();
+  griddep_wait();
+  head_mark(0);
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int tid = threadIdx.x, fl = tid & (HFL - 1), rg = tid >> 4, warp = tid >> 5, lane = tid & 31;
@@ -282,8 +317,15 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
   float s = 0.f;
 #pragma unroll
   for (int i = 0; i < HR; ++i) { const int r = rg + i * HRG; x[i] = r < N ? h1[r * HF + f] : 0.f; s += x[i]; }
+  // every other global operand is fetched now, so that no later phase starts with an exposed memory round trip
+  const float gm = gamma[f], bt = beta[f];
+  const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
+  const int tgt = (tid >> 2) < N ? (int)target[tid >> 2] : -1;
+  float bias2[HC];
+#pragma unroll
+  for (int j = 0; j < HC; ++j) bias2[j] = b2[j];
   head_colsum(S, s, 0, fl, warp);
-  if (tid < HC * HFL) S.w2[tid / HFL][tid % HFL] = w2[(tid / HFL) * HF + f0 + tid % HFL];
+  if (tid < HC * HFL) { const float wv = w2[(tid / HFL) * HF + f0 + tid % HFL]; S.w2[tid / HFL][tid % HFL] = wv; S.w2t[tid % HFL][tid / HFL] = wv; }
   if (tid == 0) S.loss = 0.f;
   __syncthreads();
   if (tid < HFL) { float t = 0.f; for (int g = 0; g < HRG / 2; ++g) t += S.red[g][tid][0]; S.stat[0][tid] = t * invN; }
@@ -306,9 +348,9 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
   }
   if (rank == 0 && tid == 0 && training && nbt) *nbt += 1;
   __syncthreads();
+  head_mark(1);
   // ---- 2. normalise + affine + ReLU + dropout ----
-  const float rstd = S.stat[1][fl], gm = gamma[f], bt = beta[f];
-  const unsigned long long st = stream + (step ? (unsigned long long)(*step) * 0x10000ull : 0ull);
+  const float rstd = S.stat[1][fl];
   const bool drop = training && p2 > 0.f;
   const float dscale = drop ? 1.f / (1.f - p2) : 1.f;
   // one Philox call yields the uniforms of 4 consecutive features of a row: lane q of a feature quad generates row q of
@@ -336,33 +378,41 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     S.h3[r][fl] = h;
   }
   __syncthreads();
-  // ---- 3a. partial logits over this CTA's 16 features ----
-  for (int o = tid; o < HMAXN * HC; o += HT) {
-    const int r = o / HC, j = o % HC;
-    float acc = 0.f;
+  head_mark(2);
+  // ---- 3a. partial logits over this CTA's 16 features: thread (row r, q) computes classes q, q + 4, q + 8 ----
+  {
+    const int r = tid >> 2, q = tid & 3;
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f;
 #pragma unroll
-    for (int q = 0; q < HFL; ++q) acc = fmaf(S.h3[r][q], S.w2[j][q], acc);
-    S.part[r][j] = acc;
+    for (int k = 0; k < HFL; ++k) {
+      const float hv = S.h3[r][k];
+      a0 = fmaf(hv, S.w2t[k][q], a0);
+      a1 = fmaf(hv, S.w2t[k][q + 4], a1);
+      if (q < 2) a2 = fmaf(hv, S.w2t[k][q + 8], a2);
+    }
+    S.part[r][q] = a0; S.part[r][q + 4] = a1;
+    if (q < 2) S.part[r][q + 8] = a2;
   }
+  head_mark(3);
   cluster.sync();
-  // ---- 3b. every CTA: sum the 8 partials (4 threads per row, 2 source CTAs each), log-softmax + nll + dlogits ----
+  head_mark(4);
+  // ---- 3b. every CTA adds up the 8 partial-logit tables with coalesced 16-byte DSMEM loads (one table = 5 KB
+  // contiguous), then 4 threads per row finish log-softmax + nll + dlogits from shared memory ----
+  if (tid < HMAXN * HC / 4) {
+    float4 acc4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+    for (int c = 0; c < HCL; ++c) {
+      const float4 t = reinterpret_cast<const float4*>(cluster.map_shared_rank(&S.part[0][0], c))[tid];
+      acc4.x += t.x; acc4.y += t.y; acc4.z += t.z; acc4.w += t.w;
+    }
+    reinterpret_cast<float4*>(&S.logit[0][0])[tid] = acc4;
+  }
+  __syncthreads();
   {
     const int r = tid >> 2, q = tid & 3;
     float acc[HC];
 #pragma unroll
-    for (int j = 0; j < HC; ++j) acc[j] = 0.f;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      const float2* rp = reinterpret_cast<const float2*>(cluster.map_shared_rank(&S.part[r][0], q * 2 + c));
-#pragma unroll
-      for (int j = 0; j < HC / 2; ++j) { const float2 t = rp[j]; acc[2 * j] += t.x; acc[2 * j + 1] += t.y; }
-    }
-#pragma unroll
-    for (int j = 0; j < HC; ++j) {
-      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 1);
-      acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], 2);
-      acc[j] += b2[j];
-    }
+    for (int j = 0; j < HC; ++j) acc[j] = S.logit[r][j] + bias2[j];
     float m = acc[0];
 #pragma unroll
     for (int j = 1; j < HC; ++j) m = fmaxf(m, acc[j]);
@@ -370,7 +420,7 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
 #pragma unroll
     for (int j = 0; j < HC; ++j) se += __expf(acc[j] - m);
     const float lse = m + __logf(se);
-    const int t = r < N ? (int)target[r] : -1;
+    const int t = tgt;
     // thread q of the row writes columns q, q + 4, q + 8
 #pragma unroll
     for (int j = 0; j < HC; ++j) {
@@ -380,14 +430,16 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
         if (rank == 0 && logits_out && r < N) logits_out[r * HC + j] = acc[j] - lse;   // log-probabilities, as the model's forward returns
       }
     }
-    if (rank == 0 && q == 0 && t >= 0 && t < HC) {
+    if (rank == 0) {                       // mean nll: one shared-memory atomic per warp
       float at = acc[0];
 #pragma unroll
       for (int j = 1; j < HC; ++j) at = j == t ? acc[j] : at;
-      atomicAdd(&S.loss, (lse - at) * invN);
+      const float lv = warp_sum((q == 0 && t >= 0 && t < HC) ? (lse - at) * invN : 0.f);
+      if (lane == 0) atomicAdd(&S.loss, lv);
     }
   }
   __syncthreads();
+  head_mark(5);
   if (rank == 0 && tid == 0) *loss_out = S.loss;
   // ---- 4. fc2 gradients (this CTA's 16 columns of dw2; db2 on CTA 0) ----
   float gw[HC];
@@ -426,7 +478,12 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     for (int w = 0; w < HRG / 2; ++w) t += S.red[w][ff][j];
     dw2[j * HF + f0 + ff] = t;
   }
-  if (rank == 0 && tid >= HT - HC) { const int j = tid - (HT - HC); float t = 0.f; for (int r = 0; r < N; ++r) t += S.dlog[r][j]; db2[j] = t; }
+  if (rank == 0 && warp >= 16 - HC) {    // db2: warp per class, 4 rows per lane (rows >= N hold zeros)
+    const int j = warp - (16 - HC);
+    const float t = warp_sum(S.dlog[lane][j] + S.dlog[lane + 32][j] + S.dlog[lane + 64][j] + S.dlog[lane + 96][j]);
+    if (lane == 0) db2[j] = t;
+  }
+  head_mark(6);
   __syncthreads();                       // S.red is reused
   head_colsum(S, sb, 0, fl, warp);
   head_colsum(S, sg, 1, fl, warp);
@@ -439,26 +496,42 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
   }
   __syncthreads();
   const float k1 = gm * rstd, k2 = S.stat[2][fl], k3 = S.stat[3][fl];
+  float sdh = 0.f;
 #pragma unroll
   for (int i = 0; i < HR; ++i) {
     const int r = rg + i * HRG;
-    if (r < N) dh1[r * HF + f] = k1 * (g[i] - k2 - S.xhat[r][fl] * k3);
+    if (r < N) { const float d = k1 * (g[i] - k2 - S.xhat[r][fl] * k3); dh1[r * HF + f] = d; sdh += d; }
   }
+  if (dbias1) {                          // gradient of the bias of the layer that produced h1 (column sums of dh1)
+    head_colsum(S, sdh, 2, fl, warp);
+    __syncthreads();
+    if (tid < HFL) { float t = 0.f; for (int w = 0; w < HRG / 2; ++w) t += S.red[w][tid][2]; dbias1[f0 + tid] = t; }
+  }
+  head_mark(7);
   cluster.sync();                        // nobody leaves while a peer may still read its partial logits
+  head_mark(8);
 }
 }  // namespace
 
 extern "C" {
-// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null.  All gradient outputs are
+// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null; dbias1 ([128], may be null)
+// receives the column sums of dh1, i.e. the bias gradient of the Linear layer in front.  All gradient outputs are
 // fully overwritten.  Training mode only (batch statistics); p2 = dropout probability of the second dropout.
 int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
                      const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2,
-                     float* db2, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id,
-                     const void* step, int training, cudaStream_t s) {
+                     float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed,
+                     unsigned long long stream_id, const void* step, int training, cudaStream_t s) {
   if (N < 1 || N > HMAXN) { dcp_set_error("convnet head: batch %d not in [1, %d]", N, HMAXN); return -1; }
-  k_convnet_head<<<HCL, HT, 0, s>>>(h1, (const long long*)target, gamma, beta, run_mean, run_var, (long long*)nbt, w2, b2, loss,
-                                    logits_out, dh1, dgamma, dbeta, dw2, db2, N, eps, momentum, p2, seed, stream_id,
-                                    (const long long*)step, training);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  {
+    static bool dbg_set = false;
+    if (!dbg_set) {
+      dbg_set = true;
+      if (const char* e = getenv("DCP_HEAD_DBG_PTR")) { unsigned long long* ptr = (unsigned long long*)strtoull(e, nullptr, 0); DCP_CUDA_CHECK(cudaMemcpyToSymbol(g_head_dbg, &ptr, sizeof ptr)); }
+    }
+  }
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_convnet_head, dim3(HCL), dim3(HT), 0, s, h1, (const long long*)target, gamma, beta, run_mean, run_var,
+                                (long long*)nbt, w2, b2, loss, logits_out, dh1, dgamma, dbeta, dw2, db2, dbias1, N, eps, momentum, p2, seed,
+                                stream_id, (const long long*)step, training));
+  return 0;
 }
 }  // extern "C"

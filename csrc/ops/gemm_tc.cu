@@ -73,6 +73,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int ks0 = blockIdx.z * per, ks1 = min(p.k_stages, ks0 + per);
   const int nst = ks1 - ks0;
 
+  griddep_launch();
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
   if (warp == 1) {
     if (lane == 0) {
@@ -87,6 +88,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *((volatile uint32_t*)&pipe->tmem_base);
+  griddep_wait();                      // prologue done; operands / outputs of earlier kernels are touched from here on
   if (dbg && threadIdx.x == 0) dbg[1] = clock64();
 
   const int m_tile = blockIdx.x, n_tile = blockIdx.y;
@@ -388,8 +390,7 @@ template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUt
   q.stages = kStages;
   while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) --q.stages;
   if (smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }
-  k_tc_gemm<kTF32, kTmemCols><<<grid, kThreads, smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3), s>>>(ma, mb, q);
-  DCP_CUDA_CHECK(cudaGetLastError());
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_tc_gemm<kTF32, kTmemCols>, grid, dim3(kThreads), smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3), s, ma, mb, q));
   return 0;
 }
 
@@ -501,6 +502,8 @@ int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, 
 // Weight repack for the data-gradient: wt[c][(r', s', k)] = w[k][R-1-r'][S-1-s'][c]  (w is [K][R][S][C]).
 namespace {
 template <typename T> __global__ void k_flip_weights(const T* __restrict__ w, T* __restrict__ wt, int K, int R, int S, int C) {
+  griddep_launch();
+  griddep_wait();
   const long total = (long)K * R * S * C;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
     // i indexes wt: ((c * R + r') * S + s') * K + k
@@ -516,6 +519,8 @@ namespace {
 __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__ scratch, float* __restrict__ out, const float* __restrict__ bias,
                                                        int nsplit, long n, int ncols, float* __restrict__ out2, long n1) {
   __shared__ float4 red[8][33];
+  griddep_launch();
+  griddep_wait();
   const int vx = threadIdx.x & 31, zl = threadIdx.x >> 5;
   const long v = (long)blockIdx.x * 32 + vx, n4 = n / 4;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -539,18 +544,18 @@ __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__
 // n and ncols must be multiples of 4.
 extern "C" int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s) {
   if ((n & 3) || (ncols & 3)) { dcp_set_error("splitk reduce: n and ncols must be multiples of 4"); return -1; }
-  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, bias, nsplit, n, ncols, nullptr, n);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_splitk_reduce, dim3((unsigned)((n / 4 + 31) / 32)), dim3(256), 0, s, scratch, out, bias, nsplit, n, ncols, (float*)nullptr, n));
+  return 0;
 }
 // Same reduction with the summed vector going to two places: elements [0, n1) to `out`, [n1, n) to `out2` (n1 % 4 == 0).
 extern "C" int dcp_splitk_reduce2(const float* scratch, float* out, float* out2, long n1, int nsplit, long n, cudaStream_t s) {
   if ((n & 3) || (n1 & 3) || n1 > n) { dcp_set_error("splitk reduce2: n and n1 must be multiples of 4, n1 <= n"); return -1; }
-  k_splitk_reduce<<<(unsigned)((n / 4 + 31) / 32), 256, 0, s>>>(scratch, out, nullptr, nsplit, n, 4, out2, n1);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_splitk_reduce, dim3((unsigned)((n / 4 + 31) / 32)), dim3(256), 0, s, scratch, out, (const float*)nullptr, nsplit, n, 4, out2, n1));
+  return 0;
 }
 
 extern "C" int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s) {
   long total = (long)K * R * S * C;
-  DISPATCH_ACT(dtype, (k_flip_weights<T><<<grid_1d(total, 256), 256, 0, s>>>((const T*)w, (T*)wt, K, R, S, C)));
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DISPATCH_ACT(dtype, DCP_CUDA_CHECK(dcp_launch_pdl(k_flip_weights<T>, dim3(grid_1d(total, 256)), dim3(256), 0, s, (const T*)w, (T*)wt, K, R, S, C)));
+  return 0;
 }

@@ -22,6 +22,8 @@ __device__ __forceinline__ void unpack4(const uint2& v, float* o) {
 
 template <int KIND, typename G>
 __global__ void __launch_bounds__(kT) k_opt(const DcpOptEntry* __restrict__ table, const float* __restrict__ hp) {
+  griddep_launch();
+  griddep_wait();
   const DcpOptEntry e = table[blockIdx.y];
   const float step = hp[6], gs = hp[7];
   const G* g = static_cast<const G*>(e.g);
@@ -52,14 +54,13 @@ __global__ void __launch_bounds__(kT) k_opt(const DcpOptEntry* __restrict__ tabl
     if (e.s2) e.s2[i] = s2;
   }
 }
-__global__ void k_opt_advance(float* hp) { hp[6] += 1.f; }
+__global__ void k_opt_advance(float* hp) { griddep_launch(); griddep_wait(); hp[6] += 1.f; }
 }  // namespace
 
 extern "C" {
 // Advance the device step counter (call once per optimizer.step(), before dcp_optim_step).
 int dcp_optim_advance(float* hp, cudaStream_t s) {
-  k_opt_advance<<<1, 1, 0, s>>>(hp);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_opt_advance, dim3(1), dim3(1), 0, s, hp)); return 0;
 }
 // kind: 0 Adadelta, 1 SGD, 2 Adam.  grad_dtype: DCP_F32 or DCP_BF16.  max_numel sizes the grid.
 int dcp_optim_step(const void* table, int ntensors, long long max_numel, const float* hp, int kind, int grad_dtype, cudaStream_t s) {
@@ -67,7 +68,7 @@ int dcp_optim_step(const void* table, int ntensors, long long max_numel, const f
   int gx = (int)((max_numel + kT * 4 - 1) / (kT * 4)); if (gx < 1) gx = 1; if (gx > 296) gx = 296;
   dim3 grid(gx, ntensors);
   const DcpOptEntry* t = static_cast<const DcpOptEntry*>(table);
-#define LAUNCH(K, G) k_opt<K, G><<<grid, kT, 0, s>>>(t, hp)
+#define LAUNCH(K, G) DCP_CUDA_CHECK(dcp_launch_pdl(k_opt<K, G>, grid, dim3(kT), 0, s, t, hp))
   if (grad_dtype == DCP_F32) { if (kind == 0) LAUNCH(0, float); else if (kind == 1) LAUNCH(1, float); else LAUNCH(2, float); }
   else if (grad_dtype == DCP_BF16) { if (kind == 0) LAUNCH(0, __nv_bfloat16); else if (kind == 1) LAUNCH(1, __nv_bfloat16); else LAUNCH(2, __nv_bfloat16); }
   else { dcp_set_error("optimizer gradients must be f32 or bf16"); return -1; }
@@ -77,8 +78,7 @@ int dcp_optim_step(const void* table, int ntensors, long long max_numel, const f
 }  // extern "C"
 
 // int64 device counter += 1 (the per-step counter that dropout streams hang off inside a CUDA graph)
-namespace { __global__ void k_counter_advance(long long* c) { *c += 1; } }
+namespace { __global__ void k_counter_advance(long long* c) { griddep_launch(); griddep_wait(); *c += 1; } }
 extern "C" int dcp_counter_advance(void* counter, cudaStream_t s) {
-  k_counter_advance<<<1, 1, 0, s>>>((long long*)counter);
-  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_counter_advance, dim3(1), dim3(1), 0, s, (long long*)counter)); return 0;
 }

@@ -25,6 +25,13 @@ void dcp_set_error(const char* fmt, ...) {
   va_list ap; va_start(ap, fmt); vsnprintf(g_err, sizeof g_err, fmt, ap); va_end(ap);
 }
 
+// DCP_PDL=0 turns programmatic dependent launch off (plain stream order); read once.
+bool dcp_pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DCP_PDL"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
+
 namespace {
 
 struct Drv {

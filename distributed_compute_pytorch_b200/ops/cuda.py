@@ -67,7 +67,7 @@ def lib():
             "dcp_convnet_pool_fwd": [vp, vp, vp, i, f, ull, ull, vp, i, vp],
             "dcp_convnet_pool_bwd": [vp, vp, vp, vp, i, f, ull, ull, vp, i, vp],
             "dcp_convnet_conv1_wgrad": [vp, vp, vp, vp, i, vp],
-            "dcp_convnet_head": [vp] * 16 + [i, f, f, f, ull, ull, vp, i, vp],
+            "dcp_convnet_head": [vp] * 17 + [i, f, f, f, ull, ull, vp, i, vp],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)

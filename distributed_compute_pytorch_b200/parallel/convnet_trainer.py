@@ -117,16 +117,16 @@ class FusedConvNetTrainer:
         tc.linear_fwd(self.pooled, p["fc1.weight"], p["fc1.bias"], self.h1, False)
         bn = net.batchnorm
         if N <= 128 and self.fused_head:
-            # BatchNorm + ReLU + dropout + fc2 + log_softmax/nll and ALL of their gradients: one single-CTA kernel
+            # BatchNorm + ReLU + dropout + fc2 + log_softmax/nll and ALL of their gradients (+ fc1's bias gradient): one 8-CTA cluster
             ck(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
                                   bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
                                   self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
-                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), N, bn.eps, bn.momentum,
-                                  net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, tr, s()))
+                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), g["fc1.bias"].data_ptr(),
+                                  N, bn.eps, bn.momentum, net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, tr, s()))
         else:
             self._head_unfused(L, ck, s, p, g, bn, N, tr, step_ptr)
+            ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
         tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
-        ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
         ev0 = self._reduce_bucket(0)
         tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
         # ---- backward: convolutional trunk
@@ -179,8 +179,8 @@ class FusedConvNetTrainer:
         K._chk(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
                                   bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
                                   self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
-                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), N, bn.eps, bn.momentum,
-                                  net.dropout2.p, self.seed, 2, K.graph_step.data_ptr(), 1, K._stream()))
+                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), g["fc1.bias"].data_ptr(),
+                                  N, bn.eps, bn.momentum, net.dropout2.p, self.seed, 2, K.graph_step.data_ptr(), 1, K._stream()))
 
     def _reduce_bucket(self, idx: int):
         if self.be is None or idx >= len(self.buckets):

@@ -124,15 +124,24 @@ int dcp_linear_wgrad_simt(const void* dy, const void* x, float* dw32, float* db3
 int dcp_colsum(const void* x, float* out, long M, int C, int dtype, cudaStream_t s);
 int dcp_cast_from_f32(const float* in, void* out, long n, int dtype, cudaStream_t s);
 
+/* ---- csrc/ops/conv_wgrad_flat_tc.cu ---- */
+// x: [P, 32] fp32 flat pixels (pitch W); dy: [P, Cout] fp32 in the same frame; scratch: [num_ctas][Cout*288 + Cout] fp32 partial
+// filters followed by partial bias gradients (finish with dcp_splitk_reduce2(scratch, dw, db, Cout*288, num_ctas, Cout*289)).
+// 3x3 filters, Cin = 32.
+// Exactly num_ctas partials are written (CTAs without pixels write zeros).
+int dcp_conv_wgrad_flat_tc(const float* x, const float* dy, float* scratch, long P, int Cout, int W, int num_ctas, cudaStream_t s);
+
 /* ---- csrc/ops/convnet_fused.cu ---- */
 int dcp_convnet_conv1_fwd(const float* x, const float* w, const float* b, float* a1, int N, cudaStream_t s);
 int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
 int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* arg, float* dy2, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
-// dw1 / db1 are accumulated into: the caller zeroes them (they normally live in the gradient bucket).
+// dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
+// (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s);
-// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null.  All gradient outputs are
+// Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null; dbias1 ([128], may be null)
+// receives the column sums of dh1, i.e. the bias gradient of the Linear layer in front.  All gradient outputs are
 // fully overwritten.  Training mode only (batch statistics); p2 = dropout probability of the second dropout.
-int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
+int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
 
 /* ---- csrc/ops/elementwise.cu ---- */
 int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
@@ -161,6 +170,8 @@ int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int 
 int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
 // n and ncols must be multiples of 4.
 int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s);
+// Same reduction with the summed vector going to two places: elements [0, n1) to `out`, [n1, n) to `out2` (n1 % 4 == 0).
+int dcp_splitk_reduce2(const float* scratch, float* out, float* out2, long n1, int nsplit, long n, cudaStream_t s);
 int dcp_flip_weights(const void* w, void* wt, int K, int R, int S, int C, int dtype, cudaStream_t s);
 
 /* ---- csrc/ops/loss.cu ---- */

@@ -116,3 +116,5 @@ def test_fused_head_kernel_matches_kernel_per_op_head():
     for n in g0:
         if n != "fc1.bias":
             assert _relerr(g0[n], g1[n]) < 2e-3, (n, _relerr(g0[n], g1[n]))
+    # fc1.bias feeds a BatchNorm: its exact gradient is 0, both paths leave rounding noise only
+    assert g0["fc1.bias"].abs().max().item() < 1e-4 and g1["fc1.bias"].abs().max().item() < 1e-4
