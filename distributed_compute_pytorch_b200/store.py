@@ -176,5 +176,45 @@ def rendezvous(init_method: Optional[str], rank: int, world_size: int, timeout: 
         raise ValueError(f"unsupported init_method {init_method!r} (use env:// or tcp://host:port)")
     if host == "localhost":
         host = "127.0.0.1"
+    if init_method.startswith("env://") and os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "").lower() == "true":
+        return _rendezvous_behind_agent(host, port, rank, world_size, timeout), rank, world_size
     store = TCPStore(host, port, world_size, is_master=(rank == 0), timeout=timeout)
     return store, rank, world_size
+
+
+_agent_inits = 0
+
+
+def _free_port(host: str) -> int:
+    import socket
+    with socket.socket() as s:
+        s.bind((host, 0))
+        return s.getsockname()[1]
+
+
+def _rendezvous_behind_agent(host: str, port: int, rank: int, world_size: int, timeout: float) -> "TCPStore":
+    """``torchrun --master-addr A --master-port P`` (static rendezvous) keeps ITS OWN store listening on P and tells the
+    workers so with TORCHELASTIC_USE_AGENT_STORE=True: MASTER_PORT is taken.  Rank 0 then opens this package's store on
+    a free port and publishes the number through the launcher's store (the one piece of torch.distributed plumbing
+    used here); the other ranks read it there."""
+    global _agent_inits
+    from datetime import timedelta
+
+    from torch.distributed import TCPStore as _LauncherStore
+    agent = _LauncherStore(host, port, world_size, False, timedelta(seconds=timeout), wait_for_workers=False)
+    key = "dcp_b200/store_port/%s/%d" % (os.environ.get("TORCHELASTIC_RESTART_COUNT", "0"), _agent_inits)
+    _agent_inits += 1
+    if rank == 0:
+        last = None
+        for _ in range(16):                       # another process may grab the port between the probe and the listen
+            own = _free_port(host)
+            try:
+                store = TCPStore(host, own, world_size, is_master=True, timeout=timeout)
+            except RuntimeError as e:
+                last = e
+                continue
+            agent.set(key, str(own))
+            return store
+        raise RuntimeError(f"rendezvous behind the launcher's store failed: {last}")
+    own = int(agent.get(key).decode())
+    return TCPStore(host, own, world_size, is_master=False, timeout=timeout)
