@@ -104,7 +104,11 @@ def run_ours(opt, rank, local_rank, world):
         per_step = step.launches_per_step
 
     def timed(pool_x, pool_y, nsteps, read_loss):
-        loss_host = torch.zeros((), dtype=torch.float32).pin_memory()
+        # end-to-end mode: every step's loss is copied to pinned host memory and READ on the host inside the timed
+        # region; the read of step i-1 happens after step i has been enqueued (two slots + events), the way a training
+        # loop logs without draining the GPU every step
+        loss_host = torch.zeros(2, dtype=torch.float32).pin_memory()
+        done = [torch.cuda.Event(), torch.cuda.Event()]
         start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         dcp.barrier(); torch.cuda.synchronize()
         l0 = K.launch_count + be.launches
@@ -114,9 +118,14 @@ def run_ours(opt, rank, local_rank, world):
         for i in range(nsteps):
             loss = step(pool_x[i % POOL_BATCHES], pool_y[i % POOL_BATCHES])
             if read_loss:
-                loss_host.copy_(loss, non_blocking=True)
-                torch.cuda.current_stream().synchronize()
-                last = float(loss_host)
+                loss_host[i & 1].copy_(loss, non_blocking=True)
+                done[i & 1].record()
+                if i > 0:
+                    done[(i - 1) & 1].synchronize()
+                    last = float(loss_host[(i - 1) & 1])
+        if read_loss and nsteps > 0:
+            done[(nsteps - 1) & 1].synchronize()
+            last = float(loss_host[(nsteps - 1) & 1])
         end.record()
         dcp.barrier(); torch.cuda.synchronize()
         wall = time.perf_counter() - t0

@@ -603,6 +603,28 @@ def gelu(x):
 
 
 # -------------------------------------------------------------------------------------- optimizer --
+def _push_hyper(opt, group: dict, ent: dict) -> None:
+    hyper = opt._hyper(group)
+    if ent["hyper"] != hyper:
+        vals = (hyper + [0.0] * 6)[:6]
+        ent["hp"][:6].copy_(torch.tensor(vals, dtype=torch.float32), non_blocking=False)
+        ent["hp"][7] = 1.0
+        ent["hyper"] = list(hyper)
+
+
+def sync_optimizer_hyper(opt) -> None:
+    """Bring the device-resident hyper-parameter blocks in line with ``opt.param_groups`` (e.g. after ``StepLR.step()``).
+    The captured training graphs call this before every replay: the kernels inside read lr & co. from device memory, so
+    a changed learning rate takes effect without re-capturing.  A no-op (a Python list compare) when nothing changed."""
+    cache = opt.__dict__.get("_dcp_cache")
+    if not cache:
+        return
+    for gi, group in enumerate(opt.param_groups):
+        ent = cache.get(gi)
+        if ent is not None and ent["hyper"] is not None and ent["hyper"] != opt._hyper(group):
+            _push_hyper(opt, group, ent)
+
+
 def fused_optimizer_step(opt, gi: int, group: dict, items: List[Tuple[torch.Tensor, torch.Tensor, dict]]) -> None:
     """One multi-tensor launch for ``items`` = [(param, grad, state)].  The pointer table and the
     hyper-parameter block live on the device and are rebuilt only when pointers / values change."""
@@ -641,11 +663,6 @@ def fused_optimizer_step(opt, gi: int, group: dict, items: List[Tuple[torch.Tens
         ent = {"key": key, "table": table, "host": host, "hp": hp, "hyper": ent["hyper"] if ent else None, "n": len(items),
                "max": max(p.numel() for p, _, _ in items)}
         cache[gi] = ent
-    hyper = opt._hyper(group)
-    if ent["hyper"] != hyper:
-        vals = (hyper + [0.0] * 6)[:6]
-        ent["hp"][:6].copy_(torch.tensor(vals, dtype=torch.float32), non_blocking=False)
-        ent["hp"][7] = 1.0
-        ent["hyper"] = list(hyper)
+    _push_hyper(opt, group, ent)
     _chk(lib().dcp_optim_advance(ent["hp"].data_ptr(), _stream()))
     _chk(lib().dcp_optim_step(ent["table"].data_ptr(), ent["n"], ent["max"], ent["hp"].data_ptr(), opt._kind, _DT[gdt], _stream()))

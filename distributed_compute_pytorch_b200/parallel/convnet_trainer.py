@@ -94,8 +94,11 @@ class FusedConvNetTrainer:
         self.training = True
         self.fused_head = True
         self.comm_ctas = 16
+        self.split_opt = os.environ.get("DCP_SPLIT_OPT", "1") == "1"
+        self.side = self.be.comm_stream if self.be is not None else torch.cuda.Stream(device=dev)
         self.launches_per_step = 0
         self.graph = None
+        self._copy_stream = None
         if use_graph:
             self._capture()
 
@@ -129,6 +132,18 @@ class FusedConvNetTrainer:
         tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
         ev0 = self._reduce_bucket(0)
         tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+        # fc1.weight has been read for the last time: the optimizer update of everything in bucket 0 (97 % of the
+        # parameters) runs on the side stream, behind that bucket's all-reduce, underneath the convolution backward
+        rows = self._opt_rows() if self.split_opt else None
+        ev_opt0 = None
+        if rows is not None:
+            ent, (r0, n0, m0), _ = rows
+            K._push_hyper(self.opt, self.opt.param_groups[0], ent)
+            ck(L.dcp_optim_advance(ent["hp"].data_ptr(), s()))
+            main = torch.cuda.current_stream(self.dev)
+            self.side.wait_stream(main)
+            ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, self.side.cuda_stream))
+            ev_opt0 = torch.cuda.Event(); ev_opt0.record(self.side)
         # ---- backward: convolutional trunk
         ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
                                   self.seed, 1, step_ptr, tr, s()))
@@ -144,11 +159,34 @@ class FusedConvNetTrainer:
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
         ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
         ev1 = self._reduce_bucket(1)
-        for ev in (ev0, ev1):
+        for ev in (ev0, ev1, ev_opt0):
             if ev is not None:
                 torch.cuda.current_stream(self.dev).wait_event(ev)
-        self.opt.step()
+        if rows is not None:
+            ent, _, (r1, n1, m1) = rows
+            ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r1, n1, m1, ent["hp"].data_ptr(), self.opt._kind, 0, s()))
+        else:
+            self.opt.step()
 
+
+    def _opt_rows(self):
+        """(cache entry, (first row, rows) of bucket 0, (first row, rows) of bucket 1) in the optimizer's device pointer
+        table, or None when the table does not exist yet (first step) or the parameters of a bucket are not adjacent rows."""
+        opt = self.opt
+        cache = opt.__dict__.get("_dcp_cache")
+        if not cache or len(opt.param_groups) != 1 or 0 not in cache or not hasattr(opt, "_kind"):
+            return None
+        names = dict(self.net.named_parameters())
+        params = [q for q in opt.param_groups[0]["params"] if q.grad is not None]
+        ent = cache[0]
+        if ent["n"] != len(params) or any(q.grad.dtype != torch.float32 for q in params):
+            return None
+        b0 = {id(names[n]) for n in READY_ORDER[:6]}
+        i0 = [i for i, q in enumerate(params) if id(q) in b0]
+        i1 = [i for i, q in enumerate(params) if id(q) not in b0]
+        if not i0 or not i1 or i0 != list(range(i0[0], i0[0] + len(i0))) or i1 != list(range(i1[0], i1[0] + len(i1))):
+            return None
+        return ent, (i0[0], len(i0), max(params[i].numel() for i in i0)), (i1[0], len(i1), max(params[i].numel() for i in i1))
 
     def _head_unfused(self, L, ck, s, p, g, bn, N, tr, step_ptr) -> None:
         """Kernel-per-op version of the head (any batch size); numerically the same as dcp_convnet_head."""
@@ -205,12 +243,43 @@ class FusedConvNetTrainer:
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """One optimisation step on batch (x, y); returns the (device, static) mean NLL loss of the batch."""
-        self.x.copy_(x.view(self.N, 1, 28, 28), non_blocking=True)
-        self.y.copy_(y, non_blocking=True)
+        if x.is_cuda:
+            self.x.copy_(x.view(self.N, 1, 28, 28), non_blocking=True)
+            self.y.copy_(y, non_blocking=True)
+        else:
+            self._stage_from_host(x, y)
         if self.graph is not None:
+            if hasattr(self.opt, "_hyper"):
+                K.sync_optimizer_hyper(self.opt)     # StepLR between replays: the captured kernels read lr from device memory
             self.graph.replay()
         else:
             self._issue()
         return self.loss
 
     __call__ = step
+
+    def _stage_from_host(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        """Host batches go through two device staging slots filled on a copy stream: the (PCIe-speed) host->device copy
+        of this step runs while the previous step is still computing; the compute stream only does a device-to-device
+        copy into the buffers the captured graph reads.  Pass pinned tensors to make the copies asynchronous."""
+        if self._copy_stream is None:
+            f32 = dict(dtype=torch.float32, device=self.dev)
+            self._copy_stream = torch.cuda.Stream(device=self.dev)
+            self._xs = [torch.empty(self.N, 1, 28, 28, **f32) for _ in range(2)]
+            self._ys = [torch.empty(self.N, dtype=torch.int64, device=self.dev) for _ in range(2)]
+            self._ready = [torch.cuda.Event() for _ in range(2)]
+            self._free = [torch.cuda.Event() for _ in range(2)]
+            self._slot = 0
+        k = self._slot
+        self._slot ^= 1
+        main = torch.cuda.current_stream(self.dev)
+        cs = self._copy_stream
+        cs.wait_event(self._free[k])              # the step that last used this slot has taken its copy
+        with torch.cuda.stream(cs):
+            self._xs[k].copy_(x.view(self.N, 1, 28, 28), non_blocking=True)
+            self._ys[k].copy_(y, non_blocking=True)
+            self._ready[k].record(cs)
+        main.wait_event(self._ready[k])
+        self.x.copy_(self._xs[k], non_blocking=True)
+        self.y.copy_(self._ys[k], non_blocking=True)
+        self._free[k].record(main)

@@ -67,5 +67,7 @@ class GraphedTrainStep:
     def __call__(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self.x.copy_(x, non_blocking=True)
         self.y.copy_(y, non_blocking=True)
+        if hasattr(self.optimizer, "_hyper"):
+            K.sync_optimizer_hyper(self.optimizer)     # StepLR between replays: lr lives in device memory
         self.graph.replay()
         return self.loss

@@ -118,3 +118,35 @@ def test_fused_head_kernel_matches_kernel_per_op_head():
             assert _relerr(g0[n], g1[n]) < 2e-3, (n, _relerr(g0[n], g1[n]))
     # fc1.bias feeds a BatchNorm: its exact gradient is 0, both paths leave rounding noise only
     assert g0["fc1.bias"].abs().max().item() < 1e-4 and g1["fc1.bias"].abs().max().item() < 1e-4
+
+
+def test_split_optimizer_and_steplr_across_graph_replays():
+    """The captured step updates bucket 0 on the side stream and bucket 1 at the end (two launches over slices of the
+    optimizer's pointer table) and reads lr from device memory.  Against the eager, single-launch optimizer path, with
+    StepLR changing the learning rate between steps, the parameters must agree to rounding."""
+    N = 128
+    g = torch.Generator().manual_seed(5)
+    xs = torch.randn(4, N, 1, 28, 28, generator=g).to(DEV); ys = torch.randint(0, 10, (4, N), generator=g).to(DEV)
+    results = []
+    for graph in (False, True):
+        net = _make().to(DEV).train()
+        opt = ops.Adadelta(net.parameters(), lr=1.0)
+        sched = ops.StepLR(opt, step_size=1, gamma=0.5)
+        tr = FusedConvNetTrainer(net, opt, N, use_graph=False)
+        tr.split_opt = graph
+        if graph:
+            state = copy.deepcopy(net.state_dict())
+            tr._capture()
+            net.load_state_dict(state)
+            for st in opt.state.values():
+                for v in st.values():
+                    if torch.is_tensor(v): v.zero_()
+            opt._dcp_cache[0]["hp"][6] = 0.0
+            assert tr._opt_rows() is not None
+        for i in range(4):
+            tr.step(xs[i], ys[i])
+            sched.step()
+        torch.cuda.synchronize()
+        results.append({n: p.detach().clone() for n, p in net.named_parameters()})
+    for n in results[0]:
+        assert _relerr(results[1][n], results[0][n]) < 1e-5, (n, _relerr(results[1][n], results[0][n]))
