@@ -96,19 +96,26 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   const int my_tiles = (p.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
-  if (warp == 0 && lane == 0) {
-    // ---- producer: weights once, then one haloed tile per stage ----
-    mbar_expect_tx(&bars->w_full, w_bytes);
-    for (int t = 0; t < p.taps; ++t)
-      for (int cc = 0; cc < cch; ++cc)
-        tma_load_2d(w_smem + (t * cch + cc) * (p.Cout * 128), &map_w, &bars->w_full, t * p.Cin + cc * 32, 0);
+  if (warp == 0) {
+    // ---- producer: weights once, then one haloed tile per stage.  The whole warp walks the loop and stays converged
+    //      (it reaches the closing __syncthreads as one); lane 0 issues.
+    if (lane == 0) {
+      mbar_expect_tx(&bars->w_full, w_bytes);
+      for (int t = 0; t < p.taps; ++t)
+        for (int cc = 0; cc < cch; ++cc)
+          tma_load_2d(w_smem + (t * cch + cc) * (p.Cout * 128), &map_w, &bars->w_full, t * p.Cin + cc * 32, 0);
+    }
+    __syncwarp();
     for (int i = 0; i < my_tiles; ++i) {
       const int st = i % stages, ph = (i / stages) & 1;
       const long p0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM;
       mbar_wait(&bars->empty[st], ph ^ 1);
-      mbar_expect_tx(&bars->full[st], stage_bytes);
-      for (int cc = 0; cc < cch; ++cc)
-        tma_load_2d(a_smem + st * stage_bytes + cc * chunk_bytes, &map_in, &bars->full[st], cc * 32, (int)(p0 + p.min_off));
+      if (lane == 0) {
+        mbar_expect_tx(&bars->full[st], stage_bytes);
+        for (int cc = 0; cc < cch; ++cc)
+          tma_load_2d(a_smem + st * stage_bytes + cc * chunk_bytes, &map_in, &bars->full[st], cc * 32, (int)(p0 + p.min_off));
+      }
+      __syncwarp();
     }
   } else if (warp == 1 || warp >= 10) {
     // ---- two MMA issuers (the single-thread issue rate, ~120 cycles per 128x64x8 instruction, is what bounds this

@@ -69,15 +69,19 @@ k_wgrad_flat(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ 
   const int s0 = blockIdx.x * per, s1 = min(p.stages_total, s0 + per);
   const int n = max(0, s1 - s0);
 
-  if (warp == 0 && lane == 0) {
+  if (warp == 0) {
+    // producer: the whole warp walks the loop (stays converged up to the closing __syncthreads), lane 0 issues
     for (int i = 0; i < n; ++i) {
       const int st = i % nstages, ph = (i / nstages) & 1;
       const int row0 = (s0 + i) * kBK;
       uint8_t* sx = smem + st * stage_bytes;
       mbar_wait(&bars->empty[st], ph ^ 1);
-      mbar_expect_tx(&bars->full[st], stage_bytes);
-      tma_load_2d(sx, &map_x, &bars->full[st], 0, row0);
-      for (int j = 0; j < dy_chunks; ++j) tma_load_2d(sx + x_bytes + j * (kBK * 128), &map_dy, &bars->full[st], j * 32, row0);
+      if (lane == 0) {
+        mbar_expect_tx(&bars->full[st], stage_bytes);
+        tma_load_2d(sx, &map_x, &bars->full[st], 0, row0);
+        for (int j = 0; j < dy_chunks; ++j) tma_load_2d(sx + x_bytes + j * (kBK * 128), &map_dy, &bars->full[st], j * 32, row0);
+      }
+      __syncwarp();
     }
   } else if (warp >= 1 && warp <= 3) {
     // issuer for filter row r: A = x tile shifted by r*W rows, M-chunks one row apart; B = dy tile

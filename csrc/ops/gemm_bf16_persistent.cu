@@ -1,0 +1,269 @@
+// Persistent bf16 GEMM for sm_100a - the Linear layers of the transformer / ResNet configurations (forward, data-gradient and
+// weight-gradient through the operand-major flags, K8 / K12 of the reference model generalised; ref:main.py:39,43).
+//
+//   C[M,N] = op(A) . op(B)^T   fp32 accumulation in TMEM, output bf16 or fp32, optional bias + ReLU
+//
+// Why a second GEMM kernel next to gemm_tc.cu: that one launches one CTA per 128 x 128 tile and drains the accumulator
+// after the main loop - prologue, epilogue and main loop are serial, and with N = 128 every tcgen05.mma is worth ~64 tensor
+// cycles while one thread can issue one only every ~128 cycles.  Here
+//   * the tile is 128 x 256 (one MMA = 128 x 256 x 16 = 128 tensor cycles: the issue rate and the tensor pipe balance),
+//   * ONE CTA per SM walks the tile list (persistent): barrier init, TMEM allocation and descriptor prefetch happen once,
+//   * the accumulator is double buffered in TMEM (2 x 256 columns): eight epilogue warps drain tile i (tcgen05.ld ->
+//     bias / ReLU / cast -> shared-memory transpose -> coalesced stores) while the MMA warp already runs tile i + 1,
+//   * a 4-stage TMA pipeline of 48 KB stages (A 128 x 64, B 256 x 64 bf16, 128-byte swizzle) feeds it,
+//   * split-K work units (tile, k-slice) write fp32 partial tiles for dcp_splitk_reduce when a problem has too few tiles.
+// Warp roles: 0 = TMA producer, 1 = MMA issuer (+ TMEM allocator), 2..9 = epilogue (lane group = warp % 4, column half = (warp-2)/4).
+#include <cstdlib>
+
+#include "ops/tc_common.cuh"
+
+struct BfGemmParams {
+  int M, N;
+  int k_stages;             // K / 64
+  int BN;                   // 128 or 256
+  int a_mn, b_mn;           // operand majors (0: K-major [rows][K]; 1: MN-major [K][rows])
+  int tiles_m, tiles_n, ksplit;
+  int stages;               // pipeline depth
+  void* out; long ldc; int out_bf16;
+  const void* bias; int bias_bf16; int relu;
+  long partial_stride;      // ksplit > 1: slice z writes fp32 to out + z * partial_stride
+};
+
+namespace {
+using namespace tc;
+#ifdef DCP_DEBUG_MBAR
+__device__ volatile int* g_pg_dbg = nullptr;
+#define PG_MARK(slot, v) do { if (g_pg_dbg && blockIdx.x == 0 && (threadIdx.x & 31) == 0) { g_pg_dbg[(threadIdx.x >> 5) * 4 + (slot)] = (v); __threadfence_system(); } } while (0)
+#else
+#define PG_MARK(slot, v) do {} while (0)
+#endif
+
+constexpr int kBM = 128, kBK = 64, kMaxStages = 6;
+constexpr int kThreads = 320, kEpiWarps = 8;
+constexpr int kABytes = kBM * 128;                       // 16 KB
+constexpr int kStgPitch = 20;                            // floats per staged row (16 columns + pad: conflict-free 16-byte accesses)
+constexpr int kStgBytes = kEpiWarps * 32 * kStgPitch * 4;
+
+struct __align__(8) PPipe {
+  uint64_t full[kMaxStages], empty[kMaxStages], acc_full[2], acc_empty[2];
+  uint32_t tmem_base;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const BfGemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = align_smem_1024(smem_raw);
+  const int b_bytes = p.BN * 128, stage_bytes = kABytes + b_bytes, nstages = p.stages;
+  float* stg_all = reinterpret_cast<float*>(smem + nstages * stage_bytes);
+  PPipe* pipe = reinterpret_cast<PPipe*>(smem + nstages * stage_bytes + kStgBytes);
+  const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
+
+  PG_MARK(0, 1);
+  griddep_launch();
+  if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
+  if (warp == 1) {
+    if (lane == 0) {
+      for (int i = 0; i < kMaxStages; ++i) { mbar_init(&pipe->full[i], 1); mbar_init(&pipe->empty[i], 1); }
+      for (int i = 0; i < 2; ++i) { mbar_init(&pipe->acc_full[i], 1); mbar_init(&pipe->acc_empty[i], kEpiWarps); }
+      mbar_fence_init();
+    }
+    __syncwarp();
+    PG_MARK(0, 2);
+    tmem_alloc<512>(&pipe->tmem_base);
+    PG_MARK(0, 3);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  PG_MARK(0, 4);
+  const uint32_t tmem = *((volatile uint32_t*)&pipe->tmem_base);
+  griddep_wait();
+  PG_MARK(0, 5);
+
+  // work units: u -> (tile, k-slice); tiles run M-fastest so that one wave of CTAs shares a few B tiles
+  const int tiles = p.tiles_m * p.tiles_n, units = tiles * p.ksplit;
+  const int kper = (p.k_stages + p.ksplit - 1) / p.ksplit;
+
+  if (warp == 0) {
+    // ================= TMA producer (the whole warp walks the loop, one lane issues: the warp stays converged and
+    // reaches the closing __syncthreads as one) =================
+    int it = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x) {
+      const int z = u / tiles, t = u % tiles, m_tile = t % p.tiles_m, n_tile = t / p.tiles_m;
+      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      for (int ks = ks0; ks < ks1; ++ks, ++it) {
+        const int st = it % nstages, ph = (it / nstages) & 1;
+        mbar_wait(&pipe->empty[st], ph ^ 1);
+        if (lane == 0) {
+          uint8_t* sa = smem + st * stage_bytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_expect_tx(&pipe->full[st], stage_bytes);
+          const int kb = ks * kBK;
+          if (!p.a_mn) tma_load_2d(sa, &map_a, &pipe->full[st], kb, m_tile * kBM);
+          else
+            for (int j = 0; j < kBM / 64; ++j) tma_load_2d(sa + j * (kBK * 128), &map_a, &pipe->full[st], m_tile * kBM + j * 64, kb);
+          if (!p.b_mn) tma_load_2d(sb, &map_b, &pipe->full[st], kb, n_tile * p.BN);
+          else
+            for (int j = 0; j < p.BN / 64; ++j) tma_load_2d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * 64, kb);
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    const uint32_t idesc = make_idesc(false, p.a_mn != 0, p.b_mn != 0, kBM, p.BN);
+    const uint64_t step_a = p.a_mn ? (uint64_t)((16 * 128) >> 4) : 2u, step_b = p.b_mn ? (uint64_t)((16 * 128) >> 4) : 2u;
+    int it = 0, tcount = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++tcount) {
+      const int z = u / tiles;
+      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      const int ab = tcount & 1, aph = (tcount >> 1) & 1;
+      mbar_wait(&pipe->acc_empty[ab], aph ^ 1);            // epilogue has drained this accumulator buffer
+      tc_fence_after();
+      const uint32_t tacc = tmem + ab * 256;
+      for (int ks = ks0; ks < ks1; ++ks, ++it) {
+        const int st = it % nstages, ph = (it / nstages) & 1;
+        PG_MARK(1, 100 + it);
+        mbar_wait(&pipe->full[st], ph);
+        tc_fence_after();
+        PG_MARK(1, 200 + it);
+        const uint32_t sa = smem_u32(smem + st * stage_bytes), sb = sa + kABytes;
+        if (elect_one()) {
+          const uint64_t da0 = p.a_mn ? make_smem_desc(sa, kBK * 128, 1024) : make_smem_desc(sa, 0, 1024);
+          const uint64_t db0 = p.b_mn ? make_smem_desc(sb, kBK * 128, 1024) : make_smem_desc(sb, 0, 1024);
+#pragma unroll
+          for (int j = 0; j < kBK / 16; ++j) umma<false>(tacc, da0 + j * step_a, db0 + j * step_b, idesc, (ks > ks0 || j > 0) ? 1u : 0u);
+          umma_commit(&pipe->empty[st]);
+          if (ks == ks1 - 1) umma_commit(&pipe->acc_full[ab]);
+        }
+        __syncwarp();
+      }
+      if (ks1 <= ks0 && elect_one()) mbar_arrive(&pipe->acc_full[ab]);   // empty k-slice: nothing to wait for
+      __syncwarp();
+    }
+  } else {
+    // ================= epilogue: TMEM -> registers -> smem transpose -> coalesced global stores =================
+    const int ew = warp - 2, lg = warp & 3, chalf = ew >> 2;
+    float* stg = stg_all + ew * (32 * kStgPitch);
+    const int cpw = p.BN / 2, cbeg = chalf * cpw;
+    int tcount = 0;
+    for (int u = blockIdx.x; u < units; u += gridDim.x, ++tcount) {
+      const int z = u / tiles, t = u % tiles, m_tile = t % p.tiles_m, n_tile = t / p.tiles_m;
+      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      const bool have = ks1 > ks0;
+      const int ab = tcount & 1, aph = (tcount >> 1) & 1;
+      PG_MARK(1, 10);
+      mbar_wait(&pipe->acc_full[ab], aph);
+      tc_fence_after();
+      PG_MARK(1, 11);
+      const bool add_bias = p.bias != nullptr && p.partial_stride == 0;
+      const long zoff = p.partial_stride ? (long)z * p.partial_stride : 0;
+      const long row0 = (long)m_tile * kBM + lg * 32;
+      for (int c0 = cbeg; c0 < cbeg + cpw; c0 += 16) {
+        uint32_t r[16];
+        if (have) { tmem_ld16(tmem + ((uint32_t)(lg * 32) << 16) + ab * 256 + c0, r); tmem_ld_wait(); }
+        else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) r[j] = 0;
+        }
+        if (c0 + 16 >= cbeg + cpw) {                         // last read of this buffer: hand it back to the MMA warp
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&pipe->acc_empty[ab]);
+        }
+        const int gn0 = n_tile * p.BN + c0;
+        const int ncol = min(16, p.N - gn0);
+        if (ncol <= 0) continue;
+        if (add_bias || p.relu) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int gn = gn0 + j;
+            float v = __uint_as_float(r[j]);
+            if (add_bias && gn < p.N) v += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn]) : ((const float*)p.bias)[gn];
+            if (p.relu) v = fmaxf(v, 0.f);
+            r[j] = __float_as_uint(v);
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(stg + lane * kStgPitch + j * 4) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        __syncwarp();
+        const int c4 = (lane & 3) * 4, nv = min(4, ncol - c4);
+#pragma unroll
+        for (int itr = 0; itr < 4; ++itr) {
+          const int rl = itr * 8 + (lane >> 2);
+          const long grow = row0 + rl;
+          if (grow >= p.M || nv <= 0) continue;
+          const float4 v = *reinterpret_cast<const float4*>(stg + rl * kStgPitch + c4);
+          if (p.out_bf16) {
+            __nv_bfloat16* o = (__nv_bfloat16*)p.out + grow * p.ldc + gn0 + c4;
+            if (nv == 4 && (reinterpret_cast<uintptr_t>(o) & 7) == 0) {
+              const __nv_bfloat162 t0 = __floats2bfloat162_rn(v.x, v.y), t1 = __floats2bfloat162_rn(v.z, v.w);
+              *reinterpret_cast<uint2*>(o) = make_uint2(*reinterpret_cast<const uint32_t*>(&t0), *reinterpret_cast<const uint32_t*>(&t1));
+            } else {
+              const float ve[4] = {v.x, v.y, v.z, v.w};
+              for (int e = 0; e < nv; ++e) o[e] = __float2bfloat16_rn(ve[e]);
+            }
+          } else {
+            float* o = (float*)p.out + zoff + grow * p.ldc + gn0 + c4;
+            if (nv == 4 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) *reinterpret_cast<float4*>(o) = v;
+            else {
+              const float ve[4] = {v.x, v.y, v.z, v.w};
+              for (int e = 0; e < nv; ++e) o[e] = ve[e];
+            }
+          }
+        }
+        __syncwarp();
+      }
+    }
+  }
+  PG_MARK(2, 1);
+  tc_fence_before();
+  __syncthreads();
+  PG_MARK(2, 2);
+  if (warp == 1) tmem_dealloc<512>(tmem);
+}
+
+}  // namespace
+
+extern "C" {
+
+// bf16 operands; see gemm_tc.cu::dcp_tc_gemm_ex for the meaning of the major flags.  ksplit > 1: `out` is a
+// [ksplit][M * ldc] fp32 scratch that receives partial tiles (finish with dcp_splitk_reduce, which also adds the bias).
+// K must be a multiple of 64; MN-major operands need their row count (M resp. N) to be a multiple of 8 (TMA stride rule).
+int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc,
+                             int a_mn, int b_mn, int out_bf16, int bias_bf16, int relu, int ksplit, int num_ctas, cudaStream_t s) {
+  if (K % kBK) { dcp_set_error("bf16 gemm: K=%d must be a multiple of %d", K, kBK); return -1; }
+  if (ksplit < 1) ksplit = 1;
+  if (ksplit > 1 && (out_bf16 || relu)) { dcp_set_error("bf16 gemm: split-K writes fp32 partials (no bf16 output / ReLU)"); return -1; }
+  BfGemmParams p{};
+  p.M = M; p.N = N; p.k_stages = K / kBK; p.a_mn = a_mn; p.b_mn = b_mn; p.ksplit = ksplit;
+  p.BN = N > 128 ? 256 : 128;
+  p.tiles_m = (M + kBM - 1) / kBM; p.tiles_n = (N + p.BN - 1) / p.BN;
+  // few work units even after the caller's K split: halve the tile so that more SMs get work
+  if (p.BN == 256 && (long)p.tiles_m * p.tiles_n * ksplit < 64) { p.BN = 128; p.tiles_n = (N + 127) / 128; }
+  p.out = out; p.ldc = ldc; p.out_bf16 = out_bf16; p.bias = bias; p.bias_bf16 = bias_bf16; p.relu = relu;
+  p.partial_stride = ksplit > 1 ? (long)M * ldc : 0;
+  const int stage_bytes = kABytes + p.BN * 128;
+  const int budget = 227 * 1024 - kStgBytes - (int)sizeof(PPipe) - 1024;
+  p.stages = budget / stage_bytes;
+  if (p.stages > kMaxStages) p.stages = kMaxStages;
+  if (p.stages < 2) { dcp_set_error("bf16 gemm: stage does not fit shared memory"); return -1; }
+  const size_t smem = (size_t)p.stages * stage_bytes + kStgBytes + sizeof(PPipe) + 1024;
+  static bool attr = false;
+  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); attr = true; }
+#ifdef DCP_DEBUG_MBAR
+  if (const char* e = getenv("DCP_PGEMM_DBG_PTR")) { volatile int* ptr = (volatile int*)strtoull(e, nullptr, 0); cudaMemcpyToSymbol(g_pg_dbg, &ptr, sizeof ptr); }
+#endif
+  CUtensorMap ma, mb;
+  if (!a_mn) { if (encode_bf16_2d(&ma, A, M, K, lda, kBK, kBM)) return -1; }
+  else { if (encode_bf16_2d(&ma, A, K, M, lda, 64, kBK)) return -1; }
+  if (!b_mn) { if (encode_bf16_2d(&mb, B, N, K, ldb, kBK, p.BN)) return -1; }
+  else { if (encode_bf16_2d(&mb, B, K, N, ldb, 64, kBK)) return -1; }
+  const int units = p.tiles_m * p.tiles_n * ksplit;
+  if (num_ctas <= 0) num_ctas = 148;
+  if (num_ctas > units) num_ctas = units;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  return 0;
+}
+
+}  // extern "C"

@@ -102,14 +102,16 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   }
 
   if (nst > 0) {
-    if (warp == 0 && lane == 0) {
-      // ================= TMA producer =================
+    if (warp == 0) {
+      // ================= TMA producer: the whole warp walks the loop and stays converged (it reaches the closing
+      // __syncthreads as one), lane 0 issues =================
       for (int i = 0; i < nst; ++i) {
         const int st = i % nstages, ph = (i / nstages) & 1;
         mbar_wait(&pipe->empty[st], ph ^ 1);
         uint8_t* sa = smem + st * stage_bytes;
         uint8_t* sb = sa + a_bytes;
         const int ks = ks0 + i;
+        if (lane != 0) { __syncwarp(); continue; }
         if (p.conv == 2) {
           // weight-grad: this stage = one box of kBK output pixels
           int t = ks;
@@ -127,6 +129,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
             const int unit = u0 + u, tap = unit / p.cchunks, cc = unit % p.cchunks;
             tma_load_4d(sa + u * (kBK * 128), &map_a, &pipe->full[st], cc * kChunk, pw0 - p.pad + tap % p.S, ph0 - p.pad + tap / p.S, pn);
           }
+          __syncwarp();
           continue;
         }
         mbar_expect_tx(&pipe->full[st], kABytes + b_bytes);
@@ -149,6 +152,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
             tma_load_2d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, kb);
         }
         if (dbg && i < 8) dbg[8 + i * 4 + 0] = clock64();
+        __syncwarp();
       }
     } else if (warp == 1) {
       // ================= MMA issuer (uniform loop, one elected lane issues) =================
@@ -410,6 +414,13 @@ extern "C" {
 // layers with allow_tf32=False) at three times the MMA count.
 int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
                    int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s);
+int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc,
+                             int a_mn, int b_mn, int out_bf16, int bias_bf16, int relu, int ksplit, int num_ctas, cudaStream_t s);
+static bool bf16_persistent_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("DCP_GEMM_PERSISTENT"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v != 0;
+}
 int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn,
                 int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s) {
   return dcp_tc_gemm_ex(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, dtype, out_bf16, bias_bf16, relu, ksplit, 0, s);
@@ -423,6 +434,9 @@ int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, in
   // tiles with plain stores (no atomics); finish with dcp_splitk_reduce (which also adds the bias)
   const bool partial = ksplit < -1;
   if (partial) ksplit = -ksplit;
+  // bf16: the persistent 128 x 256 kernel (gemm_bf16_persistent.cu) unless DCP_GEMM_PERSISTENT=0 or atomics are asked for
+  if (dtype == DCP_BF16 && (ksplit <= 1 || partial) && bf16_persistent_enabled())
+    return dcp_gemm_bf16_persistent(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, out_bf16, bias_bf16, relu, ksplit < 1 ? 1 : ksplit, 0, s);
   if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
   TcGemmParams p{};
   p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;

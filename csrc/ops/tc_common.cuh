@@ -42,10 +42,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a pipeline bug must become a trapped kernel (an error on the host), never a hung GPU.
+// Bounded wait: a pipeline bug must become a trapped kernel (an error on the host) within seconds, never a hung GPU.
+// The bound is wall time (%globaltimer), because one try_wait may itself suspend for a system-dependent while.
+__device__ __forceinline__ uint64_t global_ns() { uint64_t t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  for (uint32_t i = 0; !mbar_try_wait(bar, parity); ++i)
-    if (i > (1u << 26)) __trap();
+  if (mbar_try_wait(bar, parity)) return;
+  const uint64_t t0 = global_ns();
+  while (!mbar_try_wait(bar, parity)) {
+    if (global_ns() - t0 > 4000000000ull) {
+#ifdef DCP_DEBUG_MBAR
+      printf("mbarrier timeout: block %d thread %d barrier@%u parity %u\n", (int)blockIdx.x, (int)threadIdx.x, smem_u32(bar), parity);
+#endif
+      __trap();
+    }
+  }
 }
 
 // ---- TMA ------------------------------------------------------------------------------------------
@@ -103,6 +113,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
       : "r"(taddr)
       : "memory");
 }
+// 32 lanes x 16 columns
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+        "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- descriptors ------------------------------------------------------------------------------------
@@ -125,6 +144,25 @@ __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t 
 __host__ __device__ constexpr uint32_t make_idesc(bool tf32, bool a_mn_major, bool b_mn_major, int M, int N) {
   return (1u << 4) | ((tf32 ? 2u : 1u) << 7) | ((tf32 ? 2u : 1u) << 10) | ((a_mn_major ? 1u : 0u) << 15) | ((b_mn_major ? 1u : 0u) << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- host: 2-D bf16 tensor map with the 128-byte swizzle (row-major [rows][cols], leading dimension ld elements) ----
+#include <cudaTypedefs.h>
+inline int encode_bf16_2d(CUtensorMap* m, const void* base, long rows, long cols, long ld, int box_cols, int box_rows) {
+  static PFN_cuTensorMapEncodeTiled enc = nullptr;
+  if (!enc) {
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void**)&enc, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) enc = nullptr;
+  }
+  if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(bf16 rows=%ld cols=%ld ld=%ld box=%dx%d) failed: %d", rows, cols, ld, box_cols, box_rows, (int)r); return -1; }
+  return 0;
 }
 
 }  // namespace tc

@@ -91,7 +91,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path | None:
         obj = OBJ / (s.replace("/", "_") + ".o")
         objs.append(obj)
         if force or _newer(obj, [src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + ["-I", str(ROOT / "include"), "-I", str(CSRC), "-c", str(src), "-o", str(obj)]
+            cmd = [nvcc] + NVCC_FLAGS + os.environ.get("DCP_NVCC_EXTRA", "").split() + ["-I", str(ROOT / "include"), "-I", str(CSRC), "-c", str(src), "-o", str(obj)]
             jobs.append((cmd, OBJ / (obj.name + ".log")))
     if jobs:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:

@@ -28,6 +28,8 @@ def declare(lib) -> None:
     lib.dcp_tc_conv_wgrad.argtypes = [vp, vp, vp] + [i] * 15 + [vp]
     lib.dcp_splitk_reduce.restype = C.c_int
     lib.dcp_splitk_reduce.argtypes = [vp, vp, vp, i, l, i, vp]
+    lib.dcp_gemm_bf16_persistent.restype = C.c_int
+    lib.dcp_gemm_bf16_persistent.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, vp]
     lib.dcp_splitk_reduce2.restype = C.c_int
     lib.dcp_splitk_reduce2.argtypes = [vp, vp, vp, l, i, l, vp]
     lib.dcp_flip_weights.restype = C.c_int
@@ -64,6 +66,14 @@ def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit
 
 def _ksplit(M: int, N: int, K: int, dtype) -> int:
     """K splits for skinny problems: enough CTAs to pull the operands at full rate, >= 4 K slabs per CTA."""
+    if dtype == torch.bfloat16:
+        # persistent kernel: 128 x 256 tiles run the tensor pipe at full rate, so fill the SMs with K slices of wide
+        # tiles rather than with narrow tiles (>= 8 slabs of 64 per slice)
+        tiles = -(-M // 128) * -(-N // (256 if N > 128 else 128))
+        stages = K // 64
+        if tiles >= 100 or stages < 16:
+            return 1
+        return max(1, min(stages // 8, NUM_SMS // tiles))
     tiles = -(-M // 128) * -(-N // (32 if N <= 32 else 64 if N <= 64 else 128))
     stages = K // _bk(dtype)
     if tiles >= NUM_SMS // 2 or stages < 8:

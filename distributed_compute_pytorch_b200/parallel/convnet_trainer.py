@@ -28,6 +28,7 @@ from ..ops import cuda as K
 from ..ops import tc
 from ..types import ReduceOp
 from .ddp import DistributedDataParallel
+from .p2p_backend import CH_DDP
 
 READY_ORDER = ["fc2.bias", "fc2.weight", "batchnorm.weight", "batchnorm.bias", "fc1.bias", "fc1.weight",
                "conv2.weight", "conv2.bias", "conv1.weight", "conv1.bias"]
@@ -67,6 +68,17 @@ class FusedConvNetTrainer:
                 off += -(-p.numel() // 4) * 4
             self.buckets = [flat]
         f32 = dict(dtype=torch.float32, device=dev)
+        # ---- BatchNorm buffers in ONE flat block, so the per-forward buffer broadcast DDP does from rank 0
+        # (torch semantics, broadcast_buffers=True) is a single small collective on the side stream
+        self.bn_flat = None
+        bn = net.batchnorm
+        if self.be is not None and self.ddp is not None and self.ddp.broadcast_buffers and bn.track_running_stats:
+            flat = torch.zeros(258, **f32)
+            flat[:128].copy_(bn.running_mean); flat[128:256].copy_(bn.running_var)
+            nbt = flat[256:258].view(torch.int64)
+            nbt.copy_(bn.num_batches_tracked.reshape(1))
+            bn.running_mean.data, bn.running_var.data, bn.num_batches_tracked.data = flat[:128], flat[128:256], nbt.reshape(())
+            self.bn_flat = flat
         P = N * 676
         self.x = torch.zeros(N, 1, 28, 28, **f32)
         self.y = torch.zeros(N, dtype=torch.int64, device=dev)
@@ -112,6 +124,12 @@ class FusedConvNetTrainer:
         step_ptr = K.graph_step.data_ptr()
         tr = int(self.training)
         ck(L.dcp_counter_advance(step_ptr, s()))
+        ev_buf = None
+        if self.bn_flat is not None and tr:
+            # DDP forward semantics: rank 0's buffers win.  Runs on the side stream under conv1 / conv2.
+            self.side.wait_stream(torch.cuda.current_stream(self.dev))
+            self.be.broadcast(self.bn_flat, 0, stream=self.side, chan=CH_DDP)
+            ev_buf = torch.cuda.Event(); ev_buf.record(self.side)
         # ---- forward
         ck(L.dcp_convnet_conv1_fwd(self.x.data_ptr(), p["conv1.weight"].data_ptr(), p["conv1.bias"].data_ptr(), self.a1.data_ptr(), N, s()))
         ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
@@ -119,6 +137,8 @@ class FusedConvNetTrainer:
         ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
         tc.linear_fwd(self.pooled, p["fc1.weight"], p["fc1.bias"], self.h1, False)
         bn = net.batchnorm
+        if ev_buf is not None:
+            torch.cuda.current_stream(self.dev).wait_event(ev_buf)
         if N <= 128 and self.fused_head:
             # BatchNorm + ReLU + dropout + fc2 + log_softmax/nll and ALL of their gradients (+ fc1's bias gradient): one 8-CTA cluster
             ck(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),

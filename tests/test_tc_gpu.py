@@ -146,3 +146,33 @@ def test_conv_wgrad_flat(N, Cout, W):
         assert err < 2e-3, (parts, err)
         db_ref = dy_valid.double().sum((0, 2, 3))            # bias gradient = column sums of dy (fp32 adds, no tensor core)
         assert ((db.double() - db_ref).norm() / db_ref.norm()).item() < 1e-5
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1)])
+@pytest.mark.parametrize("M,N,K,ks", [(8192, 1000, 256, 1), (2048, 2304, 768, 1), (768, 768, 4096, 4), (136, 520, 192, 1)])
+def test_bf16_persistent_gemm(a_mn, b_mn, M, N, K, ks):
+    """gemm_bf16_persistent.cu: several tiles per CTA (double-buffered TMEM accumulator), ragged M / N tiles, both tile widths,
+    split-K through scratch, every operand-major combination used by Linear forward / dgrad / wgrad."""
+    tc = _tc()
+    torch.manual_seed(M + N + K)
+    A = torch.randn(M, K, device=DEV).to(torch.bfloat16)
+    B = (torch.randn(N, K, device=DEV) * 0.1).to(torch.bfloat16)
+    bias = torch.randn(N, device=DEV)
+    ref = A.double() @ B.double().t()
+    Ast = A.t().contiguous() if a_mn else A
+    Bst = B.t().contiguous() if b_mn else B
+    lda = M if a_mn else K
+    ldb = N if b_mn else K
+    if ks > 1:
+        out = torch.empty(M, N, device=DEV)
+        tc.gemm_splitk(Ast, Bst, out, bias, M, N, K, lda, ldb, N, a_mn, b_mn, ks)
+        ref = ref + bias.double()
+        assert _rel_err(out, ref) < 2e-3
+    else:
+        out = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+        tc.gemm(Ast, Bst, out, bias, M, N, K, lda, ldb, N, a_mn, b_mn, True, 1)
+        ref = torch.relu(ref + bias.double())
+        assert _rel_err(out, ref) < 1e-2          # bf16 output rounding
+        out32 = torch.full((M, N), float("nan"), device=DEV)
+        tc.gemm(Ast, Bst, out32, None, M, N, K, lda, ldb, N, a_mn, b_mn, False, 1)
+        assert _rel_err(out32, A.double() @ B.double().t()) < 2e-3
