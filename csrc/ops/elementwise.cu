@@ -117,6 +117,61 @@ template <typename T> __global__ void k_correct_count(const T* __restrict__ x, c
 }
 }  // namespace
 
+// Strided-convolution helpers -----------------------------------------------------------------------------------
+namespace {
+// up[n, h, w, :] = dy[n, h/2, w/2, :] where h, w are even (and inside dy), 0 elsewhere: the data-gradient of a stride-2
+// convolution is the stride-1 data-gradient of this zero-interleaved tensor.  16-byte vectors over the channels.
+__global__ void k_upsample2_zero(const uint4* __restrict__ dy, uint4* __restrict__ up, int N, int Ho, int Wo, int Hup, int Wup, int vec_per_pixel) {
+  const long total = (long)N * Hup * Wup * vec_per_pixel;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vec_per_pixel); long t = i / vec_per_pixel;
+    const int w = (int)(t % Wup); t /= Wup; const int h = (int)(t % Hup); const int n = (int)(t / Hup);
+    uint4 val = make_uint4(0, 0, 0, 0);
+    if (!(h & 1) && !(w & 1) && (h >> 1) < Ho && (w >> 1) < Wo) val = dy[(((long)n * Ho + (h >> 1)) * Wo + (w >> 1)) * vec_per_pixel + v];
+    up[i] = val;
+  }
+}
+// Patch matrix of a convolution over few input channels (the 7x7 / 3-channel ResNet stem): row = output pixel,
+// column = (r * S + s) * C + c, zero padded to Kpad columns.  out is [N*Ho*Wo, Kpad]; the stem then is a plain GEMM.
+template <typename T>
+__global__ void k_im2col_small_c(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride, int pad,
+                                 int Ho, int Wo, int Kpad) {
+  const long total = (long)N * Ho * Wo * Kpad;
+  const int Kd = R * S * C;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int col = (int)(i % Kpad); long t = i / Kpad;
+    const int wo = (int)(t % Wo); t /= Wo; const int ho = (int)(t % Ho); const int n = (int)(t / Ho);
+    T v = from_f<T>(0.f);
+    if (col < Kd) {
+      const int c = col % C, rs = col / C, s_ = rs % S, r = rs / S;
+      const int h = ho * stride - pad + r, w = wo * stride - pad + s_;
+      if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((long)n * H + h) * W + w) * C + c];
+    }
+    out[i] = v;
+  }
+}
+}  // namespace
+
+extern "C" {
+
+// dy: channels-last [N, Ho, Wo, K]; up: [N, Hup, Wup, K] (K * sizeof(element) must be a multiple of 16)
+int dcp_upsample2_zero(const void* dy, void* up, int N, int Ho, int Wo, int Hup, int Wup, int K, int dtype, cudaStream_t s) {
+  const int es = dtype == DCP_F32 ? 4 : 2;
+  if ((K * es) % 16) { dcp_set_error("upsample2_zero: %d channels of %d bytes are not a multiple of 16 bytes", K, es); return -1; }
+  const int vpp = K * es / 16;
+  const long total = (long)N * Hup * Wup * vpp;
+  k_upsample2_zero<<<grid_1d(total, kT), kT, 0, s>>>((const uint4*)dy, (uint4*)up, N, Ho, Wo, Hup, Wup, vpp);
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+int dcp_im2col_small_c(const void* x, void* out, int N, int H, int W, int C, int R, int S, int stride, int pad, int Ho, int Wo, int Kpad, int dtype,
+                       cudaStream_t s) {
+  const long total = (long)N * Ho * Wo * Kpad;
+  DISPATCH_ACT(dtype, (k_im2col_small_c<T><<<grid_1d(total, kT, 148 * 32), kT, 0, s>>>((const T*)x, (T*)out, N, H, W, C, R, S, stride, pad, Ho, Wo, Kpad)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+}  // extern "C"
+
 extern "C" {
 
 int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s) {

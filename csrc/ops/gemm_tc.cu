@@ -25,6 +25,7 @@ struct TcGemmParams {
   // conv = 2, conv weight-grad: K runs over boxes of output pixels; A chunk u of accumulator group g is the
   //           activation box shifted by filter tap (unit / cchunks) for channel chunk (unit % cchunks); B is the dy box
   int conv, S, cchunks, Cin, pad, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
+  int cstride;                  // convolution stride (1 or 2): the activation map samples every cstride-th pixel (TMA elementStrides)
   int stages;                   // pipeline depth (<= kStages)
   int x3;                       // fp32 only: 3xTF32 split (hi*hi + lo*hi + hi*lo) -> fp32-class accuracy
   int groups, units, a_bytes;   // accumulator groups per CTA (1 except wgrad), (tap, chunk) units in total, bytes of one A stage
@@ -127,7 +128,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
             tma_load_4d(sb + j * (kBK * 128), &map_b, &pipe->full[st], n_tile * p.BN + j * kChunk, pw0, ph0, pn);
           for (int u = 0; u < nu; ++u) {
             const int unit = u0 + u, tap = unit / p.cchunks, cc = unit % p.cchunks;
-            tma_load_4d(sa + u * (kBK * 128), &map_a, &pipe->full[st], cc * kChunk, pw0 - p.pad + tap % p.S, ph0 - p.pad + tap / p.S, pn);
+            tma_load_4d(sa + u * (kBK * 128), &map_a, &pipe->full[st], cc * kChunk, pw0 * p.cstride - p.pad + tap % p.S, ph0 * p.cstride - p.pad + tap / p.S, pn);
           }
           __syncwarp();
           continue;
@@ -137,7 +138,7 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
         if (p.conv) {
           const int tap = ks / p.cchunks, cc = ks % p.cchunks;
           const int r = tap / p.S, s = tap % p.S;
-          tma_load_4d(sa, &map_a, &pipe->full[st], cc * kBK, w0 - p.pad + s, h0 - p.pad + r, n0);
+          tma_load_4d(sa, &map_a, &pipe->full[st], cc * kBK, w0 * p.cstride - p.pad + s, h0 * p.cstride - p.pad + r, n0);
           kb = tap * p.Cin + cc * kBK;
         } else if (!p.a_mn) {
           tma_load_2d(sa, &map_a, &pipe->full[st], kb, m_tile * kBM);
@@ -363,13 +364,16 @@ int make_map_2d(CUtensorMap* m, const void* base, int elem_bytes, long rows, lon
   return 0;
 }
 // 4-D map over channels-last [N][H][W][C]; box = {Cb, Wb, Hb, Nb}
-int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb, bool mn_major = false) {
+// estride > 1: the box samples every estride-th pixel along W and H (a strided convolution's input window); the box still
+// delivers Cb x Wb x Hb x Nb elements to shared memory
+int make_map_4d(CUtensorMap* m, const void* base, int elem_bytes, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb, bool mn_major = false,
+                int estride = 1) {
   auto enc = get_encode();
   if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * elem_bytes, (cuuint64_t)W * C * elem_bytes, (cuuint64_t)H * W * C * elem_bytes};
-  cuuint32_t box[4] = {(cuuint32_t)Cb, (cuuint32_t)Wb, (cuuint32_t)Hb, (cuuint32_t)Nb};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  cuuint32_t box[4] = {(cuuint32_t)Cb, (cuuint32_t)(Wb * estride), (cuuint32_t)(Hb * estride), (cuuint32_t)Nb};
+  cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
   CUtensorMapDataType dt = elem_bytes == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
   CUtensorMapSwizzle sw = (mn_major && elem_bytes == 4) ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B;
   CUresult r = enc(m, dt, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
@@ -455,19 +459,28 @@ int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, in
 // Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
 //   x: channels-last [N,H,W,C]; wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] (fp32 or bf16).
 // C must be a multiple of the 128-byte slab (32 f32 / 64 bf16).  (Wb,Hb,Nb): box of output pixels per CTA, product 128.
+int dcp_tc_conv_strided(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad,
+                        int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
 int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho,
                 int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s) {
+  return dcp_tc_conv_strided(x, wmat, y, bias, N, H, W, C, Kout, R, S, pad, 1, Ho, Wo, Wb, Hb, Nb, dtype, out_bf16, bias_bf16, relu, s);
+}
+// Same with a convolution stride of 1 or 2: y[n,ho,wo,k] = sum x[n, ho*stride-pad+r, wo*stride-pad+s, c] * w[k][(r*S+s)*C + c].
+// The strided input window is one TMA box with elementStrides = stride along W and H.
+int dcp_tc_conv_strided(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad,
+                        int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s) {
   const int es = dtype == DCP_F32 ? 4 : 2, bk = 128 / es;
+  if (stride < 1 || stride > 2 || Wb * stride > 256 || Hb * stride > 256) { dcp_set_error("tc conv: stride %d / box %dx%d not supported", stride, Wb, Hb); return -1; }
   if (C % bk) { dcp_set_error("tc conv: C=%d must be a multiple of %d", C, bk); return -1; }
   if (Wb * Hb * Nb != kBM) { dcp_set_error("tc conv: box %dx%dx%d must cover %d pixels", Wb, Hb, Nb, kBM); return -1; }
   TcGemmParams p{};
   p.N = Kout; p.BN = pick_bn(Kout); p.b_bytes = p.BN * 128; p.a_bytes = kABytes; p.groups = 1; p.conv = 1; p.S = S; p.cchunks = C / bk; p.Cin = C; p.pad = pad;
-  p.k_stages = R * S * p.cchunks;
+  p.k_stages = R * S * p.cchunks; p.cstride = stride;
   p.Wb = Wb; p.Hb = Hb; p.Nb = Nb; p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
   p.out = y; p.ldc = Kout; p.bias = bias; p.relu = relu; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
   p.M = p.tiles_w * p.tiles_h * ((N + Nb - 1) / Nb) * kBM;
   CUtensorMap ma, mb;
-  if (make_map_4d(&ma, x, es, N, H, W, C, bk, Wb, Hb, Nb)) return -1;
+  if (make_map_4d(&ma, x, es, N, H, W, C, bk, Wb, Hb, Nb, false, stride)) return -1;
   if (make_map_2d(&mb, wmat, es, Kout, (long)R * S * C, (long)R * S * C, bk, p.BN)) return -1;
   dim3 grid(p.M / kBM, (Kout + p.BN - 1) / p.BN, 1);
   return dtype == DCP_F32 ? launch<true, 128>(ma, mb, p, grid, s) : launch<false, 128>(ma, mb, p, grid, s);
@@ -479,13 +492,21 @@ int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int 
 // accumulator group g is made of 128-byte channel chunks taken from the activation shifted by different filter
 // taps, B is the matching box of dy.  gridDim.z splits the pixel boxes; partial sums meet in fp32 atomics, so
 // dw32 ([Kout][R*S*C] fp32) is zeroed here.
+int dcp_tc_conv_wgrad_strided(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride,
+                              int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
 int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo,
                       int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s) {
+  return dcp_tc_conv_wgrad_strided(dy, x, dw32, N, H, W, C, Kout, R, S, pad, 1, Ho, Wo, Wb, Hb, Nb, dtype, zsplit, s);
+}
+// Same for a convolution stride of 1 or 2 (x is read at ho*stride-pad+r, wo*stride-pad+s).
+int dcp_tc_conv_wgrad_strided(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride,
+                              int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s) {
   const int es = dtype == DCP_F32 ? 4 : 2, chunk = 128 / es;
+  if (stride < 1 || stride > 2) { dcp_set_error("tc wgrad: stride %d not supported", stride); return -1; }
   if (C % chunk) { dcp_set_error("tc wgrad: C=%d must be a multiple of %d", C, chunk); return -1; }
   if (Wb * Hb * Nb != chunk) { dcp_set_error("tc wgrad: pixel box must hold %d pixels", chunk); return -1; }
   TcGemmParams p{};
-  p.conv = 2; p.N = Kout; p.BN = pick_bn(Kout); p.a_mn = 1; p.b_mn = 1; p.S = S; p.cchunks = C / chunk; p.Cin = C; p.pad = pad;
+  p.conv = 2; p.cstride = stride; p.N = Kout; p.BN = pick_bn(Kout); p.a_mn = 1; p.b_mn = 1; p.S = S; p.cchunks = C / chunk; p.Cin = C; p.pad = pad;
   p.units = R * S * p.cchunks;
   const int upg = kBM / chunk;                       // units per accumulator group
   const int groups_total = (p.units + upg - 1) / upg;
@@ -502,7 +523,7 @@ int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, 
   p.partial_stride = partial ? (long)Kout * R * S * C : 0;
   if (!partial) DCP_CUDA_CHECK(cudaMemsetAsync(dw32, 0, sizeof(float) * (size_t)Kout * R * S * C, s));
   CUtensorMap ma, mb;
-  if (make_map_4d(&ma, x, es, N, H, W, C, chunk, Wb, Hb, Nb, true)) return -1;
+  if (make_map_4d(&ma, x, es, N, H, W, C, chunk, Wb, Hb, Nb, true, stride)) return -1;
   if (make_map_4d(&mb, dy, es, N, Ho, Wo, Kout, chunk, Wb, Hb, Nb, true)) return -1;
   const int gtiles = (groups_total + p.groups - 1) / p.groups;
   if (zsplit < 1) zsplit = 1;

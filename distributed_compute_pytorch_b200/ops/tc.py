@@ -24,6 +24,14 @@ def declare(lib) -> None:
     lib.dcp_tc_gemm_ex.argtypes = [vp, vp, vp, vp, i, i, i, l, l, l, i, i, i, i, i, i, i, i, vp]
     lib.dcp_tc_conv.restype = C.c_int
     lib.dcp_tc_conv.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
+    lib.dcp_tc_conv_strided.restype = C.c_int
+    lib.dcp_tc_conv_strided.argtypes = [vp, vp, vp, vp] + [i] * 18 + [vp]
+    lib.dcp_tc_conv_wgrad_strided.restype = C.c_int
+    lib.dcp_tc_conv_wgrad_strided.argtypes = [vp, vp, vp] + [i] * 16 + [vp]
+    lib.dcp_upsample2_zero.restype = C.c_int
+    lib.dcp_upsample2_zero.argtypes = [vp, vp] + [i] * 7 + [vp]
+    lib.dcp_im2col_small_c.restype = C.c_int
+    lib.dcp_im2col_small_c.argtypes = [vp, vp] + [i] * 12 + [vp]
     lib.dcp_tc_conv_wgrad.restype = C.c_int
     lib.dcp_tc_conv_wgrad.argtypes = [vp, vp, vp] + [i] * 15 + [vp]
     lib.dcp_splitk_reduce.restype = C.c_int
@@ -146,25 +154,74 @@ def _pick_box(Wo: int, Ho: int, N: int, pixels: int = 128):
     return best[1]
 
 
+def _small_c(p, dtype) -> bool:
+    """Few input channels (the 7x7 / 3-channel stem): patch matrix (im2col, zero padded to the K slab) + GEMM."""
+    return _ok_dtype(dtype) and p.C < 8 and p.K % 8 == 0 and p.K >= 16 and (p.N * p.Ho * p.Wo) % 8 == 0 and os.environ.get("DCP_TC_CONV", "1") == "1"
+
+
+def _kpad(p, dtype) -> int:
+    bk = _bk(dtype)
+    return -(-(p.R * p.S * p.C) // bk) * bk
+
+
+def _patches(x, p):
+    k = _k()
+    kp = _kpad(p, x.dtype)
+    out = torch.empty(p.N * p.Ho * p.Wo, kp, dtype=x.dtype, device=x.device)
+    k._chk(_lib.dcp_im2col_small_c(x.data_ptr(), out.data_ptr(), p.N, p.H, p.W, p.C, p.R, p.S, p.stride, p.pad, p.Ho, p.Wo, kp, k._dt(x), k._stream()))
+    return out, kp
+
+
 def conv_fwd_supported(p, dtype) -> bool:
-    return _ok_dtype(dtype) and p.stride == 1 and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16 and os.environ.get("DCP_TC_CONV", "1") == "1"
+    if _small_c(p, dtype):
+        return True
+    return (_ok_dtype(dtype) and p.stride in (1, 2) and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16
+            and os.environ.get("DCP_TC_CONV", "1") == "1")
+
+
+def _is_1x1_gemm(p, dtype) -> bool:
+    """1x1 / stride 1 / no padding on channels-last bf16 tensors IS a GEMM over the flattened pixels: it goes to the
+    persistent bf16 GEMM (gemm_bf16_persistent.cu) instead of the implicit-conv kernel."""
+    return p.R == 1 and p.S == 1 and p.pad == 0 and p.stride == 1 and dtype == torch.bfloat16
 
 
 def conv2d_fwd(x, w, b, y, p, relu) -> None:
     k = _k()
+    if _is_1x1_gemm(p, x.dtype) and p.C % 64 == 0:
+        gemm(x, w, y, b, p.N * p.H * p.W, p.K, p.C, p.C, p.C, p.K, 0, 0, relu, 1)
+        return
+    if _small_c(p, x.dtype):
+        pm, kp = _patches(x, p)
+        kd = p.R * p.S * p.C
+        wp = torch.zeros(p.K, kp, dtype=w.dtype, device=w.device)
+        wp[:, :kd] = w.permute(0, 2, 3, 1).reshape(p.K, kd)              # physical (K, R, S, C) order, zero padded columns
+        gemm(pm, wp, y, b, p.N * p.Ho * p.Wo, p.K, kp, kp, kp, p.K, 0, 0, relu, 1, x3=False)
+        return
     wb, hb, nb = _pick_box(p.Wo, p.Ho, p.N)
-    k._chk(_lib.dcp_tc_conv(x.data_ptr(), w.data_ptr(), y.data_ptr(), k._p(b), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo, wb, hb, nb,
-                            k._dt(x), int(y.dtype == torch.bfloat16), int(b is not None and b.dtype == torch.bfloat16), int(relu), k._stream()))
+    k._chk(_lib.dcp_tc_conv_strided(x.data_ptr(), w.data_ptr(), y.data_ptr(), k._p(b), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.stride, p.Ho, p.Wo,
+                                    wb, hb, nb, k._dt(x), int(y.dtype == torch.bfloat16), int(b is not None and b.dtype == torch.bfloat16), int(relu),
+                                    k._stream()))
 
 
 def conv_dgrad_supported(p, dtype) -> bool:
-    return (_ok_dtype(dtype) and p.stride == 1 and p.K % _bk(dtype) == 0 and p.C % 8 == 0 and p.C >= 16 and p.R - 1 - p.pad >= 0
+    return (_ok_dtype(dtype) and p.stride in (1, 2) and p.K % _bk(dtype) == 0 and p.C % 8 == 0 and p.C >= 16 and p.R - 1 - p.pad >= 0
             and os.environ.get("DCP_TC_CONV", "1") == "1")
 
 
 def conv2d_dgrad(dy, w, dx, p) -> None:
     """dx = conv(dy, flipped weights) with padding R-1-pad: the same implicit-GEMM kernel as forward."""
     k = _k()
+    if p.stride == 2:
+        # stride 2: interleave dy with zeros (one small kernel), then it is the stride-1 data-gradient of that tensor
+        hup, wup = p.H + 2 * p.pad - p.R + 1, p.W + 2 * p.pad - p.S + 1
+        up = torch.empty(p.N * hup * wup * p.K, dtype=dy.dtype, device=dy.device)
+        k._chk(_lib.dcp_upsample2_zero(dy.data_ptr(), up.data_ptr(), p.N, p.Ho, p.Wo, hup, wup, p.K, k._dt(dy), k._stream()))
+        p1 = type(p)(p.N, p.H, p.W, p.C, p.K, p.R, p.S, 1, p.pad, hup, wup)
+        conv2d_dgrad(up, w, dx, p1)
+        return
+    if _is_1x1_gemm(p, dy.dtype) and p.K % 64 == 0:
+        gemm(dy, w, dx, None, p.N * p.H * p.W, p.C, p.K, p.K, p.C, p.C, 0, 1, False, 1)      # dx[M,C] = dy[M,K] . w[K,C]
+        return
     wt = torch.empty(p.C * p.R * p.S * p.K, dtype=w.dtype, device=w.device)
     k._chk(_lib.dcp_flip_weights(w.data_ptr(), wt.data_ptr(), p.K, p.R, p.S, p.C, k._dt(w), k._stream()))
     wb, hb, nb = _pick_box(p.W, p.H, p.N)
@@ -172,28 +229,54 @@ def conv2d_dgrad(dy, w, dx, p) -> None:
                             wb, hb, nb, k._dt(dy), int(dx.dtype == torch.bfloat16), 0, 0, k._stream()))
 
 
-def conv_wgrad_launch(dy, x, dw32, N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb, zsplit) -> None:
+def conv_wgrad_launch(dy, x, dw32, N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb, zsplit, stride=1) -> None:
     """Weight-gradient kernel; with several pixel splits the partial filters meet in a scratch buffer + reduce."""
     k = _k()
     if zsplit > 1:
         n = Kout * R * S * Cc
         scratch = torch.empty(zsplit * n, dtype=torch.float32, device=dw32.device)
-        k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), scratch.data_ptr(), N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb,
-                                      k._dt(dy), -zsplit, k._stream()))
+        k._chk(_lib.dcp_tc_conv_wgrad_strided(dy.data_ptr(), x.data_ptr(), scratch.data_ptr(), N, H, W, Cc, Kout, R, S, pad, stride, Ho, Wo, wb, hb, nb,
+                                              k._dt(dy), -zsplit, k._stream()))
         k._chk(_lib.dcp_splitk_reduce(scratch.data_ptr(), dw32.data_ptr(), None, zsplit, n, 4, k._stream()))
     else:
-        k._chk(_lib.dcp_tc_conv_wgrad(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), N, H, W, Cc, Kout, R, S, pad, Ho, Wo, wb, hb, nb,
-                                      k._dt(dy), 1, k._stream()))
+        k._chk(_lib.dcp_tc_conv_wgrad_strided(dy.data_ptr(), x.data_ptr(), dw32.data_ptr(), N, H, W, Cc, Kout, R, S, pad, stride, Ho, Wo, wb, hb, nb,
+                                              k._dt(dy), 1, k._stream()))
 
 
 def conv_wgrad_supported(p, dtype) -> bool:
-    return (_ok_dtype(dtype) and p.stride == 1 and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16
+    if _small_c(p, dtype) and (p.N * p.Ho * p.Wo) % _bk(dtype) == 0:
+        return True
+    return (_ok_dtype(dtype) and p.stride in (1, 2) and p.C % _bk(dtype) == 0 and p.K % 8 == 0 and p.K >= 16
             and os.environ.get("DCP_TC_CONV", "1") == "1")
 
 
 def conv2d_wgrad(dy, x, dw32, db32, p) -> None:
     """dw (fp32 [K,R,S,C]) on tcgen05 with both operands read MN-major from the channels-last tensors."""
     k = _k()
+    M = p.N * p.H * p.W
+    if _is_1x1_gemm(p, dy.dtype) and M % 64 == 0:
+        ks = _ksplit(p.K, p.C, M, dy.dtype)                                                  # dw[K,C] = dy[M,K]^T . x[M,C]
+        if ks > 1:
+            gemm_splitk(dy, x, dw32, None, p.K, p.C, M, p.K, p.C, p.C, 1, 1, ks)
+        else:
+            gemm(dy, x, dw32, None, p.K, p.C, M, p.K, p.C, p.C, 1, 1, False, 1)
+        if db32 is not None:
+            k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), M, p.K, k._dt(dy), k._stream()))
+        return
+    if _small_c(p, dy.dtype):
+        # stem: dw[K, Kpad] = dy[M, K]^T . patches[M, Kpad] (patch matrix recomputed: cheaper than keeping 300 MB alive)
+        pm, kp = _patches(x, p)
+        Mo, kd = p.N * p.Ho * p.Wo, p.R * p.S * p.C
+        dwp = torch.empty(p.K, kp, dtype=torch.float32, device=dy.device)
+        ks = _ksplit(p.K, kp, Mo, dy.dtype)
+        if ks > 1:
+            gemm_splitk(dy, pm, dwp, None, p.K, kp, Mo, p.K, kp, kp, 1, 1, ks, x3=False)
+        else:
+            gemm(dy, pm, dwp, None, p.K, kp, Mo, p.K, kp, kp, 1, 1, False, 1, x3=False)
+        dw32.permute(0, 2, 3, 1).copy_(dwp[:, :kd].view(p.K, p.R, p.S, p.C))
+        if db32 is not None:
+            k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), Mo, p.K, k._dt(dy), k._stream()))
+        return
     chunk = _bk(dy.dtype)
     wb, hb, nb = _pick_box(p.Wo, p.Ho, p.N, chunk)
     boxes = -(-p.Wo // wb) * -(-p.Ho // hb) * -(-p.N // nb)
@@ -203,6 +286,6 @@ def conv2d_wgrad(dy, x, dw32, db32, p) -> None:
     g = max(1, min(3, groups_total, 512 // bn))
     ctas = -(-groups_total // g) * -(-p.K // bn)
     zsplit = max(1, min(boxes, NUM_SMS // ctas if ctas < NUM_SMS else 1))
-    conv_wgrad_launch(dy, x, dw32, p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo, wb, hb, nb, zsplit)
+    conv_wgrad_launch(dy, x, dw32, p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.Ho, p.Wo, wb, hb, nb, zsplit, p.stride)
     if db32 is not None:
         k._chk(k.lib().dcp_colsum(dy.data_ptr(), db32.data_ptr(), p.N * p.Ho * p.Wo, p.K, k._dt(dy), k._stream()))

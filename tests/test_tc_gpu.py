@@ -80,21 +80,25 @@ def test_gemm_splitk_bias_relu_bf16_out():
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-@pytest.mark.parametrize("N,C,H,W,K,R,pad", [(128, 32, 26, 26, 64, 3, 0), (4, 64, 14, 14, 128, 3, 1), (6, 128, 7, 9, 64, 1, 0), (2, 64, 20, 20, 32, 3, 1)])
-def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
+@pytest.mark.parametrize("N,C,H,W,K,R,pad,stride", [(128, 32, 26, 26, 64, 3, 0, 1), (4, 64, 14, 14, 128, 3, 1, 1), (6, 128, 7, 9, 64, 1, 0, 1),
+                                                      (2, 64, 20, 20, 32, 3, 1, 1), (4, 64, 28, 28, 128, 3, 1, 2), (4, 128, 28, 28, 256, 1, 0, 2),
+                                                      (3, 64, 15, 17, 64, 3, 1, 2), (8, 3, 32, 32, 64, 7, 3, 2)])
+def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad, stride):
+    """Implicit-GEMM convolution forward / data-gradient / weight-gradient on tcgen05, stride 1 and 2 (TMA elementStrides;
+    zero-interleaved dy for the stride-2 data-gradient), 1x1 as plain GEMM, and the few-channel stem via patch matrix + GEMM."""
     from distributed_compute_pytorch_b200.ops import cuda
     tc = _tc()
-    if C % (32 if dtype == torch.float32 else 64):
+    if C >= 8 and C % (32 if dtype == torch.float32 else 64):
         pytest.skip("C not a multiple of the K slab for this dtype")
     torch.manual_seed(0)
     x = torch.randn(N, C, H, W, device=DEV).to(dtype).contiguous(memory_format=torch.channels_last)
     w = (torch.randn(K, C, R, R, device=DEV) * 0.1).to(dtype).contiguous(memory_format=torch.channels_last)
     b = torch.randn(K, device=DEV).to(dtype)
-    p = cuda._convp(x.shape, w.shape, 1, pad)
+    p = cuda._convp(x.shape, w.shape, stride, pad)
     assert tc.conv_fwd_supported(p, dtype)
     y = torch.empty((N, K, p.Ho, p.Wo), dtype=dtype, device=DEV, memory_format=torch.channels_last)
     tc.conv2d_fwd(x, w, b, y, p, True)
-    ref = F.relu(F.conv2d(x.double(), w.double(), b.double(), 1, pad))
+    ref = F.relu(F.conv2d(x.double(), w.double(), b.double(), stride, pad))
     tol = 3e-3 if dtype == torch.float32 else 1.5e-2
     assert _rel_err(y, ref) < tol, _rel_err(y, ref)
     if tc.conv_dgrad_supported(p, dtype):
@@ -102,7 +106,7 @@ def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
         dx = torch.empty_like(x)
         tc.conv2d_dgrad(dy, w, dx, p)
         xr = x.double().requires_grad_(True)
-        F.conv2d(xr, w.double(), None, 1, pad).backward(dy.double())
+        F.conv2d(xr, w.double(), None, stride, pad).backward(dy.double())
         assert _rel_err(dx, xr.grad) < tol, _rel_err(dx, xr.grad)
     if tc.conv_wgrad_supported(p, dtype):
         dy = torch.randn_like(y)
@@ -111,7 +115,7 @@ def test_conv_fwd_and_dgrad(dtype, N, C, H, W, K, R, pad):
         tc.conv2d_wgrad(dy, x, dw32, db32, p)
         wr = w.double().requires_grad_(True)
         br = b.double().requires_grad_(True)
-        F.conv2d(x.double(), wr, br, 1, pad).backward(dy.double())
+        F.conv2d(x.double(), wr, br, stride, pad).backward(dy.double())
         assert _rel_err(dw32, wr.grad) < tol, _rel_err(dw32, wr.grad)
         assert _rel_err(db32, br.grad) < tol
 
