@@ -47,6 +47,8 @@ def declare(lib) -> None:
 
 def _k():
     from . import cuda
+    if _lib is None:
+        cuda.lib()          # loads libdcp_cuda.so and calls declare() above
     return cuda
 
 

@@ -167,10 +167,16 @@ class FusedConvNetTrainer:
         # ---- backward: convolutional trunk
         ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
                                   self.seed, 1, step_ptr, tr, s()))
+        split1, ev1a = 0, None
         if self.flat_wgrad:
             ck(L.dcp_conv_wgrad_flat_tc(self.a1.data_ptr(), self.dy2.data_ptr(), self.wg_scratch.data_ptr(), N * 676, 64, 26, self.wg_parts, s()))
             ck(tc._lib.dcp_splitk_reduce2(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), g["conv2.bias"].data_ptr(), 64 * 288,
                                           self.wg_parts, 64 * 289, s()))
+            # conv2's gradients (98 % of bucket 1) are final here: reduce that part of the bucket now, under the data-gradient
+            # and conv1's weight-gradient; only conv1's 320 values are left for the tail of the step
+            split1 = self._bucket1_split(g)
+            if split1:
+                ev1a = self.be.all_reduce_async(self.buckets[1][:split1], ReduceOp.AVG, max_ctas=self.comm_ctas)
         else:
             tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
             ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
@@ -178,8 +184,11 @@ class FusedConvNetTrainer:
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
         ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
-        ev1 = self._reduce_bucket(1)
-        for ev in (ev0, ev1, ev_opt0):
+        if split1:
+            ev1 = self.be.all_reduce_async(self.buckets[1][split1:], ReduceOp.AVG, max_ctas=self.comm_ctas)
+        else:
+            ev1 = self._reduce_bucket(1)
+        for ev in (ev0, ev1a, ev1, ev_opt0):
             if ev is not None:
                 torch.cuda.current_stream(self.dev).wait_event(ev)
         if rows is not None:
@@ -188,6 +197,17 @@ class FusedConvNetTrainer:
         else:
             self.opt.step()
 
+
+    def _bucket1_split(self, g) -> int:
+        """Number of leading elements of bucket 1 that hold conv2's gradients (0: not splittable / no communication)."""
+        if self.be is None or len(self.buckets) < 2:
+            return 0
+        b = self.buckets[1]
+        w2, b2, w1 = g["conv2.weight"], g["conv2.bias"], g["conv1.weight"]
+        n2 = w2.numel() + b2.numel()
+        if w2.data_ptr() != b.data_ptr() or b2.data_ptr() != b.data_ptr() + 4 * w2.numel() or w1.data_ptr() != b.data_ptr() + 4 * n2 or n2 % 4:
+            return 0
+        return n2
 
     def _opt_rows(self):
         """(cache entry, (first row, rows) of bucket 0, (first row, rows) of bucket 1) in the optimizer's device pointer
