@@ -202,7 +202,17 @@ __device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nb
 __device__ __forceinline__ void push_all_nvls(const DcpDevCtx& c, size_t off, const char* src, size_t nbytes, size_t tid, size_t stride) {
   const size_t nfull = nbytes / 16;
   const bool al = (reinterpret_cast<uintptr_t>(src) & 15) == 0;
-  for (size_t v = tid; v < nfull; v += stride) {
+  size_t v = tid;
+  if (al) {
+    // four independent loads in flight per thread before the (posted) multicast stores: a single source has to fill
+    // its whole NVLink egress on its own in broadcast
+    for (; v + 3 * stride < nfull; v += 4 * stride) {
+      const uint4 x0 = ld16(src + v * 16), x1 = ld16(src + (v + stride) * 16), x2 = ld16(src + (v + 2 * stride) * 16), x3 = ld16(src + (v + 3 * stride) * 16);
+      multimem_st16(c.mc + off + v * 16, x0); multimem_st16(c.mc + off + (v + stride) * 16, x1);
+      multimem_st16(c.mc + off + (v + 2 * stride) * 16, x2); multimem_st16(c.mc + off + (v + 3 * stride) * 16, x3);
+    }
+  }
+  for (; v < nfull; v += stride) {
     uint4 x;
     if (al) x = ld16(src + v * 16);
     else { unsigned char* b = reinterpret_cast<unsigned char*>(&x); for (int j = 0; j < 16; ++j) b[j] = (unsigned char)src[v * 16 + j]; }
@@ -395,7 +405,7 @@ int grid_for(size_t nbytes, int max_ctas) {
   size_t per_cta = (size_t)kThreads * 16 * 4;  // ~4 vectors per thread before adding CTAs
   long g = (long)((nbytes + per_cta - 1) / per_cta);
   if (g < 1) g = 1;
-  if (max_ctas <= 0) max_ctas = 64;
+  if (max_ctas <= 0) max_ctas = nbytes >= ((size_t)32 << 20) ? 128 : 64;   // big messages: more CTAs = more loads / stores in flight
   if (g > max_ctas) g = max_ctas;
   if (g > DCP_MAX_BLOCKS) g = DCP_MAX_BLOCKS;
   return (int)g;
