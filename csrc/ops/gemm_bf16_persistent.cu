@@ -159,6 +159,61 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const bool add_bias = p.bias != nullptr && p.partial_stride == 0;
       const long zoff = p.partial_stride ? (long)z * p.partial_stride : 0;
       const long row0 = (long)m_tile * kBM + lg * 32;
+      if (p.out_bf16 && have) {
+        // bf16 output (the common case, and the one whose epilogue must keep up with a 12-stage main loop): 32 columns per
+        // TMEM load, converted to bf16 BEFORE the shared-memory transpose (half the staging traffic), 64 contiguous bytes
+        // per row and store; the TMEM load of the next chunk is in flight while this one is stored.
+        uint32_t* stw = reinterpret_cast<uint32_t*>(stg);                 // [32 rows][20 words]: 16 words of data + pad
+        uint32_t r[32];
+        tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * 256 + cbeg, r);
+        for (int c0 = cbeg; c0 < cbeg + cpw; c0 += 32) {
+          tmem_ld_wait();
+          const int gn0 = n_tile * p.BN + c0;
+          const int ncol = min(32, p.N - gn0);
+          uint32_t w[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            float v0 = __uint_as_float(r[2 * j]), v1 = __uint_as_float(r[2 * j + 1]);
+            if (add_bias) {
+              const int g0 = min(gn0 + 2 * j, p.N - 1), g1 = min(gn0 + 2 * j + 1, p.N - 1);
+              v0 += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[g0]) : ((const float*)p.bias)[g0];
+              v1 += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[g1]) : ((const float*)p.bias)[g1];
+            }
+            if (p.relu) { v0 = fmaxf(v0, 0.f); v1 = fmaxf(v1, 0.f); }
+            const __nv_bfloat162 t = __floats2bfloat162_rn(v0, v1);
+            w[j] = *reinterpret_cast<const uint32_t*>(&t);
+          }
+          if (c0 + 32 < cbeg + cpw) tmem_ld32(tmem + ((uint32_t)(lg * 32) << 16) + ab * 256 + c0 + 32, r);   // next chunk, asynchronous
+          else {                                               // that was the last read of this buffer: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&pipe->acc_empty[ab]);
+          }
+          if (ncol > 0) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<uint4*>(stw + lane * kStgPitch + j * 4) = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+          }
+          __syncwarp();
+          const int c8 = (lane & 3) * 8, nv = min(8, ncol - c8);      // 8 bf16 = 16 bytes per lane, 4 lanes per row
+          if (ncol > 0) {
+#pragma unroll
+            for (int itr = 0; itr < 4; ++itr) {
+              const int rl = itr * 8 + (lane >> 2);
+              const long grow = row0 + rl;
+              if (grow >= p.M || nv <= 0) continue;
+              const uint4 v = *reinterpret_cast<const uint4*>(stw + rl * kStgPitch + (lane & 3) * 4);
+              __nv_bfloat16* o = (__nv_bfloat16*)p.out + grow * p.ldc + gn0 + c8;
+              if (nv == 8 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) *reinterpret_cast<uint4*>(o) = v;
+              else {
+                const __nv_bfloat16* ve = reinterpret_cast<const __nv_bfloat16*>(&v);
+                for (int e = 0; e < nv; ++e) o[e] = ve[e];
+              }
+            }
+          }
+          __syncwarp();
+        }
+        continue;
+      }
       for (int c0 = cbeg; c0 < cbeg + cpw; c0 += 16) {
         uint32_t r[16];
         if (have) { tmem_ld16(tmem + ((uint32_t)(lg * 32) << 16) + ab * 256 + c0, r); tmem_ld_wait(); }

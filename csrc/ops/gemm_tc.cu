@@ -575,10 +575,31 @@ __global__ void __launch_bounds__(256) k_splitk_reduce(const float* __restrict__
     *reinterpret_cast<float4*>(v * 4 < n1 ? out + v * 4 : out2 + (v * 4 - n1)) = acc;
   }
 }
+// few splits: one thread per output vector, the splits are consecutive independent loads (fully coalesced, no shared memory)
+__global__ void __launch_bounds__(256) k_splitk_reduce_few(const float* __restrict__ scratch, float* __restrict__ out, const float* __restrict__ bias,
+                                                           int nsplit, long n, int ncols, float* __restrict__ out2, long n1) {
+  griddep_launch();
+  griddep_wait();
+  const long n4 = n / 4;
+  for (long v = (long)blockIdx.x * blockDim.x + threadIdx.x; v < n4; v += (long)gridDim.x * blockDim.x) {
+    float4 acc = *reinterpret_cast<const float4*>(scratch + v * 4);
+    for (int z = 1; z < nsplit; ++z) {
+      const float4 x = *reinterpret_cast<const float4*>(scratch + (long)z * n + v * 4);
+      acc.x += x.x; acc.y += x.y; acc.z += x.z; acc.w += x.w;
+    }
+    if (bias) { const int c = (int)((v * 4) % ncols); acc.x += bias[c]; acc.y += bias[c + 1]; acc.z += bias[c + 2]; acc.w += bias[c + 3]; }
+    *reinterpret_cast<float4*>(v * 4 < n1 ? out + v * 4 : out2 + (v * 4 - n1)) = acc;
+  }
+}
 }  // namespace
 // n and ncols must be multiples of 4.
 extern "C" int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s) {
   if ((n & 3) || (ncols & 3)) { dcp_set_error("splitk reduce: n and ncols must be multiples of 4"); return -1; }
+  if (nsplit <= 4) {
+    long g = (n / 4 + 255) / 256; if (g > 148 * 16) g = 148 * 16; if (g < 1) g = 1;
+    DCP_CUDA_CHECK(dcp_launch_pdl(k_splitk_reduce_few, dim3((unsigned)g), dim3(256), 0, s, scratch, out, bias, nsplit, n, ncols, (float*)nullptr, n));
+    return 0;
+  }
   DCP_CUDA_CHECK(dcp_launch_pdl(k_splitk_reduce, dim3((unsigned)((n / 4 + 31) / 32)), dim3(256), 0, s, scratch, out, bias, nsplit, n, ncols, (float*)nullptr, n));
   return 0;
 }
