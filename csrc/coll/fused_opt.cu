@@ -28,7 +28,8 @@ __global__ void __launch_bounds__(kThreads) k_fused_rs_opt_ag(DcpDevCtx c, size_
   const size_t nvec = (n + GV - 1) / GV;
   const size_t per = (nvec + W - 1) / W;
   const size_t vb = min(per * c.rank, nvec), ve = min(vb + per, nvec);
-  const float step = hp[6], gs = hp[7], inv_w = 1.f / (float)W;
+  const OptHyper H = load_hyper<KIND>(hp);
+  const float gs = hp[7], inv_w = 1.f / (float)W;
   dcp_barrier(c, chan);
   for (size_t v = vb + tid; v < ve; v += stride) {
     float g[GV];
@@ -57,14 +58,31 @@ __global__ void __launch_bounds__(kThreads) k_fused_rs_opt_ag(DcpDevCtx c, size_
     float pv[GV];
 #pragma unroll
     for (int i = 0; i < GV; i += 4) *reinterpret_cast<float4*>(&pv[i]) = *reinterpret_cast<const float4*>(mine + e0 + i);
-    const size_t sidx = e0 - vb * GV;               // index into the local state shard
+    const size_t sidx = e0 - vb * GV;               // index into the local state shard (a multiple of GV: 16-byte aligned)
+    if (e0 + GV <= n) {
+      // whole vector inside the tensor (all but possibly the last one): 16-byte state accesses
+      float a[GV], b[GV];
 #pragma unroll
-    for (int i = 0; i < GV; ++i) {
-      if (e0 + i < n) {
-        float a = s1 ? s1[sidx + i] : 0.f, b = s2 ? s2[sidx + i] : 0.f;
-        opt_update<KIND, G>(pv[i], g[i] * gs, a, b, hp, step);
-        if (s1) s1[sidx + i] = a;
-        if (s2) s2[sidx + i] = b;
+      for (int i = 0; i < GV; i += 4) {
+        *reinterpret_cast<float4*>(&a[i]) = s1 ? *reinterpret_cast<const float4*>(s1 + sidx + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+        *reinterpret_cast<float4*>(&b[i]) = s2 ? *reinterpret_cast<const float4*>(s2 + sidx + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int i = 0; i < GV; ++i) opt_update_h<KIND>(pv[i], g[i] * gs, a[i], b[i], H);
+#pragma unroll
+      for (int i = 0; i < GV; i += 4) {
+        if (s1) *reinterpret_cast<float4*>(s1 + sidx + i) = *reinterpret_cast<const float4*>(&a[i]);
+        if (s2) *reinterpret_cast<float4*>(s2 + sidx + i) = *reinterpret_cast<const float4*>(&b[i]);
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < GV; ++i) {
+        if (e0 + i < n) {
+          float a = s1 ? s1[sidx + i] : 0.f, b = s2 ? s2[sidx + i] : 0.f;
+          opt_update_h<KIND>(pv[i], g[i] * gs, a, b, H);
+          if (s1) s1[sidx + i] = a;
+          if (s2) s2[sidx + i] = b;
+        }
       }
     }
 #pragma unroll
@@ -110,7 +128,7 @@ int dcp_fused_rs_opt_ag(void* h, const void* grads, float* params, float* s1, fl
   const size_t shard_bytes = n * 4 / (c.world ? c.world : 1);
   long grid = (long)((shard_bytes + (size_t)kThreads * 16 * 4 - 1) / ((size_t)kThreads * 16 * 4));
   if (grid < 1) grid = 1;
-  if (max_ctas <= 0) max_ctas = 64;
+  if (max_ctas <= 0) max_ctas = 296;        // the shard is streamed once (5-7 arrays): every SM has to pull, two CTAs each
   if (grid > max_ctas) grid = max_ctas;
   if (grid > DCP_MAX_BLOCKS) grid = DCP_MAX_BLOCKS;
 #define LAUNCH(K, G, NV) k_fused_rs_opt_ag<K, G, NV><<<(int)grid, kThreads, 0, stream>>>(c, goff, poff, s1, s2, n, hp, chan)

@@ -25,7 +25,8 @@ __global__ void __launch_bounds__(kT) k_opt(const DcpOptEntry* __restrict__ tabl
   griddep_launch();
   griddep_wait();
   const DcpOptEntry e = table[blockIdx.y];
-  const float step = hp[6], gs = hp[7];
+  const OptHyper H = load_hyper<KIND>(hp);
+  const float gs = hp[7];
   const G* g = static_cast<const G*>(e.g);
   const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthr = (long long)gridDim.x * blockDim.x;
   // 16-byte path: four elements per thread and iteration (parameter views inside the flat buckets are 16-byte aligned
@@ -41,14 +42,14 @@ __global__ void __launch_bounds__(kT) k_opt(const DcpOptEntry* __restrict__ tabl
     unpack4(reinterpret_cast<const GV*>(g)[i], gv);
     float* pp = reinterpret_cast<float*>(&p4); float* pa = reinterpret_cast<float*>(&a4); float* pb = reinterpret_cast<float*>(&b4);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) opt_update<KIND, float>(pp[j], gv[j] * gs, pa[j], pb[j], hp, step);
+    for (int j = 0; j < 4; ++j) opt_update_h<KIND>(pp[j], gv[j] * gs, pa[j], pb[j], H);
     reinterpret_cast<float4*>(e.p)[i] = p4;
     if (e.s1) reinterpret_cast<float4*>(e.s1)[i] = a4;
     if (e.s2) reinterpret_cast<float4*>(e.s2)[i] = b4;
   }
   for (long long i = n4 * 4 + tid; i < e.n; i += nthr) {
     float p = e.p[i], s1 = e.s1 ? e.s1[i] : 0.f, s2 = e.s2 ? e.s2[i] : 0.f;
-    opt_update<KIND, G>(p, to_f(g[i]) * gs, s1, s2, hp, step);
+    opt_update_h<KIND>(p, to_f(g[i]) * gs, s1, s2, H);
     e.p[i] = p;
     if (e.s1) e.s1[i] = s1;
     if (e.s2) e.s2[i] = s2;

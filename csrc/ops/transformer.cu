@@ -50,6 +50,132 @@ __global__ void __launch_bounds__(kT) k_layernorm_bwd(const T* __restrict__ x, c
   for (int c = threadIdx.x; c < C; c += blockDim.x) { atomicAdd(&dgamma[c], acc[c]); atomicAdd(&dbeta[c], acc[C + c]); }
 }
 
+// ---- warp-per-row variants (C a multiple of the 16-byte vector, C <= 32 * kVPL vectors): one warp owns a row, reads it ONCE
+// with 16-byte loads, keeps it in registers, reduces with shuffles (no block barriers); a CTA of 8 warps walks rows with a
+// grid stride.  Backward: each lane owns fixed columns, so the dgamma / dbeta partial sums stay in registers over all rows
+// of the warp, meet in shared memory once per CTA and leave with one atomic per column and CTA.
+template <typename T> struct Vec16;
+template <> struct Vec16<float> { static constexpr int N = 4; __device__ static void load(const float* p, float* o) { const float4 v = *reinterpret_cast<const float4*>(p); o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+                                  __device__ static void store(float* p, const float* o) { *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]); } };
+template <> struct Vec16<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ static void load(const __nv_bfloat16* p, float* o) {
+    const uint4 v = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { o[2 * i] = __low2float(h[i]); o[2 * i + 1] = __high2float(h[i]); }
+  }
+  __device__ static void store(__nv_bfloat16* p, const float* o) {
+    uint4 v; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(o[2 * i], o[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = v;
+  }
+};
+constexpr int kVPL = 4;      // 16-byte vectors per lane: C <= 32 * 4 * 8 = 1024 (bf16) / 512 (f32)
+
+template <typename T>
+__global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__ x, T* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
+                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out, int C, int rows, float eps) {
+  constexpr int VN = Vec16<T>::N;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nvec = C / VN;
+  const float invC = 1.f / (float)C;
+  for (int r = blockIdx.x * (kT / 32) + warp; r < rows; r += gridDim.x * (kT / 32)) {
+    const T* xr = x + (long)r * C;
+    float v[kVPL][VN];
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k) {
+      const int vi = lane + 32 * k;
+      if (vi < nvec) {
+        Vec16<T>::load(xr + vi * VN, v[k]);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) s += v[k][i];
+      }
+    }
+    const float mean = warp_sum(s) * invC;
+    float q = 0.f;
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k)
+      if (lane + 32 * k < nvec) {
+#pragma unroll
+        for (int i = 0; i < VN; ++i) { const float d = v[k][i] - mean; q += d * d; }
+      }
+    const float rstd = rsqrtf(warp_sum(q) * invC + eps);
+    if (lane == 0) { mean_out[r] = mean; rstd_out[r] = rstd; }
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k) {
+      const int vi = lane + 32 * k;
+      if (vi < nvec) {
+        float o[VN];
+#pragma unroll
+        for (int i = 0; i < VN; ++i) o[i] = (v[k][i] - mean) * rstd * g[vi * VN + i] + b[vi * VN + i];
+        Vec16<T>::store(y + (long)r * C + vi * VN, o);
+      }
+    }
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ g,
+                                                           const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int rows) {
+  constexpr int VN = Vec16<T>::N;
+  extern __shared__ float acc[];                     // [2][C], zeroed, then += the 8 warps' partial sums
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nvec = C / VN;
+  const float invC = 1.f / (float)C;
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) acc[c] = 0.f;
+  float gam[kVPL][VN], dg[kVPL][VN], db[kVPL][VN];
+#pragma unroll
+  for (int k = 0; k < kVPL; ++k)
+#pragma unroll
+    for (int i = 0; i < VN; ++i) {
+      const int c = (lane + 32 * k) * VN + i;
+      gam[k][i] = c < C ? g[c] : 0.f; dg[k][i] = 0.f; db[k][i] = 0.f;
+    }
+  for (int r = blockIdx.x * (kT / 32) + warp; r < rows; r += gridDim.x * (kT / 32)) {
+    const long o = (long)r * C;
+    const float mu = mean[r], rs = rstd[r];
+    float xh[kVPL][VN], d[kVPL][VN];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k) {
+      const int vi = lane + 32 * k;
+      if (vi < nvec) {
+        Vec16<T>::load(x + o + vi * VN, xh[k]);
+        Vec16<T>::load(dy + o + vi * VN, d[k]);
+#pragma unroll
+        for (int i = 0; i < VN; ++i) {
+          xh[k][i] = (xh[k][i] - mu) * rs;
+          const float gy = d[k][i] * gam[k][i];
+          s1 += gy; s2 += gy * xh[k][i];
+          dg[k][i] += d[k][i] * xh[k][i]; db[k][i] += d[k][i];
+        }
+      }
+    }
+    s1 = warp_sum(s1) * invC; s2 = warp_sum(s2) * invC;
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k) {
+      const int vi = lane + 32 * k;
+      if (vi < nvec) {
+        float out[VN];
+#pragma unroll
+        for (int i = 0; i < VN; ++i) out[i] = rs * (d[k][i] * gam[k][i] - s1 - xh[k][i] * s2);
+        Vec16<T>::store(dx + o + vi * VN, out);
+      }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int k = 0; k < kVPL; ++k)
+    if (lane + 32 * k < nvec) {
+#pragma unroll
+      for (int i = 0; i < VN; ++i) { const int c = (lane + 32 * k) * VN + i; atomicAdd(&acc[c], dg[k][i]); atomicAdd(&acc[C + c], db[k][i]); }
+    }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) { atomicAdd(&dgamma[c], acc[c]); atomicAdd(&dbeta[c], acc[C + c]); }
+}
+
 __device__ __forceinline__ float gelu_tanh(float x) {
   const float k = 0.7978845608028654f, a = 0.044715f;
   return 0.5f * x * (1.f + tanhf(k * (x + a * x * x * x)));
@@ -71,6 +197,12 @@ template <typename T> __global__ void k_gelu_bwd(const T* __restrict__ x, const 
 extern "C" {
 int dcp_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, float* mean, float* rstd, int rows, int C, float eps, int dtype,
                       cudaStream_t s) {
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (C % vn == 0 && C / vn <= 32 * kVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0)) {
+    const int ctas = min((rows + kT / 32 - 1) / (kT / 32), 148 * 8);
+    DISPATCH_ACT(dtype, (k_layernorm_fwd_warp<T><<<ctas, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, rows, eps)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   DISPATCH_ACT(dtype, (k_layernorm_fwd<T><<<rows, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, eps)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
@@ -79,6 +211,12 @@ int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const f
                       int rows, int C, int dtype, cudaStream_t s) {
   DCP_CUDA_CHECK(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, s));
   DCP_CUDA_CHECK(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, s));
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (C % vn == 0 && C / vn <= 32 * kVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0)) {
+    const int ctasw = min((rows + kT / 32 - 1) / (kT / 32), 148 * 2);
+    DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   int ctas = rows < 148 * 2 ? rows : 148 * 2;
   int rpc = (rows + ctas - 1) / ctas;
   ctas = (rows + rpc - 1) / rpc;

@@ -66,11 +66,14 @@ def test_gpt2_small_config_matches_cpu_and_bf16():
     assert sum(p.numel() for p in dcp.models.GPT2().parameters()) == 124_439_808 + (50304 - 50257) * 768
 
 
-def test_layernorm_gelu_kernels():
+@pytest.mark.parametrize("rows,C", [(64, 768), (4100, 256), (2500, 1024)])
+def test_layernorm_gelu_kernels(rows, C):
+    """LayerNorm forward / backward (warp-per-row 16-byte kernels where the row fits the registers, CTA-per-row otherwise) and
+    tanh-GELU, f32 and bf16, against PyTorch on the CPU."""
     torch.manual_seed(0)
     for dtype, tol in ((torch.float32, 1e-5), (torch.bfloat16, 2e-2)):
-        x = torch.randn(64, 768, requires_grad=True); g = torch.randn(64, 768)
-        ln = ops.LayerNorm(768); ln.weight.data.uniform_(0.5, 1.5); ln.bias.data.uniform_(-0.5, 0.5)
+        x = torch.randn(rows, C, requires_grad=True); g = torch.randn(rows, C)
+        ln = ops.LayerNorm(C); ln.weight.data.uniform_(0.5, 1.5); ln.bias.data.uniform_(-0.5, 0.5)
         y = ln(x); y.backward(g)
         lg = copy.deepcopy(ln).to(DEV); xg = x.detach().to(DEV).to(dtype).requires_grad_(True)
         yg = lg(xg); yg.backward(g.to(DEV).to(dtype))

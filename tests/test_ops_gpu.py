@@ -112,7 +112,7 @@ def test_batchnorm_train_and_eval(shape, relu):
 
 def test_loss_kernels():
     torch.manual_seed(0)
-    for M, C in ((128, 10), (64, 1000), (8, 50257)):
+    for M, C in ((128, 10), (64, 1000), (8, 50257), (16, 50304), (6, 4096)):     # the last two take the 16-byte single-pass kernels
         x = torch.randn(M, C, requires_grad=True); t = torch.randint(0, C, (M,))
         xg = x.detach().to(DEV).requires_grad_(True); tg = t.to(DEV)
         for red in ("mean", "sum"):
@@ -124,6 +124,12 @@ def test_loss_kernels():
             lc = ops.cross_entropy(xg, tg, reduction=red); lc.backward()
             _cmp(lc, l, what=f"ce {red}"); _cmp(xg.grad, x.grad, what=f"ce grad {red}", atol=1e-5)
         assert ops.correct_count(xg, tg).item() == x.argmax(1).eq(t).sum().item()
+    # bf16 logits over a padded 50k vocabulary (the GPT-2 head): vectorised single-pass kernels vs fp32 math on the same bf16 values
+    xb = (torch.randn(32, 50304) * 3).to(torch.bfloat16); tb = torch.randint(0, 50257, (32,))
+    xr = xb.float().requires_grad_(True); lr = F.cross_entropy(xr, tb); lr.backward()
+    xg = xb.to(DEV).requires_grad_(True); lg = ops.cross_entropy(xg, tb.to(DEV)); lg.backward()
+    assert abs(lg.item() - lr.item()) < 2e-3 * abs(lr.item())
+    assert ((xg.grad.float().cpu() - xr.grad).norm() / xr.grad.norm()).item() < 1e-2
 
 
 def test_pool_relu_dropout_gap():
