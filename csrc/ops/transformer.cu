@@ -72,9 +72,9 @@ template <> struct Vec16<__nv_bfloat16> {
     *reinterpret_cast<uint4*>(p) = v;
   }
 };
-constexpr int kVPL = 4;      // 16-byte vectors per lane: C <= 32 * 4 * 8 = 1024 (bf16) / 512 (f32)
+constexpr int kMaxVPL = 4;   // 16-byte vectors per lane (template parameter VPL = ceil(C / vector / 32)): C <= 1024 (bf16) / 512 (f32)
 
-template <typename T>
+template <typename T, int kVPL>
 __global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__ x, T* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
                                                            float* __restrict__ mean_out, float* __restrict__ rstd_out, int C, int rows, float eps) {
   constexpr int VN = Vec16<T>::N;
@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__
   }
 }
 
-template <typename T>
+template <typename T, int kVPL>
 __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ g,
                                                            const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int rows) {
@@ -198,9 +198,12 @@ extern "C" {
 int dcp_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, float* mean, float* rstd, int rows, int C, float eps, int dtype,
                       cudaStream_t s) {
   const int vn = dtype == DCP_F32 ? 4 : 8;
-  if (C % vn == 0 && C / vn <= 32 * kVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0)) {
+  if (C % vn == 0 && C / vn <= 32 * kMaxVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0)) {
     const int ctas = min((rows + kT / 32 - 1) / (kT / 32), 148 * 8);
-    DISPATCH_ACT(dtype, (k_layernorm_fwd_warp<T><<<ctas, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, rows, eps)));
+    const int vpl = (C / vn + 31) / 32;
+#define LN_FWD(V) DISPATCH_ACT(dtype, (k_layernorm_fwd_warp<T, V><<<ctas, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, rows, eps)))
+    if (vpl == 1) { LN_FWD(1); } else if (vpl == 2) { LN_FWD(2); } else if (vpl == 3) { LN_FWD(3); } else { LN_FWD(4); }
+#undef LN_FWD
     DCP_CUDA_CHECK(cudaGetLastError()); return 0;
   }
   DISPATCH_ACT(dtype, (k_layernorm_fwd<T><<<rows, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, eps)));
@@ -212,9 +215,12 @@ int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const f
   DCP_CUDA_CHECK(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, s));
   DCP_CUDA_CHECK(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, s));
   const int vn = dtype == DCP_F32 ? 4 : 8;
-  if (C % vn == 0 && C / vn <= 32 * kVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0)) {
+  if (C % vn == 0 && C / vn <= 32 * kMaxVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0)) {
     const int ctasw = min((rows + kT / 32 - 1) / (kT / 32), 148 * 2);
-    DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows)));
+    const int vpl = (C / vn + 31) / 32;
+#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows)))
+    if (vpl == 1) { LN_BWD(1); } else if (vpl == 2) { LN_BWD(2); } else if (vpl == 3) { LN_BWD(3); } else { LN_BWD(4); }
+#undef LN_BWD
     DCP_CUDA_CHECK(cudaGetLastError()); return 0;
   }
   int ctas = rows < 148 * 2 ? rows : 148 * 2;

@@ -26,7 +26,7 @@ _KINDS = {"adadelta": 0, "sgd": 1, "adam": 2, "adamw": 2}
 class FusedShardedOptimizer:
     def __init__(self, ddp: DistributedDataParallel, kind: str = "adam", lr: float = 1e-3, rho: float = 0.9, eps: float = None,
                  momentum: float = 0.0, dampening: float = 0.0, nesterov: bool = False, betas=(0.9, 0.999), weight_decay: float = 0.0,
-                 use_nvls: bool = True, max_ctas: int = 32):
+                 use_nvls: bool = True, max_ctas: int = 0):
         if ddp._cuda_backend is None:
             raise RuntimeError("FusedShardedOptimizer needs the NVLink P2P backend (CUDA parameters, world_size >= 1)")
         self.ddp, self.be = ddp, ddp._cuda_backend
