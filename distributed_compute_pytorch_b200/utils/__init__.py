@@ -1,3 +1,4 @@
-"""Utilities: synthetic datasets, device timers, clock sampling, checkpoint helpers."""
+"""Utilities: synthetic datasets, device timers, clock sampling, tracing."""
 from .data import SyntheticMNIST, SyntheticImages, SyntheticTokens  # noqa: F401
 from .timing import CudaTimer, ClockSampler  # noqa: F401
+from .trace import Tracer  # noqa: F401

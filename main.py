@@ -106,12 +106,18 @@ def proc(rank, world_size, opt, use_cuda):
     optimizer = ops.Adadelta(model.parameters(), lr=opt.lr)
     scheduler = ops.StepLR(optimizer, step_size=1, gamma=opt.gamma)
 
+    from distributed_compute_pytorch_b200.utils import Tracer
+    tracer = Tracer(rank=rank)                 # DCP_TRACE=<prefix> writes <prefix>_rank<r>.json (chrome://tracing) at the end
     for epoch in range(opt.epochs):
         t0 = time.time()
-        train(opt, model, rank, train_loader, optimizer, epoch, device)
-        test(opt, model, rank, train_loader, optimizer, epoch, device)   # the reference evaluates on the train loader (ref:main.py:130)
+        with tracer.range(f"train epoch {epoch}"):
+            train(opt, model, rank, train_loader, optimizer, epoch, device)
+        with tracer.range(f"eval epoch {epoch}"):
+            test(opt, model, rank, train_loader, optimizer, epoch, device)   # the reference evaluates on the train loader (ref:main.py:130)
         scheduler.step()
         print(f"time to complete this epoch: {time.time() - t0} seconds")
+    if tracer.enabled:
+        tracer.export_chrome(f"{os.environ['DCP_TRACE']}_rank{rank}.json")
     if rank == 0:
         torch.save(model.state_dict(), opt.checkpoint)
     dist.barrier()

@@ -37,3 +37,25 @@ def test_main_world2_cpu(tmp_path, free_port):
     assert list(sd.keys()) == expect
     assert tuple(sd["module.fc1.weight"].shape) == (128, 9216) and sd["module.batchnorm.num_batches_tracked"].item() == 16
     assert hasattr(sd, "_metadata")
+
+
+def test_tracer_cpu(tmp_path):
+    """utils.Tracer: ranges, summary and the chrome-trace export work without a GPU (host row only)."""
+    import json
+    import time
+    from distributed_compute_pytorch_b200.utils import Tracer
+    tr = Tracer(enabled=True, rank=3)
+    with tr.range("a"):
+        time.sleep(0.01)
+    with tr.range("a"):
+        pass
+    tr.mark("m")
+    s = tr.summary()
+    assert s["a"]["count"] == 2 and s["a"]["host_ms"] >= 9.0
+    path = tr.export_chrome(str(tmp_path / "t.json"))
+    ev = json.load(open(path))["traceEvents"]
+    assert any(e.get("name") == "a" and e.get("ph") == "X" and e["pid"] == 3 for e in ev)
+    off = Tracer(enabled=False)
+    with off.range("x"):
+        pass
+    assert off.summary() == {}
