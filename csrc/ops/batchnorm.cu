@@ -140,6 +140,212 @@ __global__ void k_bn_keep_local(double* acc, int C) {
   if (i < 2 * C) acc[2 * C + i] = acc[i];
 }
 
+// ---- 16-byte variants (C a multiple of the vector width, 16-byte aligned tensors): what the ResNet layers hit ----------
+// One thread moves 8 bf16 / 4 f32 channels of a pixel per access.  Reductions: a CTA of 256 threads = (column lanes x row
+// lanes), a thread keeps the sums of ITS channels in registers over all rows it visits (4 rows in flight), the row lanes
+// meet in shared-memory atomics, one fp64 atomic per channel and CTA goes to the accumulator.
+template <typename T> struct BnVec;
+template <> struct BnVec<float> {
+  static constexpr int N = 4;
+  __device__ static void load(const float* p, float* o) { const float4 v = *reinterpret_cast<const float4*>(p); o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w; }
+  __device__ static void store(float* p, const float* o) { *reinterpret_cast<float4*>(p) = make_float4(o[0], o[1], o[2], o[3]); }
+};
+template <> struct BnVec<__nv_bfloat16> {
+  static constexpr int N = 8;
+  __device__ static void load(const __nv_bfloat16* p, float* o) {
+    const uint4 v = *reinterpret_cast<const uint4*>(p);
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) { o[2 * i] = __low2float(h[i]); o[2 * i + 1] = __high2float(h[i]); }
+  }
+  __device__ static void store(__nv_bfloat16* p, const float* o) {
+    uint4 v; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&v);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) h[i] = __floats2bfloat162_rn(o[2 * i], o[2 * i + 1]);
+    *reinterpret_cast<uint4*>(p) = v;
+  }
+};
+constexpr int kVT = 256;      // threads per CTA of the vector kernels
+
+// kBwd = false: sums of x and x^2.  kBwd = true: sums of dy' and dy' * xhat (dy' = dy masked by y > 0 when relu).
+template <typename T, bool kBwd>
+__global__ void __launch_bounds__(kVT) k_bn_reduce_vec(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy,
+                                                        const float* __restrict__ mean, const float* __restrict__ rstd, double* __restrict__ acc,
+                                                        long M, int C, int cl, long rows_per_cta, int relu) {
+  constexpr int VN = BnVec<T>::N;
+  __shared__ float sacc[32 * 8 * 2];                     // [column lane][VN][2]
+  const int rl = kVT / cl;                              // row lanes
+  const int lx = threadIdx.x % cl, ly = threadIdx.x / cl;
+  const int vcol = blockIdx.x * cl + lx;                // vector column
+  const bool live = vcol * VN < C;
+  for (int i = threadIdx.x; i < cl * VN * 2; i += kVT) sacc[i] = 0.f;
+  __syncthreads();
+  float a[VN], b[VN], mu[VN], rs[VN];
+#pragma unroll
+  for (int i = 0; i < VN; ++i) { a[i] = 0.f; b[i] = 0.f; mu[i] = 0.f; rs[i] = 1.f; }
+  if (kBwd && live) {
+#pragma unroll
+    for (int i = 0; i < VN; ++i) { mu[i] = mean[vcol * VN + i]; rs[i] = rstd[vcol * VN + i]; }
+  }
+  const long r0 = (long)blockIdx.y * rows_per_cta, r1 = min(M, r0 + rows_per_cta);
+  if (live) {
+    for (long r = r0 + ly; r < r1; r += 4L * rl) {
+      // branch-free: rows past the end are clamped to the last row and weighted 0, so all 4 (x 3) loads issue back to back
+      float xv[4][VN], gv[4][VN], yv[4][VN], wgt[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const long rr = r + (long)u * rl;
+        wgt[u] = rr < r1 ? 1.f : 0.f;
+        const long o = min(rr, r1 - 1) * C + (long)vcol * VN;
+        BnVec<T>::load(x + o, xv[u]);
+        if (kBwd) { BnVec<T>::load(dy + o, gv[u]); if (relu) BnVec<T>::load(y + o, yv[u]); }
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int i = 0; i < VN; ++i) {
+          if (kBwd) gv[u][i] *= wgt[u]; else xv[u][i] *= wgt[u];
+        }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int i = 0; i < VN; ++i) {
+          if (!kBwd) { a[i] += xv[u][i]; b[i] += xv[u][i] * xv[u][i]; }
+          else {
+            float g = gv[u][i];
+            if (relu && !(yv[u][i] > 0.f)) g = 0.f;
+            a[i] += g; b[i] += g * (xv[u][i] - mu[i]) * rs[i];
+          }
+        }
+    }
+  }
+  // row lanes that share a warp (cl < 32: lanes lx, lx + cl, ...) fold by shuffle first, then one shared-memory atomic per
+  // channel and warp (cl divides 32 or is a multiple of it in every case that matters; otherwise every lane adds for itself)
+  const bool fold = cl < 32 && (32 % cl) == 0;
+  if (fold) {
+#pragma unroll
+    for (int i = 0; i < VN; ++i)
+      for (int o = cl; o < 32; o <<= 1) { a[i] += __shfl_xor_sync(0xffffffffu, a[i], o); b[i] += __shfl_xor_sync(0xffffffffu, b[i], o); }
+  }
+  if (live && (!fold || (threadIdx.x & 31) < cl)) {
+#pragma unroll
+    for (int i = 0; i < VN; ++i) { atomicAdd(&sacc[(lx * VN + i) * 2], a[i]); atomicAdd(&sacc[(lx * VN + i) * 2 + 1], b[i]); }
+  }
+  __syncthreads();
+  (void)rl;
+  for (int i = threadIdx.x; i < cl * VN; i += kVT) {
+    const int c = blockIdx.x * cl * VN + i;
+    if (c < C) { atomicAdd(&acc[c], (double)sacc[i * 2]); atomicAdd(&acc[C + c], (double)sacc[i * 2 + 1]); }
+  }
+}
+
+// forward apply, 16 bytes per access: same prologue as k_bn_apply (every CTA derives scale / shift from the accumulator,
+// CTA 0 updates the running statistics), then y = x * scale[c] + shift[c] (+ReLU)
+template <typename T>
+__global__ void __launch_bounds__(kVT) k_bn_apply_vec(const T* __restrict__ x, T* __restrict__ y, const double* __restrict__ acc, const float* __restrict__ gamma,
+                                                       const float* __restrict__ beta, float* __restrict__ run_mean, float* __restrict__ run_var,
+                                                       long long* __restrict__ nbt, float* __restrict__ save_mean, float* __restrict__ save_rstd, long nvec, int C,
+                                                       double count, float eps, float momentum, int relu, int training) {
+  constexpr int VN = BnVec<T>::N;
+  extern __shared__ __align__(16) float sm[];            // scale[C], shift[C]
+  float* scale = sm; float* shift = sm + C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var;
+    if (training) {
+      const double m = acc[c] / count;
+      double v = acc[C + c] / count - m * m;
+      if (v < 0) v = 0;
+      mean = (float)m; var = (float)v;
+    } else { mean = run_mean[c]; var = run_var[c]; }
+    const float rstd = rsqrtf(var + eps), g = gamma ? gamma[c] : 1.f, bt = beta ? beta[c] : 0.f;
+    scale[c] = g * rstd; shift[c] = bt - mean * g * rstd;
+    if (blockIdx.x == 0 && training) {
+      save_mean[c] = mean; save_rstd[c] = rstd;
+      if (run_mean) {
+        const float unbiased = count > 1 ? var * (float)(count / (count - 1.0)) : var;
+        run_mean[c] = (1.f - momentum) * run_mean[c] + momentum * mean;
+        run_var[c] = (1.f - momentum) * run_var[c] + momentum * unbiased;
+      }
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0 && training && nbt) *nbt += 1;
+  __syncthreads();
+  const int vpr = C / VN;                                // vectors per row
+  for (long v = (long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long)gridDim.x * blockDim.x) {
+    const int c0 = (int)((uint32_t)v % (uint32_t)vpr) * VN;       // nvec < 2^32 (checked on the host)
+    float t[VN], sc[VN], sh[VN];
+    BnVec<T>::load(x + v * VN, t);
+#pragma unroll
+    for (int i = 0; i < VN; i += 4) {                            // 16-byte shared-memory reads (scalar ones are 8-way bank conflicted)
+      *reinterpret_cast<float4*>(&sc[i]) = *reinterpret_cast<const float4*>(&scale[c0 + i]);
+      *reinterpret_cast<float4*>(&sh[i]) = *reinterpret_cast<const float4*>(&shift[c0 + i]);
+    }
+#pragma unroll
+    for (int i = 0; i < VN; ++i) { t[i] = t[i] * sc[i] + sh[i]; if (relu) t[i] = fmaxf(t[i], 0.f); }
+    BnVec<T>::store(y + v * VN, t);
+  }
+}
+template <typename T>
+__global__ void __launch_bounds__(kVT) k_bn_bwd_apply_vec(const T* __restrict__ x, const T* __restrict__ y, const T* __restrict__ dy, T* __restrict__ dx,
+                                                           const float* __restrict__ mean, const float* __restrict__ rstd, const float* __restrict__ gamma,
+                                                           const double* __restrict__ acc, float* __restrict__ dgamma, float* __restrict__ dbeta, long nvec,
+                                                           int C, double count, int relu) {
+  constexpr int VN = BnVec<T>::N;
+  extern __shared__ __align__(16) float sm[];            // k1 = gamma*rstd, k2 = sum_dy/count, k3 = sum_dy_xhat/count, mean, rstd
+  float* k1 = sm; float* k2 = sm + C; float* k3 = sm + 2 * C; float* smu = sm + 3 * C; float* srs = sm + 4 * C;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float g = gamma ? gamma[c] : 1.f;
+    k1[c] = g * rstd[c]; k2[c] = (float)(acc[c] / count); k3[c] = (float)(acc[C + c] / count); smu[c] = mean[c]; srs[c] = rstd[c];
+    if (blockIdx.x == 0) {
+      if (dgamma) dgamma[c] = (float)acc[3 * C + c];
+      if (dbeta) dbeta[c] = (float)acc[2 * C + c];
+    }
+  }
+  __syncthreads();
+  const int vpr = C / VN;
+  for (long v = (long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long)gridDim.x * blockDim.x) {
+    const int c0 = (int)((uint32_t)v % (uint32_t)vpr) * VN;
+    float xv[VN], gv[VN], yv[VN], q1[VN], q2[VN], q3[VN], qm[VN], qr[VN];
+    BnVec<T>::load(x + v * VN, xv);
+    BnVec<T>::load(dy + v * VN, gv);
+    if (relu) BnVec<T>::load(y + v * VN, yv);
+#pragma unroll
+    for (int i = 0; i < VN; i += 4) {
+      *reinterpret_cast<float4*>(&q1[i]) = *reinterpret_cast<const float4*>(&k1[c0 + i]);
+      *reinterpret_cast<float4*>(&q2[i]) = *reinterpret_cast<const float4*>(&k2[c0 + i]);
+      *reinterpret_cast<float4*>(&q3[i]) = *reinterpret_cast<const float4*>(&k3[c0 + i]);
+      *reinterpret_cast<float4*>(&qm[i]) = *reinterpret_cast<const float4*>(&smu[c0 + i]);
+      *reinterpret_cast<float4*>(&qr[i]) = *reinterpret_cast<const float4*>(&srs[c0 + i]);
+    }
+#pragma unroll
+    for (int i = 0; i < VN; ++i) {
+      float g = gv[i];
+      if (relu && !(yv[i] > 0.f)) g = 0.f;
+      const float xhat = (xv[i] - qm[i]) * qr[i];
+      xv[i] = q1[i] * (g - q2[i] - xhat * q3[i]);
+    }
+    BnVec<T>::store(dx + v * VN, xv);
+  }
+}
+template <typename T> bool bn_vec_ok(long M, int C, const void* a, const void* b, const void* c, const void* d) {
+  constexpr int VN = BnVec<T>::N;
+  auto al = [](const void* p) { return p == nullptr || (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  return C % VN == 0 && C <= 2048 && M * (long)C >= 65536 && M * (long)C / VN < 4000000000L && al(a) && al(b) && al(c) && al(d);
+}
+// grid of the vector reductions: column lanes per CTA (<= 32), CTAs over columns, row splits
+void reduce_grid_vec(long M, int C, int vn, int* cl, dim3* grid, long* rows_per_cta) {
+  const int ncl = C / vn;
+  *cl = ncl < 32 ? ncl : 32;
+  while (kVT % *cl) --*cl;                              // row lanes = 256 / cl must be whole (ncl is a power of two in practice)
+  const int gx = (ncl + *cl - 1) / *cl;
+  const int rl = kVT / *cl;
+  long want = (148L * 2 + gx - 1) / gx;
+  long maxy = (M + rl * 4L - 1) / (rl * 4L);
+  long gy = want < maxy ? want : maxy; if (gy < 1) gy = 1; if (gy > 65535) gy = 65535;
+  *rows_per_cta = (M + gy - 1) / gy;
+  *grid = dim3(gx, (unsigned)gy);
+}
+
 void stats_grid(long M, int C, dim3* grid, long* rows_per_cta) {
   int cx = ceil_div(C, kCols);
   long want = (148L * 4 + cx - 1) / cx;           // ~4 CTAs per SM in total
@@ -156,7 +362,15 @@ extern "C" {
 // scratch: >= 4*C doubles.  Phase 1 of forward: zero + accumulate (sum, sumsq).
 int dcp_bn_stats(const void* x, void* scratch, long M, int C, int dtype, cudaStream_t s) {
   DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, s));
-  dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);
+  dim3 grid; long rpc;
+  bool vec = false;
+  DISPATCH_ACT(dtype, (vec = bn_vec_ok<T>(M, C, x, nullptr, nullptr, nullptr)));
+  if (vec) {
+    int cl; reduce_grid_vec(M, C, dtype == DCP_F32 ? 4 : 8, &cl, &grid, &rpc);
+    DISPATCH_ACT(dtype, (k_bn_reduce_vec<T, false><<<grid, kVT, 0, s>>>((const T*)x, nullptr, nullptr, nullptr, nullptr, (double*)scratch, M, C, cl, rpc, 0)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
+  stats_grid(M, C, &grid, &rpc);
   DISPATCH_ACT(dtype, (k_bn_stats<T><<<grid, kRows * kCols, 0, s>>>((const T*)x, (double*)scratch, M, C, rpc)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
@@ -167,6 +381,14 @@ int dcp_bn_apply(const void* x, void* y, const void* scratch, const float* gamma
                  cudaStream_t s) {
   int grid = grid_1d(M * C, 256, 148 * 8);
   size_t smem = sizeof(float) * 2 * C;
+  bool vec = false;
+  DISPATCH_ACT(dtype, (vec = bn_vec_ok<T>(M, C, x, y, nullptr, nullptr)));
+  if (vec) {
+    const long nvec = M * C / (dtype == DCP_F32 ? 4 : 8);
+    DISPATCH_ACT(dtype, (k_bn_apply_vec<T><<<grid_1d(nvec, kVT, 148 * 8), kVT, smem, s>>>((const T*)x, (T*)y, (const double*)scratch, gamma, beta, run_mean, run_var,
+                                                                                         (long long*)nbt, save_mean, save_rstd, nvec, C, count, eps, momentum, relu, training)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   DISPATCH_ACT(dtype, (k_bn_apply<T><<<grid, 256, smem, s>>>((const T*)x, (T*)y, (const double*)scratch, gamma, beta, run_mean, run_var,
                                                              (long long*)nbt, save_mean, save_rstd, M, C, count, eps, momentum, relu, training)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
@@ -176,7 +398,16 @@ int dcp_bn_apply(const void* x, void* y, const void* scratch, const float* gamma
 int dcp_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float* mean, const float* rstd, void* scratch, long M, int C, int relu,
                       int dtype, cudaStream_t s) {
   DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * C, s));
-  dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);
+  dim3 grid; long rpc;
+  bool vec = false;
+  DISPATCH_ACT(dtype, (vec = bn_vec_ok<T>(M, C, x, y, dy, nullptr)));
+  if (vec) {
+    int cl; reduce_grid_vec(M, C, dtype == DCP_F32 ? 4 : 8, &cl, &grid, &rpc);
+    DISPATCH_ACT(dtype, (k_bn_reduce_vec<T, true><<<grid, kVT, 0, s>>>((const T*)x, (const T*)y, (const T*)dy, mean, rstd, (double*)scratch, M, C, cl, rpc, relu)));
+    k_bn_keep_local<<<ceil_div(2 * C, 256), 256, 0, s>>>((double*)scratch, C);
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
+  stats_grid(M, C, &grid, &rpc);
   DISPATCH_ACT(dtype, (k_bn_bwd_reduce<T><<<grid, kRows * kCols, 0, s>>>((const T*)x, (const T*)y, (const T*)dy, mean, rstd, (double*)scratch, M, C, rpc, relu)));
   k_bn_keep_local<<<ceil_div(2 * C, 256), 256, 0, s>>>((double*)scratch, C);
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
@@ -187,6 +418,14 @@ int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, con
                      const void* scratch, float* dgamma, float* dbeta, long M, int C, double count, int relu, int dtype, cudaStream_t s) {
   int grid = grid_1d(M * C, 256, 148 * 8);
   size_t smem = sizeof(float) * 3 * C;
+  bool vec = false;
+  DISPATCH_ACT(dtype, (vec = bn_vec_ok<T>(M, C, x, y, dy, dx)));
+  if (vec) {
+    const long nvec = M * C / (dtype == DCP_F32 ? 4 : 8);
+    DISPATCH_ACT(dtype, (k_bn_bwd_apply_vec<T><<<grid_1d(nvec, kVT, 148 * 8), kVT, sizeof(float) * 5 * C, s>>>((const T*)x, (const T*)y, (const T*)dy, (T*)dx, mean, rstd,
+                                                                                   gamma, (const double*)scratch, dgamma, dbeta, nvec, C, count, relu)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   DISPATCH_ACT(dtype, (k_bn_bwd_apply<T><<<grid, 256, smem, s>>>((const T*)x, (const T*)y, (const T*)dy, (T*)dx, mean, rstd, gamma,
                                                                  (const double*)scratch, dgamma, dbeta, M, C, count, relu)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;

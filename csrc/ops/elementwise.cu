@@ -136,18 +136,26 @@ __global__ void k_upsample2_zero(const uint4* __restrict__ dy, uint4* __restrict
 template <typename T>
 __global__ void k_im2col_small_c(const T* __restrict__ x, T* __restrict__ out, int N, int H, int W, int C, int R, int S, int stride, int pad,
                                  int Ho, int Wo, int Kpad) {
-  const long total = (long)N * Ho * Wo * Kpad;
-  const int Kd = R * S * C;
+  // one thread = one 16-byte vector of a patch row (Kpad is a multiple of the K slab, hence of the vector)
+  constexpr int VN = 16 / sizeof(T);
+  const int vpr = Kpad / VN, Kd = R * S * C;
+  const long total = (long)N * Ho * Wo * vpr;
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
-    const int col = (int)(i % Kpad); long t = i / Kpad;
+    const int col0 = (int)(i % vpr) * VN; long t = i / vpr;
     const int wo = (int)(t % Wo); t /= Wo; const int ho = (int)(t % Ho); const int n = (int)(t / Ho);
-    T v = from_f<T>(0.f);
-    if (col < Kd) {
-      const int c = col % C, rs = col / C, s_ = rs % S, r = rs / S;
-      const int h = ho * stride - pad + r, w = wo * stride - pad + s_;
-      if (h >= 0 && h < H && w >= 0 && w < W) v = x[(((long)n * H + h) * W + w) * C + c];
+    alignas(16) T v[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) {
+      const int col = col0 + j;
+      T e = from_f<T>(0.f);
+      if (col < Kd) {
+        const int c = col % C, rs = col / C, s_ = rs % S, r = rs / S;
+        const int h = ho * stride - pad + r, w = wo * stride - pad + s_;
+        if (h >= 0 && h < H && w >= 0 && w < W) e = x[(((long)n * H + h) * W + w) * C + c];
+      }
+      v[j] = e;
     }
-    out[i] = v;
+    *reinterpret_cast<uint4*>(out + i * VN) = *reinterpret_cast<const uint4*>(v);
   }
 }
 }  // namespace
@@ -165,7 +173,8 @@ int dcp_upsample2_zero(const void* dy, void* up, int N, int Ho, int Wo, int Hup,
 }
 int dcp_im2col_small_c(const void* x, void* out, int N, int H, int W, int C, int R, int S, int stride, int pad, int Ho, int Wo, int Kpad, int dtype,
                        cudaStream_t s) {
-  const long total = (long)N * Ho * Wo * Kpad;
+  if (Kpad % 8) { dcp_set_error("im2col: Kpad must be a multiple of 8"); return -1; }
+  const long total = (long)N * Ho * Wo * Kpad / 4;
   DISPATCH_ACT(dtype, (k_im2col_small_c<T><<<grid_1d(total, kT, 148 * 32), kT, 0, s>>>((const T*)x, (T*)out, N, H, W, C, R, S, stride, pad, Ho, Wo, Kpad)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }

@@ -85,7 +85,8 @@ def test_linear(M, K, N, relu):
     _cmp_norm(lg.weight.grad, lin.weight.grad, btol, "dw"); _cmp_norm(lg.bias.grad, lin.bias.grad, btol, "db")
 
 
-@pytest.mark.parametrize("shape,relu", [((128, 128), True), ((128, 128), False), ((16, 64, 12, 12), True), ((4, 200, 5, 7), False)])
+@pytest.mark.parametrize("shape,relu", [((128, 128), True), ((128, 128), False), ((16, 64, 12, 12), True), ((4, 200, 5, 7), False),
+                                        ((8, 256, 14, 14), True), ((33, 72, 9, 9), False), ((2, 2048, 7, 7), True)])
 def test_batchnorm_train_and_eval(shape, relu):
     torch.manual_seed(0)
     C = shape[1]
