@@ -76,6 +76,73 @@ template <typename T> __global__ void k_maxpool_bwd(const T* __restrict__ dy, co
   }
 }
 
+// 16-byte variants for channels-last tensors whose C is a multiple of the vector (8 bf16 / 4 f32): one thread = one pixel x
+// one channel vector, 32-bit index arithmetic, the argmax bytes of a vector written as one word.
+template <typename T> struct PoolVec { static constexpr int N = 16 / sizeof(T); };
+template <typename T> __device__ __forceinline__ void pool_load(const T* p, float* o) {
+  alignas(16) T t[PoolVec<T>::N];
+  *reinterpret_cast<uint4*>(t) = *reinterpret_cast<const uint4*>(p);
+#pragma unroll
+  for (int i = 0; i < PoolVec<T>::N; ++i) o[i] = to_f(t[i]);
+}
+template <typename T> __device__ __forceinline__ void pool_store(T* p, const float* o) {
+  alignas(16) T t[PoolVec<T>::N];
+#pragma unroll
+  for (int i = 0; i < PoolVec<T>::N; ++i) t[i] = from_f<T>(o[i]);
+  *reinterpret_cast<uint4*>(p) = *reinterpret_cast<const uint4*>(t);
+}
+template <typename T> __global__ void k_maxpool_fwd_vec(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ arg, int N, int H, int W, int C,
+                                                        int Ho, int Wo, int k, int s, int pad) {
+  constexpr int VN = PoolVec<T>::N;
+  const int vpp = C / VN;
+  const long total = (long)N * Ho * Wo * vpp;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vpp); long r = i / vpp; const int wo = (int)(r % Wo); r /= Wo; const int ho = (int)(r % Ho); const int n = (int)(r / Ho);
+    float best[VN]; alignas(8) uint8_t bi[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    for (int kh = 0; kh < k; ++kh) for (int kw = 0; kw < k; ++kw) {
+      const int h = ho * s - pad + kh, w = wo * s - pad + kw;
+      if (h < 0 || h >= H || w < 0 || w >= W) continue;
+      float t[VN];
+      pool_load(x + (((long)n * H + h) * W + w) * C + v * VN, t);
+#pragma unroll
+      for (int j = 0; j < VN; ++j) if (t[j] > best[j]) { best[j] = t[j]; bi[j] = (uint8_t)(kh * k + kw); }
+    }
+    pool_store(y + i * VN, best);
+    if (VN == 8) *reinterpret_cast<uint2*>(arg + i * VN) = *reinterpret_cast<const uint2*>(bi);
+    else *reinterpret_cast<uint32_t*>(arg + i * VN) = *reinterpret_cast<const uint32_t*>(bi);
+  }
+}
+template <typename T> __global__ void k_maxpool_bwd_vec(const T* __restrict__ dy, const uint8_t* __restrict__ arg, T* __restrict__ dx, int N, int H, int W,
+                                                        int C, int Ho, int Wo, int k, int s, int pad) {
+  constexpr int VN = PoolVec<T>::N;
+  const int vpp = C / VN;
+  const long total = (long)N * H * W * vpp;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vpp); long r = i / vpp; const int w = (int)(r % W); r /= W; const int h = (int)(r % H); const int n = (int)(r / H);
+    float acc[VN];
+#pragma unroll
+    for (int j = 0; j < VN; ++j) acc[j] = 0.f;
+    const int ho_lo = max(0, (h + pad - k + s) / s), ho_hi = min(Ho - 1, (h + pad) / s);
+    const int wo_lo = max(0, (w + pad - k + s) / s), wo_hi = min(Wo - 1, (w + pad) / s);
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+      const int kh = h + pad - ho * s, kw = w + pad - wo * s;
+      if (kh < 0 || kh >= k || kw < 0 || kw >= k) continue;
+      const long oi = ((((long)n * Ho + ho) * Wo + wo) * vpp + v) * VN;
+      alignas(8) uint8_t a[VN];
+      if (VN == 8) *reinterpret_cast<uint2*>(a) = *reinterpret_cast<const uint2*>(arg + oi);
+      else *reinterpret_cast<uint32_t*>(a) = *reinterpret_cast<const uint32_t*>(arg + oi);
+      float g[VN];
+      pool_load(dy + oi, g);
+      const int code = kh * k + kw;
+#pragma unroll
+      for (int j = 0; j < VN; ++j) if (a[j] == code) acc[j] += g[j];
+    }
+    pool_store(dx + i * VN, acc);
+  }
+}
+
 // [N, HW, C] -> [N, C] mean; one block per (n, 32-channel group), threads = 32 channels x 8 row lanes
 template <typename T> __global__ void k_gap_fwd(const T* __restrict__ x, T* __restrict__ y, int HW, int C) {
   __shared__ float sm[8][33];
@@ -202,11 +269,21 @@ int dcp_dropout(const void* x, void* y, long n, float p, unsigned long long seed
 }
 int dcp_maxpool_fwd(const void* x, void* y, void* arg, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s) {
   long total = (long)N * Ho * Wo * C;
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (!out_nchw && C % vn == 0 && ((uintptr_t)x % 16 == 0) && ((uintptr_t)y % 16 == 0) && ((uintptr_t)arg % 8 == 0)) {
+    DISPATCH_ACT(dtype, (k_maxpool_fwd_vec<T><<<grid_1d(total / vn, kT), kT, 0, s>>>((const T*)x, (T*)y, (uint8_t*)arg, N, H, W, C, Ho, Wo, k, st, pad)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   DISPATCH_ACT(dtype, (k_maxpool_fwd<T><<<grid_1d(total, kT), kT, 0, s>>>((const T*)x, (T*)y, (uint8_t*)arg, N, H, W, C, Ho, Wo, k, st, pad, out_nchw)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 int dcp_maxpool_bwd(const void* dy, const void* arg, void* dx, int N, int H, int W, int C, int Ho, int Wo, int k, int st, int pad, int out_nchw, int dtype, cudaStream_t s) {
   long total = (long)N * H * W * C;
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (!out_nchw && C % vn == 0 && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0) && ((uintptr_t)arg % 8 == 0)) {
+    DISPATCH_ACT(dtype, (k_maxpool_bwd_vec<T><<<grid_1d(total / vn, kT), kT, 0, s>>>((const T*)dy, (const uint8_t*)arg, (T*)dx, N, H, W, C, Ho, Wo, k, st, pad)));
+    DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+  }
   DISPATCH_ACT(dtype, (k_maxpool_bwd<T><<<grid_1d(total, kT), kT, 0, s>>>((const T*)dy, (const uint8_t*)arg, (T*)dx, N, H, W, C, Ho, Wo, k, st, pad, out_nchw)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
