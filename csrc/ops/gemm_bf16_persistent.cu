@@ -27,6 +27,10 @@ struct BfGemmParams {
   void* out; long ldc; int out_bf16;
   const void* bias; int bias_bf16; int relu;
   long partial_stride;      // ksplit > 1: slice z writes fp32 to out + z * partial_stride
+  // conv = 1: implicit-GEMM convolution (stride 1 or 2).  An M tile is a box of Nb x Hb x Wb = 128 output pixels, K stage ks is
+  // (filter tap, 64-channel chunk): A = 4-D TMA box of the channels-last activation shifted by the tap (OOB zero fill = padding,
+  // elementStrides = convolution stride), B = the matching 64 columns of the [Kout][R*S*C] filter matrix.
+  int conv, S, cchunks, Cin, pad, cstride, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
 };
 
 namespace {
@@ -98,8 +102,15 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
           uint8_t* sa = smem + st * stage_bytes;
           uint8_t* sb = sa + kABytes;
           mbar_expect_tx(&pipe->full[st], stage_bytes);
-          const int kb = ks * kBK;
-          if (!p.a_mn) tma_load_2d(sa, &map_a, &pipe->full[st], kb, m_tile * kBM);
+          int kb = ks * kBK;
+          if (p.conv) {
+            int tt = m_tile;
+            const int tw = tt % p.tiles_w; tt /= p.tiles_w;
+            const int th = tt % p.tiles_h; tt /= p.tiles_h;
+            const int tap = ks / p.cchunks, cc = ks % p.cchunks;
+            tma_load_4d(sa, &map_a, &pipe->full[st], cc * kBK, tw * p.Wb * p.cstride - p.pad + tap % p.S, th * p.Hb * p.cstride - p.pad + tap / p.S, tt * p.Nb);
+            kb = tap * p.Cin + cc * kBK;
+          } else if (!p.a_mn) tma_load_2d(sa, &map_a, &pipe->full[st], kb, m_tile * kBM);
           else
             for (int j = 0; j < kBM / 64; ++j) tma_load_2d(sa + j * (kBK * 128), &map_a, &pipe->full[st], m_tile * kBM + j * 64, kb);
           if (!p.b_mn) tma_load_2d(sb, &map_b, &pipe->full[st], kb, n_tile * p.BN);
@@ -159,6 +170,21 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const bool add_bias = p.bias != nullptr && p.partial_stride == 0;
       const long zoff = p.partial_stride ? (long)z * p.partial_stride : 0;
       const long row0 = (long)m_tile * kBM + lg * 32;
+      long orow[4];                                            // output row of the 4 tile rows this lane stores (-1: outside)
+#pragma unroll
+      for (int itr = 0; itr < 4; ++itr) {
+        const int rt = lg * 32 + itr * 8 + (lane >> 2);         // row inside the 128-row tile
+        if (p.conv) {
+          int tt = m_tile;
+          const int tw = tt % p.tiles_w; tt /= p.tiles_w;
+          const int th = tt % p.tiles_h; tt /= p.tiles_h;
+          const int n = tt * p.Nb + rt / (p.Hb * p.Wb), h = th * p.Hb + (rt / p.Wb) % p.Hb, w = tw * p.Wb + rt % p.Wb;
+          orow[itr] = (n < p.Nimg && h < p.Ho && w < p.Wo) ? ((long)n * p.Ho + h) * p.Wo + w : -1;
+        } else {
+          orow[itr] = (long)m_tile * kBM + rt < p.M ? (long)m_tile * kBM + rt : -1;
+        }
+      }
+      (void)row0;
       if (p.out_bf16 && have) {
         // bf16 output (the common case, and the one whose epilogue must keep up with a 12-stage main loop): 32 columns per
         // TMEM load, converted to bf16 BEFORE the shared-memory transpose (half the staging traffic), 64 contiguous bytes
@@ -199,8 +225,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
 #pragma unroll
             for (int itr = 0; itr < 4; ++itr) {
               const int rl = itr * 8 + (lane >> 2);
-              const long grow = row0 + rl;
-              if (grow >= p.M || nv <= 0) continue;
+              const long grow = orow[itr];
+              if (grow < 0 || nv <= 0) continue;
               const uint4 v = *reinterpret_cast<const uint4*>(stw + rl * kStgPitch + (lane & 3) * 4);
               __nv_bfloat16* o = (__nv_bfloat16*)p.out + grow * p.ldc + gn0 + c8;
               if (nv == 8 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) *reinterpret_cast<uint4*>(o) = v;
@@ -246,8 +272,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
 #pragma unroll
         for (int itr = 0; itr < 4; ++itr) {
           const int rl = itr * 8 + (lane >> 2);
-          const long grow = row0 + rl;
-          if (grow >= p.M || nv <= 0) continue;
+          const long grow = orow[itr];
+          if (grow < 0 || nv <= 0) continue;
           const float4 v = *reinterpret_cast<const float4*>(stg + rl * kStgPitch + c4);
           if (p.out_bf16) {
             __nv_bfloat16* o = (__nv_bfloat16*)p.out + grow * p.ldc + gn0 + c4;
@@ -317,6 +343,40 @@ int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void
   const int units = p.tiles_m * p.tiles_n * ksplit;
   if (num_ctas <= 0) num_ctas = 148;
   if (num_ctas > units) num_ctas = units;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  return 0;
+}
+
+
+// Implicit-GEMM convolution on the persistent kernel (bf16, stride 1 or 2): y[n,ho,wo,k] = sum x[n, ho*stride-pad+r, wo*stride-pad+s, c] * w[k][(r*S+s)*C + c]
+//   x: channels-last [N,H,W,C] (C a multiple of 64); wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] bf16 or fp32.
+//   (Wb, Hb, Nb): box of output pixels per M tile, product 128.  The data-gradient is the same call on dy with flipped filters.
+int dcp_conv_bf16_persistent(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad,
+                             int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int out_bf16, int bias_bf16, int relu, cudaStream_t s) {
+  if (C % kBK) { dcp_set_error("bf16 conv: C=%d must be a multiple of %d", C, kBK); return -1; }
+  if (Wb * Hb * Nb != kBM) { dcp_set_error("bf16 conv: box %dx%dx%d must cover %d pixels", Wb, Hb, Nb, kBM); return -1; }
+  if (stride < 1 || stride > 2 || Wb * stride > 256 || Hb * stride > 256) { dcp_set_error("bf16 conv: stride %d / box %dx%d not supported", stride, Wb, Hb); return -1; }
+  BfGemmParams p{};
+  p.conv = 1; p.S = S; p.cchunks = C / kBK; p.Cin = C; p.pad = pad; p.cstride = stride; p.Wb = Wb; p.Hb = Hb; p.Nb = Nb;
+  p.tiles_w = (Wo + Wb - 1) / Wb; p.tiles_h = (Ho + Hb - 1) / Hb; p.Ho = Ho; p.Wo = Wo; p.Nimg = N;
+  p.tiles_m = p.tiles_w * p.tiles_h * ((N + Nb - 1) / Nb);
+  p.M = p.tiles_m * kBM; p.N = Kout; p.k_stages = R * S * p.cchunks; p.ksplit = 1;
+  p.BN = Kout > 128 ? 256 : 128;
+  p.tiles_n = (Kout + p.BN - 1) / p.BN;
+  if (p.BN == 256 && (long)p.tiles_m * p.tiles_n < 64) { p.BN = 128; p.tiles_n = (Kout + 127) / 128; }
+  p.out = y; p.ldc = Kout; p.out_bf16 = out_bf16; p.bias = bias; p.bias_bf16 = bias_bf16; p.relu = relu;
+  const int stage_bytes = kABytes + p.BN * 128;
+  const int budget = 227 * 1024 - kStgBytes - (int)sizeof(PPipe) - 1024;
+  p.stages = budget / stage_bytes;
+  if (p.stages > kMaxStages) p.stages = kMaxStages;
+  const size_t smem = (size_t)p.stages * stage_bytes + kStgBytes + sizeof(PPipe) + 1024;
+  static bool attr = false;
+  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); attr = true; }
+  CUtensorMap ma, mb;
+  if (encode_bf16_4d(&ma, x, N, H, W, C, kBK, Wb, Hb, Nb, stride)) return -1;
+  if (encode_bf16_2d(&mb, wmat, Kout, (long)R * S * C, (long)R * S * C, kBK, p.BN)) return -1;
+  int num_ctas = p.tiles_m * p.tiles_n;
+  if (num_ctas > 148) num_ctas = 148;
   DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
   return 0;
 }

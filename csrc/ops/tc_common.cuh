@@ -165,4 +165,23 @@ inline int encode_bf16_2d(CUtensorMap* m, const void* base, long rows, long cols
   return 0;
 }
 
+// 4-D bf16 map over a channels-last [N][H][W][C] tensor; box = {Cb, Wb, Hb, Nb} elements delivered to shared memory, sampled every
+// `estride`-th pixel along W and H (the input window of a strided convolution)
+inline int encode_bf16_4d(CUtensorMap* m, const void* base, int N, int H, int W, int C, int Cb, int Wb, int Hb, int Nb, int estride) {
+  static PFN_cuTensorMapEncodeTiled enc = nullptr;
+  if (!enc) {
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", (void**)&enc, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) enc = nullptr;
+  }
+  if (!enc) { dcp_set_error("cuTensorMapEncodeTiled unavailable"); return -1; }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 2, (cuuint64_t)W * C * 2, (cuuint64_t)H * W * C * 2};
+  cuuint32_t box[4] = {(cuuint32_t)Cb, (cuuint32_t)(Wb * estride), (cuuint32_t)(Hb * estride), (cuuint32_t)Nb};
+  cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(bf16 4d N=%d H=%d W=%d C=%d box=%d,%d,%d,%d stride %d) failed: %d", N, H, W, C, Cb, Wb, Hb, Nb, estride, (int)r); return -1; }
+  return 0;
+}
+
 }  // namespace tc

@@ -28,6 +28,8 @@ def declare(lib) -> None:
     lib.dcp_tc_conv_strided.argtypes = [vp, vp, vp, vp] + [i] * 18 + [vp]
     lib.dcp_tc_conv_wgrad_strided.restype = C.c_int
     lib.dcp_tc_conv_wgrad_strided.argtypes = [vp, vp, vp] + [i] * 16 + [vp]
+    lib.dcp_conv_bf16_persistent.restype = C.c_int
+    lib.dcp_conv_bf16_persistent.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
     lib.dcp_upsample2_zero.restype = C.c_int
     lib.dcp_upsample2_zero.argtypes = [vp, vp] + [i] * 7 + [vp]
     lib.dcp_im2col_small_c.restype = C.c_int
@@ -62,6 +64,7 @@ def _ok_dtype(dtype) -> bool:
 
 # fp32 Linear layers default to 3xTF32 (fp32-class accuracy, like the reference's cuBLAS fp32 matmul);
 # DCP_LINEAR_PRECISION=tf32 selects the single-pass tf32 multiply instead.
+PERSISTENT_CONV = os.environ.get("DCP_CONV_PERSISTENT", "1") == "1"     # bf16 implicit-GEMM convs on gemm_bf16_persistent.cu
 LINEAR_X3 = os.environ.get("DCP_LINEAR_PRECISION", "tf32x3") == "tf32x3"
 
 
@@ -200,6 +203,10 @@ def conv2d_fwd(x, w, b, y, p, relu) -> None:
         gemm(pm, wp, y, b, p.N * p.Ho * p.Wo, p.K, kp, kp, kp, p.K, 0, 0, relu, 1, x3=False)
         return
     wb, hb, nb = _pick_box(p.Wo, p.Ho, p.N)
+    if x.dtype == torch.bfloat16 and PERSISTENT_CONV:
+        k._chk(_lib.dcp_conv_bf16_persistent(x.data_ptr(), w.data_ptr(), y.data_ptr(), k._p(b), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.stride, p.Ho, p.Wo,
+                                             wb, hb, nb, int(y.dtype == torch.bfloat16), int(b is not None and b.dtype == torch.bfloat16), int(relu), k._stream()))
+        return
     k._chk(_lib.dcp_tc_conv_strided(x.data_ptr(), w.data_ptr(), y.data_ptr(), k._p(b), p.N, p.H, p.W, p.C, p.K, p.R, p.S, p.pad, p.stride, p.Ho, p.Wo,
                                     wb, hb, nb, k._dt(x), int(y.dtype == torch.bfloat16), int(b is not None and b.dtype == torch.bfloat16), int(relu),
                                     k._stream()))
@@ -227,6 +234,10 @@ def conv2d_dgrad(dy, w, dx, p) -> None:
     wt = torch.empty(p.C * p.R * p.S * p.K, dtype=w.dtype, device=w.device)
     k._chk(_lib.dcp_flip_weights(w.data_ptr(), wt.data_ptr(), p.K, p.R, p.S, p.C, k._dt(w), k._stream()))
     wb, hb, nb = _pick_box(p.W, p.H, p.N)
+    if dy.dtype == torch.bfloat16 and PERSISTENT_CONV:
+        k._chk(_lib.dcp_conv_bf16_persistent(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), None, p.N, p.Ho, p.Wo, p.K, p.C, p.R, p.S, p.R - 1 - p.pad, 1, p.H, p.W,
+                                             wb, hb, nb, int(dx.dtype == torch.bfloat16), 0, 0, k._stream()))
+        return
     k._chk(_lib.dcp_tc_conv(dy.data_ptr(), wt.data_ptr(), dx.data_ptr(), None, p.N, p.Ho, p.Wo, p.K, p.C, p.R, p.S, p.R - 1 - p.pad, p.H, p.W,
                             wb, hb, nb, k._dt(dy), int(dx.dtype == torch.bfloat16), 0, 0, k._stream()))
 
