@@ -144,6 +144,9 @@ int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float*
 int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
 
 /* ---- csrc/ops/elementwise.cu ---- */
+// dy: channels-last [N, Ho, Wo, K]; up: [N, Hup, Wup, K] (K * sizeof(element) must be a multiple of 16)
+int dcp_upsample2_zero(const void* dy, void* up, int N, int Ho, int Wo, int Hup, int Wup, int K, int dtype, cudaStream_t s);
+int dcp_im2col_small_c(const void* x, void* out, int N, int H, int W, int C, int R, int S, int stride, int pad, int Ho, int Wo, int Kpad, int dtype, cudaStream_t s);
 int dcp_relu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
 int dcp_relu_bwd(const void* y, const void* dy, void* dx, long n, int dtype, cudaStream_t s);
 int dcp_add_relu_fwd(const void* a, const void* b, void* y, long n, int dtype, cudaStream_t s);
@@ -154,20 +157,26 @@ int dcp_gap_fwd(const void* x, void* y, int N, int HW, int C, int dtype, cudaStr
 int dcp_gap_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, cudaStream_t s);
 int dcp_correct_count(const void* x, const void* target, void* count, int M, int C, int dtype, cudaStream_t s);
 
+/* ---- csrc/ops/gemm_bf16_persistent.cu ---- */
+// bf16 operands; see gemm_tc.cu::dcp_tc_gemm_ex for the meaning of the major flags.  ksplit > 1: `out` is a
+// [ksplit][M * ldc] fp32 scratch that receives partial tiles (finish with dcp_splitk_reduce, which also adds the bias).
+// K must be a multiple of 64; MN-major operands need their row count (M resp. N) to be a multiple of 8 (TMA stride rule).
+int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int out_bf16, int bias_bf16, int relu, int ksplit, int num_ctas, cudaStream_t s);
+// Implicit-GEMM convolution on the persistent kernel (bf16, stride 1 or 2): y[n,ho,wo,k] = sum x[n, ho*stride-pad+r, wo*stride-pad+s, c] * w[k][(r*S+s)*C + c]
+//   x: channels-last [N,H,W,C] (C a multiple of 64); wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] bf16 or fp32.
+//   (Wb, Hb, Nb): box of output pixels per M tile, product 128.  The data-gradient is the same call on dy with flipped filters.
+int dcp_conv_bf16_persistent(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
+
 /* ---- csrc/ops/gemm_tc.cu ---- */
 int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s);
 int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s);
-// Implicit-GEMM convolution (stride 1): y[n,ho,wo,k] = sum_{r,s,c} x[n, ho-pad+r, wo-pad+s, c] * w[k][(r*S+s)*C + c]
-//   x: channels-last [N,H,W,C]; wmat: [Kout][R*S*C] row-major; y: channels-last [N,Ho,Wo,Kout] (fp32 or bf16).
-// C must be a multiple of the 128-byte slab (32 f32 / 64 bf16).  (Wb,Hb,Nb): box of output pixels per CTA, product 128.
 int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
-// Convolution weight gradient (stride 1) on tcgen05: dw[k][r][s][c] += sum_pixels dy[n,ho,wo,k] * x[n, ho-pad+r, wo-pad+s, c].
-// Both operands are read MN-major straight from the channels-last tensors (no im2col, no transposes): the K
-// dimension of the MMA runs over boxes of (Wb x Hb x Nb) = 32 (f32) / 64 (bf16) output pixels, the A operand of
-// accumulator group g is made of 128-byte channel chunks taken from the activation shifted by different filter
-// taps, B is the matching box of dy.  gridDim.z splits the pixel boxes; partial sums meet in fp32 atomics, so
-// dw32 ([Kout][R*S*C] fp32) is zeroed here.
+// Same with a convolution stride of 1 or 2: y[n,ho,wo,k] = sum x[n, ho*stride-pad+r, wo*stride-pad+s, c] * w[k][(r*S+s)*C + c].
+// The strided input window is one TMA box with elementStrides = stride along W and H.
+int dcp_tc_conv_strided(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
 int dcp_tc_conv_wgrad(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
+// Same for a convolution stride of 1 or 2 (x is read at ho*stride-pad+r, wo*stride-pad+s).
+int dcp_tc_conv_wgrad_strided(const void* dy, const void* x, float* dw32, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int zsplit, cudaStream_t s);
 // n and ncols must be multiples of 4.
 int dcp_splitk_reduce(const float* scratch, float* out, const float* bias, int nsplit, long n, int ncols, cudaStream_t s);
 // Same reduction with the summed vector going to two places: elements [0, n1) to `out`, [n1, n) to `out2` (n1 % 4 == 0).
