@@ -41,6 +41,9 @@ class FusedConvNetTrainer:
         if not isinstance(self.net, ConvNet):
             raise TypeError("FusedConvNetTrainer drives models.ConvNet (optionally DDP-wrapped)")
         self.opt, self.N = optimizer, int(batch_size)
+        if self.N < 32 or self.N % 32:
+            raise ValueError(f"FusedConvNetTrainer: batch size {self.N} must be a multiple of 32 (the batch is the K axis of fc1's weight-gradient GEMM); "
+                             "use GraphedTrainStep or the plain autograd path for other sizes")
         net, N = self.net, self.N
         dev = net.fc1.weight.device
         self.dev = dev
