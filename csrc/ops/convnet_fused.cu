@@ -135,8 +135,18 @@ constexpr int kC1Blocks = 148, kC1Lanes = 16, kC1Fly = 6;
 static __device__ float g_c1w_part[kC1Blocks][320];
 static __device__ unsigned g_c1w_ticket;
 
+// Fused data-parallel tail (ar.on): the CTA that finishes the sum also all-reduces (averages) the 320 values with the other ranks
+// in the same kernel - one-shot push into a [2 halves][W][320] payload block of every peer's symmetric heap, one signal /
+// wait on a reserved (channel, block) pair, local sum.  Same protocol and parity double-buffering as k_allreduce_oneshot in
+// coll.cu; it replaces a separate all-reduce launch plus a stream hop at the very end of the backward pass.
+struct C1AllReduce {
+  int on, chan, blk;
+  size_t pay_off;           // heap offset of the payload block (identical on every rank)
+  DcpDevCtx c;
+};
+
 __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
-                                                               float* __restrict__ db1, long total_pixels) {
+                                                               float* __restrict__ db1, long total_pixels, const C1AllReduce ar) {
   __shared__ float red[kC1Lanes][32][11];
   __shared__ float sx[784];
   __shared__ bool last;
@@ -223,9 +233,42 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
     float tot = 0.f;
 #pragma unroll
     for (int l = 0; l < kC1Lanes; ++l) tot += red2[l * 320 + threadIdx.x];
-    if (t < 9) dw1[cc * 9 + t] = tot; else db1[cc] = tot;
+    if (!ar.on) { if (t < 9) dw1[cc * 9 + t] = tot; else db1[cc] = tot; }
+    else red2[threadIdx.x] = tot;              // keep for the exchange below (row 0 of red2 is this thread's own column)
   }
   if (threadIdx.x == 0) g_c1w_ticket = 0;
+  if (!ar.on) return;
+  // ---- all-reduce (AVG) of the 320 sums across the ranks, by this one CTA ----
+  const DcpDevCtx& cx = ar.c;
+  const int W = cx.world;
+  char* me = cx.peer[cx.rank];
+  __shared__ uint32_t s_half, s_epoch;
+  if (threadIdx.x == 0) { s_half = *((volatile uint32_t*)dcp_calls(me, ar.chan, ar.blk)) & 1u; s_epoch = *((volatile uint32_t*)dcp_epoch(me, ar.chan, ar.blk)) + 1; }
+  __syncthreads();
+  const size_t half_off = ar.pay_off + (size_t)s_half * W * 320 * sizeof(float);
+  if (threadIdx.x < 320) {
+    const float v = red2[threadIdx.x];
+    for (int p = 0; p < W; ++p) reinterpret_cast<float*>(cx.peer[p] + half_off)[cx.rank * 320 + threadIdx.x] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < W) {
+    __threadfence_system();
+    st_release_sys(dcp_sig(cx.peer[threadIdx.x], ar.chan, ar.blk, cx.rank), s_epoch);
+    wait_ge(cx, dcp_sig(me, ar.chan, ar.blk, threadIdx.x), s_epoch);
+  }
+  __syncthreads();
+  if (threadIdx.x < 320) {
+    const float* slots = reinterpret_cast<const float*>(me + half_off);
+    float sum = 0.f;
+    for (int p = 0; p < W; ++p) sum += __ldcg(slots + p * 320 + threadIdx.x);
+    sum *= 1.f / (float)W;
+    const int cc = threadIdx.x / 10, t = threadIdx.x % 10;
+    if (t < 9) dw1[cc * 9 + t] = sum; else db1[cc] = sum;
+  }
+  if (threadIdx.x == 0) {
+    *((volatile uint32_t*)dcp_epoch(me, ar.chan, ar.blk)) = s_epoch;
+    volatile uint32_t* calls = dcp_calls(me, ar.chan, ar.blk); *calls = *calls + 1;
+  }
 }
 
 }  // namespace
@@ -247,7 +290,27 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
 // dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
 // (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1)); return 0;
+  C1AllReduce ar{};
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar)); return 0;
+}
+// The same kernel with the data-parallel all-reduce (AVG over the ranks of symmetric heap `h`) of dw1 / db1 fused into its last
+// CTA.  payload: a block of 2 * world * 320 floats INSIDE the symmetric heap, allocated in the same order on every rank and
+// used by nothing else; (chan, blk): a signal-pad slot no other kernel uses (the trainer passes CH_DDP, DCP_MAX_BLOCKS - 1).
+// Every rank must make this call the same number of times.  dw1 / db1 receive the averaged gradients.
+const DcpDevCtx* dcp_symm_ctx(void* h);
+size_t dcp_symm_bytes(void* h);
+int dcp_convnet_conv1_wgrad_allreduce(void* h, const float* dz1, const float* x, float* dw1, float* db1, int N, void* payload, int chan, int blk,
+                                      cudaStream_t s) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  const char* base = c.peer[c.rank];
+  const char* pay = static_cast<const char*>(payload);
+  if (pay < base || pay + (size_t)2 * c.world * 320 * 4 > base + dcp_symm_bytes(h) || ((pay - base) & 15)) {
+    dcp_set_error("conv1 wgrad + all-reduce: the payload block must be a 16-byte aligned region of the symmetric heap"); return -1;
+  }
+  if (chan < 0 || chan >= DCP_NUM_CHANNELS || blk < 0 || blk >= DCP_MAX_BLOCKS) { dcp_set_error("conv1 wgrad + all-reduce: bad signal slot (%d, %d)", chan, blk); return -1; }
+  C1AllReduce ar{};
+  ar.on = c.world > 1; ar.chan = chan; ar.blk = blk; ar.pay_off = (size_t)(pay - base); ar.c = c;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar)); return 0;
 }
 
 }  // extern "C"

@@ -67,6 +67,7 @@ def lib():
             "dcp_convnet_pool_fwd": [vp, vp, vp, i, f, ull, ull, vp, i, vp],
             "dcp_convnet_pool_bwd": [vp, vp, vp, vp, i, f, ull, ull, vp, i, vp],
             "dcp_convnet_conv1_wgrad": [vp, vp, vp, vp, i, vp],
+            "dcp_convnet_conv1_wgrad_allreduce": [vp, vp, vp, vp, vp, i, vp, i, i, vp],
             "dcp_convnet_head": [vp] * 17 + [i, f, f, f, ull, ull, vp, i, vp],
         }
         for name, args in sigs.items():

@@ -110,6 +110,10 @@ class FusedConvNetTrainer:
         self.fused_head = True
         self.comm_ctas = 16
         self.split_opt = os.environ.get("DCP_SPLIT_OPT", "1") == "1"
+        # data-parallel tail: conv1's 320 gradients are averaged across the ranks INSIDE the conv1 weight-gradient kernel (its last
+        # CTA pushes / signals / sums over NVLink peer memory) instead of by a separate all-reduce launch on the side stream
+        self.fuse_tail = self.be is not None and os.environ.get("DCP_FUSE_TAIL", "1") == "1"
+        self.c1_payload = self.be.empty_symmetric(2 * self.world * 320, torch.float32) if self.fuse_tail else None
         self.side = self.be.comm_stream if self.be is not None else torch.cuda.Stream(device=dev)
         self.launches_per_step = 0
         self.graph = None
@@ -186,11 +190,16 @@ class FusedConvNetTrainer:
         ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
-        ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
-        if split1:
-            ev1 = self.be.all_reduce_async(self.buckets[1][split1:], ReduceOp.AVG, max_ctas=self.comm_ctas)
+        if split1 and self.fuse_tail:
+            ck(L.dcp_convnet_conv1_wgrad_allreduce(self.be.handle, self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(),
+                                                   g["conv1.bias"].data_ptr(), N, self.c1_payload.data_ptr(), CH_DDP, 511, s()))
+            ev1 = None
         else:
-            ev1 = self._reduce_bucket(1)
+            ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
+            if split1:
+                ev1 = self.be.all_reduce_async(self.buckets[1][split1:], ReduceOp.AVG, max_ctas=self.comm_ctas)
+            else:
+                ev1 = self._reduce_bucket(1)
         for ev in (ev0, ev1a, ev1, ev_opt0):
             if ev is not None:
                 torch.cuda.current_stream(self.dev).wait_event(ev)
