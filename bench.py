@@ -29,8 +29,8 @@ POOL_BATCHES = 512  # rotating input pool: 512 x 128 x 784 x 4 B = 205 MB > 126 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=1000)
+    ap.add_argument("--warmup", type=int, default=50)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (the reference's --batch_size default, ref:main.py:139)")
     ap.add_argument("--lr", type=float, default=0.001)
@@ -133,7 +133,7 @@ def run_ours(opt, rank, local_rank, world):
         return start.elapsed_time(end), wall, last, eager_launches
 
     timed(xs, ys, opt.warmup, False)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank, period_s=0.05) as clocks:
         ms, wall, _, eager_l = timed(xs, ys, opt.steps, False)
     timed(hx, hy, max(3, opt.warmup // 2), True)
     ms_e2e, wall_e2e, last_loss, _ = timed(hx, hy, opt.steps, True)
@@ -240,7 +240,7 @@ def run_reference(opt, rank, local_rank, world):
         return t.item()
 
     timed(xs, ys, opt.warmup)
-    with ClockSampler(local_rank) as clocks:
+    with ClockSampler(local_rank, period_s=0.05) as clocks:
         ms, wall = timed(xs, ys, opt.steps)
     timed(hx, hy, max(3, opt.warmup // 2))
     ms_e2e, wall_e2e = timed(hx, hy, opt.steps)
