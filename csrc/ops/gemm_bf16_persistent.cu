@@ -31,6 +31,11 @@ struct BfGemmParams {
   // (filter tap, 64-channel chunk): A = 4-D TMA box of the channels-last activation shifted by the tap (OOB zero fill = padding,
   // elementStrides = convolution stride), B = the matching 64 columns of the [Kout][R*S*C] filter matrix.
   int conv, S, cchunks, Cin, pad, cstride, Wb, Hb, Nb, tiles_w, tiles_h, Ho, Wo, Nimg;
+  // Tail split (ksplit == 1 only): tiles [0, tail_t0) are whole tiles; each tile of the last, partial wave [tail_t0, tiles) is cut
+  // into tail_ks K slices that other (otherwise idle) CTAs take, writing tile-local fp32 partials [128][BN] to tail_ws; the
+  // fix-up kernel adds them up.  148 + 44 tiles then cost 1 + 1/3 waves instead of 2.
+  int tail_t0, tail_ks;
+  float* tail_ws;
 };
 
 namespace {
@@ -53,6 +58,25 @@ struct __align__(8) PPipe {
   uint32_t tmem_base;
 };
 
+struct Unit { int m_tile, n_tile, ks0, ks1, z; float* part; };
+template <bool kTail> __device__ __forceinline__ Unit decode_unit(const BfGemmParams& p, int u, int tiles, int kper) {
+  Unit w;
+  if (!kTail || p.ksplit > 1 || u < p.tail_t0) {
+    w.z = u / tiles; const int t = u % tiles;
+    w.m_tile = t % p.tiles_m; w.n_tile = t / p.tiles_m;
+    w.ks0 = w.z * kper; w.ks1 = min(p.k_stages, w.ks0 + kper); w.part = nullptr;
+  } else {
+    const int r = u - p.tail_t0, t = p.tail_t0 + r / p.tail_ks, sl = r % p.tail_ks;
+    const int kp = (p.k_stages + p.tail_ks - 1) / p.tail_ks;
+    w.z = 0; w.m_tile = t % p.tiles_m; w.n_tile = t / p.tiles_m;
+    w.ks0 = sl * kp; w.ks1 = min(p.k_stages, w.ks0 + kp);
+    w.part = p.tail_ws + (size_t)r * kBM * p.BN;
+  }
+  return w;
+}
+
+// kTail: the launch uses the tail split (a separate instantiation keeps the common path free of its bookkeeping)
+template <bool kTail>
 __global__ void __launch_bounds__(kThreads, 1)
 k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const BfGemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -85,7 +109,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
   PG_MARK(0, 5);
 
   // work units: u -> (tile, k-slice); tiles run M-fastest so that one wave of CTAs shares a few B tiles
-  const int tiles = p.tiles_m * p.tiles_n, units = tiles * p.ksplit;
+  const int tiles = p.tiles_m * p.tiles_n;
+  const int units = (!kTail || p.ksplit > 1) ? tiles * p.ksplit : p.tail_t0 + (tiles - p.tail_t0) * p.tail_ks;
   const int kper = (p.k_stages + p.ksplit - 1) / p.ksplit;
 
   if (warp == 0) {
@@ -93,8 +118,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
     // reaches the closing __syncthreads as one) =================
     int it = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x) {
-      const int z = u / tiles, t = u % tiles, m_tile = t % p.tiles_m, n_tile = t / p.tiles_m;
-      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      const Unit w = decode_unit<kTail>(p, u, tiles, kper);
+      const int m_tile = w.m_tile, n_tile = w.n_tile, ks0 = w.ks0, ks1 = w.ks1;
       for (int ks = ks0; ks < ks1; ++ks, ++it) {
         const int st = it % nstages, ph = (it / nstages) & 1;
         mbar_wait(&pipe->empty[st], ph ^ 1);
@@ -126,8 +151,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
     const uint64_t step_a = p.a_mn ? (uint64_t)((16 * 128) >> 4) : 2u, step_b = p.b_mn ? (uint64_t)((16 * 128) >> 4) : 2u;
     int it = 0, tcount = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++tcount) {
-      const int z = u / tiles;
-      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      const Unit w = decode_unit<kTail>(p, u, tiles, kper);
+      const int ks0 = w.ks0, ks1 = w.ks1;
       const int ab = tcount & 1, aph = (tcount >> 1) & 1;
       mbar_wait(&pipe->acc_empty[ab], aph ^ 1);            // epilogue has drained this accumulator buffer
       tc_fence_after();
@@ -159,15 +184,15 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
     const int cpw = p.BN / 2, cbeg = chalf * cpw;
     int tcount = 0;
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++tcount) {
-      const int z = u / tiles, t = u % tiles, m_tile = t % p.tiles_m, n_tile = t / p.tiles_m;
-      const int ks0 = z * kper, ks1 = min(p.k_stages, ks0 + kper);
+      const Unit w = decode_unit<kTail>(p, u, tiles, kper);
+      const int z = w.z, m_tile = w.m_tile, n_tile = w.n_tile, ks0 = w.ks0, ks1 = w.ks1;
       const bool have = ks1 > ks0;
       const int ab = tcount & 1, aph = (tcount >> 1) & 1;
       PG_MARK(1, 10);
       mbar_wait(&pipe->acc_full[ab], aph);
       tc_fence_after();
       PG_MARK(1, 11);
-      const bool add_bias = p.bias != nullptr && p.partial_stride == 0;
+      const bool add_bias = p.bias != nullptr && p.partial_stride == 0 && w.part == nullptr;
       const long zoff = p.partial_stride ? (long)z * p.partial_stride : 0;
       const long row0 = (long)m_tile * kBM + lg * 32;
       long orow[4];                                            // output row of the 4 tile rows this lane stores (-1: outside)
@@ -185,7 +210,7 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
         }
       }
       (void)row0;
-      if (p.out_bf16 && have) {
+      if (p.out_bf16 && have && w.part == nullptr) {
         // bf16 output (the common case, and the one whose epilogue must keep up with a 12-stage main loop): 32 columns per
         // TMEM load, converted to bf16 BEFORE the shared-memory transpose (half the staging traffic), 64 contiguous bytes
         // per row and store; the TMEM load of the next chunk is in flight while this one is stored.
@@ -253,15 +278,16 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
           if (lane == 0) mbar_arrive(&pipe->acc_empty[ab]);
         }
         const int gn0 = n_tile * p.BN + c0;
-        const int ncol = min(16, p.N - gn0);
+        const bool relu = p.relu && w.part == nullptr;
+        const int ncol = w.part ? 16 : min(16, p.N - gn0);
         if (ncol <= 0) continue;
-        if (add_bias || p.relu) {
+        if (add_bias || relu) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             const int gn = gn0 + j;
             float v = __uint_as_float(r[j]);
             if (add_bias && gn < p.N) v += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn]) : ((const float*)p.bias)[gn];
-            if (p.relu) v = fmaxf(v, 0.f);
+            if (relu) v = fmaxf(v, 0.f);
             r[j] = __float_as_uint(v);
           }
         }
@@ -272,6 +298,10 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
 #pragma unroll
         for (int itr = 0; itr < 4; ++itr) {
           const int rl = itr * 8 + (lane >> 2);
+          if (w.part) {                                      // tail slice: tile-local fp32 partial, every row and column of the tile
+            *reinterpret_cast<float4*>(w.part + (size_t)(lg * 32 + rl) * p.BN + c0 + c4) = *reinterpret_cast<const float4*>(stg + rl * kStgPitch + c4);
+            continue;
+          }
           const long grow = orow[itr];
           if (grow < 0 || nv <= 0) continue;
           const float4 v = *reinterpret_cast<const float4*>(stg + rl * kStgPitch + c4);
@@ -304,9 +334,59 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
   if (warp == 1) tmem_dealloc<512>(tmem);
 }
 
+// Fix-up of the tail split: out tile = sum of its tail_ks tile-local partials (+ bias, ReLU, cast).  One thread = 8 columns of a row.
+__global__ void __launch_bounds__(256) k_gemm_tail_fixup(const BfGemmParams p) {
+  griddep_launch();
+  griddep_wait();
+  const int tiles = p.tiles_m * p.tiles_n, ntail = tiles - p.tail_t0;
+  const int vpr = p.BN / 8;                                    // 8-column vectors per tile row
+  const long total = (long)ntail * kBM * vpr;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vpr); long r_ = i / vpr; const int row = (int)(r_ % kBM); const int tt = (int)(r_ / kBM);
+    const int t = p.tail_t0 + tt, m_tile = t % p.tiles_m, n_tile = t / p.tiles_m;
+    const long grow = (long)m_tile * kBM + row;
+    const int gn0 = n_tile * p.BN + v * 8;
+    if (grow >= p.M || gn0 >= p.N) continue;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int sl = 0; sl < p.tail_ks; ++sl) {
+      const float* src = p.tail_ws + ((size_t)(tt * p.tail_ks + sl) * kBM + row) * p.BN + v * 8;
+      const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+      acc[0] += a.x; acc[1] += a.y; acc[2] += a.z; acc[3] += a.w; acc[4] += b.x; acc[5] += b.y; acc[6] += b.z; acc[7] += b.w;
+    }
+    const int nv = min(8, p.N - gn0);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      if (p.bias && j < nv) acc[j] += p.bias_bf16 ? __bfloat162float(((const __nv_bfloat16*)p.bias)[gn0 + j]) : ((const float*)p.bias)[gn0 + j];
+      if (p.relu) acc[j] = fmaxf(acc[j], 0.f);
+    }
+    if (p.out_bf16) {
+      __nv_bfloat16* o = (__nv_bfloat16*)p.out + grow * p.ldc + gn0;
+      if (nv == 8 && (reinterpret_cast<uintptr_t>(o) & 15) == 0) {
+        uint4 pk; __nv_bfloat162* h = reinterpret_cast<__nv_bfloat162*>(&pk);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h[j] = __floats2bfloat162_rn(acc[2 * j], acc[2 * j + 1]);
+        *reinterpret_cast<uint4*>(o) = pk;
+      } else for (int j = 0; j < nv; ++j) o[j] = __float2bfloat16_rn(acc[j]);
+    } else {
+      float* o = (float*)p.out + grow * p.ldc + gn0;
+      for (int j = 0; j < nv; ++j) o[j] = acc[j];
+    }
+  }
+}
+
+// workspace for the tail split, registered by the host binding (the library itself does not allocate): one per process / device
+float* g_tail_ws = nullptr;
+size_t g_tail_ws_bytes = 0;
+
 }  // namespace
 
 extern "C" {
+
+// Hand the GEMM a scratch buffer (device memory, 16-byte aligned) for the tail split of two-wave problems; nullptr / 0 disables it.
+// GEMMs that use it must not overlap on different streams.
+int dcp_gemm_set_workspace(void* ws, size_t bytes) { g_tail_ws = static_cast<float*>(ws); g_tail_ws_bytes = bytes; return 0; }
 
 // bf16 operands; see gemm_tc.cu::dcp_tc_gemm_ex for the meaning of the major flags.  ksplit > 1: `out` is a
 // [ksplit][M * ldc] fp32 scratch that receives partial tiles (finish with dcp_splitk_reduce, which also adds the bias).
@@ -331,7 +411,11 @@ int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void
   if (p.stages < 2) { dcp_set_error("bf16 gemm: stage does not fit shared memory"); return -1; }
   const size_t smem = (size_t)p.stages * stage_bytes + kStgBytes + sizeof(PPipe) + 1024;
   static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); attr = true; }
+  if (!attr) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr = true;
+  }
 #ifdef DCP_DEBUG_MBAR
   if (const char* e = getenv("DCP_PGEMM_DBG_PTR")) { volatile int* ptr = (volatile int*)strtoull(e, nullptr, 0); cudaMemcpyToSymbol(g_pg_dbg, &ptr, sizeof ptr); }
 #endif
@@ -340,10 +424,27 @@ int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void
   else { if (encode_bf16_2d(&ma, A, K, M, lda, 64, kBK)) return -1; }
   if (!b_mn) { if (encode_bf16_2d(&mb, B, N, K, ldb, kBK, p.BN)) return -1; }
   else { if (encode_bf16_2d(&mb, B, K, N, ldb, 64, kBK)) return -1; }
-  const int units = p.tiles_m * p.tiles_n * ksplit;
   if (num_ctas <= 0) num_ctas = 148;
+  const int tiles = p.tiles_m * p.tiles_n;
+  p.tail_t0 = tiles; p.tail_ks = 1; p.tail_ws = nullptr;
+  // tail split: the last wave holds few tiles and K is long enough to cut -> spread those tiles over the idle CTAs
+  const int tail = tiles % num_ctas;
+  if (ksplit == 1 && tiles > num_ctas && tail > 0 && tail <= num_ctas / 2 && p.k_stages >= 16 && g_tail_ws != nullptr) {
+    int ks = num_ctas / tail;
+    if (ks > p.k_stages / 8) ks = p.k_stages / 8;
+    if (ks > 8) ks = 8;
+    const size_t need = (size_t)tail * ks * kBM * p.BN * sizeof(float);
+    if (ks >= 2 && need <= g_tail_ws_bytes) { p.tail_t0 = tiles - tail; p.tail_ks = ks; p.tail_ws = g_tail_ws; }
+  }
+  const int units = ksplit > 1 ? tiles * ksplit : p.tail_t0 + (tiles - p.tail_t0) * p.tail_ks;
   if (num_ctas > units) num_ctas = units;
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  if (p.tail_ws) DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent<true>, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  else DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent<false>, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  if (p.tail_ws) {
+    const long total = (long)(tiles - p.tail_t0) * kBM * (p.BN / 8);
+    long g = (total + 255) / 256; if (g > 148 * 8) g = 148 * 8;
+    DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_tail_fixup, dim3((unsigned)g), dim3(256), 0, s, p));
+  }
   return 0;
 }
 
@@ -365,19 +466,24 @@ int dcp_conv_bf16_persistent(const void* x, const void* wmat, void* y, const voi
   p.tiles_n = (Kout + p.BN - 1) / p.BN;
   if (p.BN == 256 && (long)p.tiles_m * p.tiles_n < 64) { p.BN = 128; p.tiles_n = (Kout + 127) / 128; }
   p.out = y; p.ldc = Kout; p.out_bf16 = out_bf16; p.bias = bias; p.bias_bf16 = bias_bf16; p.relu = relu;
+  p.tail_t0 = p.tiles_m * p.tiles_n; p.tail_ks = 1; p.tail_ws = nullptr;      // no tail split in convolution mode
   const int stage_bytes = kABytes + p.BN * 128;
   const int budget = 227 * 1024 - kStgBytes - (int)sizeof(PPipe) - 1024;
   p.stages = budget / stage_bytes;
   if (p.stages > kMaxStages) p.stages = kMaxStages;
   const size_t smem = (size_t)p.stages * stage_bytes + kStgBytes + sizeof(PPipe) + 1024;
   static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024)); attr = true; }
+  if (!attr) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    attr = true;
+  }
   CUtensorMap ma, mb;
   if (encode_bf16_4d(&ma, x, N, H, W, C, kBK, Wb, Hb, Nb, stride)) return -1;
   if (encode_bf16_2d(&mb, wmat, Kout, (long)R * S * C, (long)R * S * C, kBK, p.BN)) return -1;
   int num_ctas = p.tiles_m * p.tiles_n;
   if (num_ctas > 148) num_ctas = 148;
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_gemm_bf16_persistent<false>, dim3(num_ctas), dim3(kThreads), smem, s, ma, mb, p));
   return 0;
 }
 

@@ -28,6 +28,8 @@ def declare(lib) -> None:
     lib.dcp_tc_conv_strided.argtypes = [vp, vp, vp, vp] + [i] * 18 + [vp]
     lib.dcp_tc_conv_wgrad_strided.restype = C.c_int
     lib.dcp_tc_conv_wgrad_strided.argtypes = [vp, vp, vp] + [i] * 16 + [vp]
+    lib.dcp_gemm_set_workspace.restype = C.c_int
+    lib.dcp_gemm_set_workspace.argtypes = [vp, C.c_size_t]
     lib.dcp_conv_bf16_persistent.restype = C.c_int
     lib.dcp_conv_bf16_persistent.argtypes = [vp, vp, vp, vp] + [i] * 17 + [vp]
     lib.dcp_upsample2_zero.restype = C.c_int
@@ -68,9 +70,22 @@ PERSISTENT_CONV = os.environ.get("DCP_CONV_PERSISTENT", "1") == "1"     # bf16 i
 LINEAR_X3 = os.environ.get("DCP_LINEAR_PRECISION", "tf32x3") == "tf32x3"
 
 
+_workspace = None
+
+
+def _ensure_workspace(device) -> None:
+    """20 MB of scratch for the persistent GEMM's tail split (fp32 partial tiles of the last, partial wave); registered once."""
+    global _workspace
+    if _workspace is None and os.environ.get("DCP_GEMM_TAIL_SPLIT", "1") == "1":
+        _workspace = torch.empty(20 << 20, dtype=torch.uint8, device=device)
+        _lib.dcp_gemm_set_workspace(_workspace.data_ptr(), _workspace.numel())
+
+
 def gemm(A, B, out, bias, M, N, K, lda, ldb, ldc, a_mn, b_mn, relu=False, ksplit=1, x3=None) -> None:
     """out[M,N] (+)= op(A) op(B)^T on tcgen05 (see dcp_tc_gemm_ex)."""
     k = _k()
+    if A.dtype == torch.bfloat16 and _workspace is None:
+        _ensure_workspace(A.device)
     x3 = LINEAR_X3 if x3 is None else x3
     k._chk(_lib.dcp_tc_gemm_ex(A.data_ptr(), B.data_ptr(), out.data_ptr(), k._p(bias), M, N, K, lda, ldb, ldc, int(a_mn), int(b_mn), k._dt(A),
                                int(out.dtype == torch.bfloat16), int(bias is not None and bias.dtype == torch.bfloat16), int(relu), int(ksplit),

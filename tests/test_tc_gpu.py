@@ -153,7 +153,8 @@ def test_conv_wgrad_flat(N, Cout, W):
 
 
 @pytest.mark.parametrize("a_mn,b_mn", [(0, 0), (0, 1), (1, 1)])
-@pytest.mark.parametrize("M,N,K,ks", [(8192, 1000, 256, 1), (2048, 2304, 768, 1), (768, 768, 4096, 4), (136, 520, 192, 1)])
+@pytest.mark.parametrize("M,N,K,ks", [(8192, 1000, 256, 1), (2048, 2304, 768, 1), (768, 768, 4096, 4), (136, 520, 192, 1),
+                                      (8192, 768, 2048, 1), (8104, 760, 1024, 1)])       # the last two: 192 tiles = 148 + a 44-tile tail that is K-split
 def test_bf16_persistent_gemm(a_mn, b_mn, M, N, K, ks):
     """gemm_bf16_persistent.cu: several tiles per CTA (double-buffered TMEM accumulator), ragged M / N tiles, both tile widths,
     split-K through scratch, every operand-major combination used by Linear forward / dgrad / wgrad."""
