@@ -205,3 +205,16 @@ def test_convnet_forward_backward_matches_cpu():
         else:
             _cmp_norm(p.grad, q.grad, 6e-2, n)
     assert list(gpu.state_dict().keys()) == list(cpu.state_dict().keys())
+
+
+@pytest.mark.parametrize("M,C,dtype", [(8192, 3072, torch.bfloat16), (4100, 72, torch.float32), (3000, 768, torch.bfloat16), (100, 10, torch.float32)])
+def test_colsum_bias_gradient(M, C, dtype):
+    """dcp_colsum (bias gradients of Linear / conv): 16-byte kernel for aligned shapes, scalar kernel otherwise, vs an fp64 sum."""
+    from distributed_compute_pytorch_b200.ops import cuda
+    L = cuda.lib()
+    torch.manual_seed(M + C)
+    x = torch.randn(M, C, device=DEV).to(dtype)
+    out = torch.full((C,), float("nan"), device=DEV)
+    cuda._chk(L.dcp_colsum(x.data_ptr(), out.data_ptr(), M, C, cuda._dt(x), cuda._stream()))
+    ref = x.double().sum(0)
+    assert ((out.double() - ref).abs().max() / ref.abs().max()).item() < 1e-4
