@@ -29,6 +29,27 @@ class GPT2Config:
         return -(-self.vocab_size // 128) * 128
 
 
+class _SplitHeads(torch.autograd.Function):
+    """qkv [B*T, 3C] -> q, k, v as [B, H, T, D] strided views (no copies forward).  Backward writes dq / dk / dv straight into one
+    [B, T, 3, H, D] buffer (three strided copies) instead of autograd's zero-fill + add per selected slice."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, T, H):
+        D = qkv.shape[1] // (3 * H)
+        ctx.dims = (B, T, H, D)
+        v = qkv.view(B, T, 3, H, D)
+        return v[:, :, 0].transpose(1, 2), v[:, :, 1].transpose(1, 2), v[:, :, 2].transpose(1, 2)
+
+    @staticmethod
+    def backward(ctx, dq, dk, dv):
+        B, T, H, D = ctx.dims
+        out = torch.empty(B, T, 3, H, D, dtype=dq.dtype, device=dq.device)
+        out[:, :, 0].copy_(dq.transpose(1, 2))
+        out[:, :, 1].copy_(dk.transpose(1, 2))
+        out[:, :, 2].copy_(dv.transpose(1, 2))
+        return out.view(B * T, 3 * H * D), None, None, None
+
+
 class Block(nn.Module):
     def __init__(self, cfg: GPT2Config):
         super().__init__()
@@ -43,8 +64,7 @@ class Block(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, T, C = x.shape
-        qkv = self.attn_qkv(self.ln_1(x).view(B * T, C)).view(B, T, 3, self.n_head, C // self.n_head)
-        q, k, v = (qkv[:, :, i].transpose(1, 2) for i in range(3))
+        q, k, v = _SplitHeads.apply(self.attn_qkv(self.ln_1(x).view(B * T, C)), B, T, self.n_head)
         y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
         y = y.transpose(1, 2).reshape(B * T, C)
         x = x + self.attn_proj(y).view(B, T, C)
