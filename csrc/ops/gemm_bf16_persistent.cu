@@ -40,12 +40,6 @@ struct BfGemmParams {
 
 namespace {
 using namespace tc;
-#ifdef DCP_DEBUG_MBAR
-__device__ volatile int* g_pg_dbg = nullptr;
-#define PG_MARK(slot, v) do { if (g_pg_dbg && blockIdx.x == 0 && (threadIdx.x & 31) == 0) { g_pg_dbg[(threadIdx.x >> 5) * 4 + (slot)] = (v); __threadfence_system(); } } while (0)
-#else
-#define PG_MARK(slot, v) do {} while (0)
-#endif
 
 constexpr int kBM = 128, kBK = 64, kMaxStages = 6;
 constexpr int kThreads = 320, kEpiWarps = 8;
@@ -86,7 +80,6 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
   PPipe* pipe = reinterpret_cast<PPipe*>(smem + nstages * stage_bytes + kStgBytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
 
-  PG_MARK(0, 1);
   griddep_launch();
   if (warp == 0 && lane == 0) { tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); }
   if (warp == 1) {
@@ -96,17 +89,13 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       mbar_fence_init();
     }
     __syncwarp();
-    PG_MARK(0, 2);
     tmem_alloc<512>(&pipe->tmem_base);
-    PG_MARK(0, 3);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  PG_MARK(0, 4);
   const uint32_t tmem = *((volatile uint32_t*)&pipe->tmem_base);
   griddep_wait();
-  PG_MARK(0, 5);
 
   // work units: u -> (tile, k-slice); tiles run M-fastest so that one wave of CTAs shares a few B tiles
   const int tiles = p.tiles_m * p.tiles_n;
@@ -159,10 +148,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const uint32_t tacc = tmem + ab * 256;
       for (int ks = ks0; ks < ks1; ++ks, ++it) {
         const int st = it % nstages, ph = (it / nstages) & 1;
-        PG_MARK(1, 100 + it);
         mbar_wait(&pipe->full[st], ph);
         tc_fence_after();
-        PG_MARK(1, 200 + it);
         const uint32_t sa = smem_u32(smem + st * stage_bytes), sb = sa + kABytes;
         if (elect_one()) {
           const uint64_t da0 = p.a_mn ? make_smem_desc(sa, kBK * 128, 1024) : make_smem_desc(sa, 0, 1024);
@@ -188,10 +175,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       const int z = w.z, m_tile = w.m_tile, n_tile = w.n_tile, ks0 = w.ks0, ks1 = w.ks1;
       const bool have = ks1 > ks0;
       const int ab = tcount & 1, aph = (tcount >> 1) & 1;
-      PG_MARK(1, 10);
       mbar_wait(&pipe->acc_full[ab], aph);
       tc_fence_after();
-      PG_MARK(1, 11);
       const bool add_bias = p.bias != nullptr && p.partial_stride == 0 && w.part == nullptr;
       const long zoff = p.partial_stride ? (long)z * p.partial_stride : 0;
       const long row0 = (long)m_tile * kBM + lg * 32;
@@ -327,10 +312,8 @@ k_gemm_bf16_persistent(const __grid_constant__ CUtensorMap map_a, const __grid_c
       }
     }
   }
-  PG_MARK(2, 1);
   tc_fence_before();
   __syncthreads();
-  PG_MARK(2, 2);
   if (warp == 1) tmem_dealloc<512>(tmem);
 }
 
@@ -416,9 +399,6 @@ int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void
     DCP_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_bf16_persistent<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     attr = true;
   }
-#ifdef DCP_DEBUG_MBAR
-  if (const char* e = getenv("DCP_PGEMM_DBG_PTR")) { volatile int* ptr = (volatile int*)strtoull(e, nullptr, 0); cudaMemcpyToSymbol(g_pg_dbg, &ptr, sizeof ptr); }
-#endif
   CUtensorMap ma, mb;
   if (!a_mn) { if (encode_bf16_2d(&ma, A, M, K, lda, kBK, kBM)) return -1; }
   else { if (encode_bf16_2d(&ma, A, K, M, lda, 64, kBK)) return -1; }
