@@ -26,10 +26,10 @@ __global__ void __launch_bounds__(256) k_conv1_fwd(const float* __restrict__ x, 
   for (int i = threadIdx.x; i < 32 * 9; i += blockDim.x) sw[i] = w[i];
   if (threadIdx.x < 32) sb[threadIdx.x] = b[threadIdx.x];
   __syncthreads();
-  // 4 threads per pixel, 8 channels each
+  // 2 threads per pixel, 16 channels each: the 9 input taps are loaded once per 16 outputs and every thread writes 64 contiguous bytes
   const long gid = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  const long pix = gid >> 2;
-  const int cg = (int)(gid & 3) * 8;
+  const long pix = gid >> 1;
+  const int cg = (int)(gid & 1) * 16;
   if (pix >= total_pixels) return;
   const int n = (int)(pix / P1), q = (int)(pix % P1), h = q / HW1, wq = q % HW1;
   const float* xi = x + (long)n * 784 + h * 28 + wq;
@@ -38,17 +38,19 @@ __global__ void __launch_bounds__(256) k_conv1_fwd(const float* __restrict__ x, 
   for (int r = 0; r < 3; ++r)
 #pragma unroll
     for (int s = 0; s < 3; ++s) v[r * 3 + s] = __ldg(xi + r * 28 + s);
-  float o[8];
-#pragma unroll
-  for (int c = 0; c < 8; ++c) {
-    float acc = sb[cg + c];
-#pragma unroll
-    for (int t = 0; t < 9; ++t) acc = fmaf(v[t], sw[(cg + c) * 9 + t], acc);
-    o[c] = fmaxf(acc, 0.f);
-  }
   float4* dst = reinterpret_cast<float4*>(a1 + pix * 32 + cg);
-  dst[0] = make_float4(o[0], o[1], o[2], o[3]);
-  dst[1] = make_float4(o[4], o[5], o[6], o[7]);
+#pragma unroll
+  for (int c4 = 0; c4 < 4; ++c4) {
+    float o[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      float acc = sb[cg + c4 * 4 + c];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) acc = fmaf(v[t], sw[(cg + c4 * 4 + c) * 9 + t], acc);
+      o[c] = fmaxf(acc, 0.f);
+    }
+    dst[c4] = make_float4(o[0], o[1], o[2], o[3]);
+  }
 }
 
 // grid (12 pooled rows, N); 256 threads.  a2 rows 2*ph, 2*ph+1 of image n -> pooled[n][c][ph][0..11]
@@ -277,7 +279,7 @@ extern "C" {
 
 int dcp_convnet_conv1_fwd(const float* x, const float* w, const float* b, float* a1, int N, cudaStream_t s) {
   const long pixels = (long)N * P1;
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_fwd, dim3((unsigned)((pixels * 4 + 255) / 256)), dim3(256), 0, s, x, w, b, a1, pixels)); return 0;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_fwd, dim3((unsigned)((pixels * 2 + 255) / 256)), dim3(256), 0, s, x, w, b, a1, pixels)); return 0;
 }
 int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float p, unsigned long long seed, unsigned long long stream,
                          const void* step, int training, cudaStream_t s) {
