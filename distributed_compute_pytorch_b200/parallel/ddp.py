@@ -269,7 +269,15 @@ class DistributedDataParallel(nn.Module):
                 bucket.flat.copy_(out)
             return
         if self._cuda_backend is not None:
+            timing = getattr(self, "_comm_timing", None)
+            if timing is not None:      # opt-in (enable_comm_timing): CUDA events on the side stream around this bucket's collective
+                be = self._cuda_backend
+                be.comm_stream.wait_stream(torch.cuda.current_stream(be._torch_dev))
+                e0 = torch.cuda.Event(enable_timing=True); e0.record(be.comm_stream)
             bucket.work_event = self._cuda_backend.all_reduce_async(bucket.flat, ReduceOp.AVG, max_ctas=self.comm_ctas)
+            if timing is not None:
+                e1 = torch.cuda.Event(enable_timing=True); e1.record(be.comm_stream)
+                timing.append((bucket.index, bucket.flat.numel() * bucket.flat.element_size(), e0, e1))
         else:
             dist.all_reduce(bucket.flat, ReduceOp.AVG)
 
@@ -328,7 +336,32 @@ class DistributedDataParallel(nn.Module):
             with torch.no_grad():
                 broadcast_coalesced(bufs, 0)
 
+    def enable_comm_timing(self, on: bool = True) -> None:
+        """Record CUDA events around every gradient bucket's all-reduce; read them with ``comm_timings()``.
+        Not for use inside a captured CUDA graph."""
+        self._comm_timing = [] if on else None
+
+    def comm_timings(self, clear: bool = True):
+        """[(bucket index, bytes, milliseconds on the side stream)] since the last call (synchronises)."""
+        rec = getattr(self, "_comm_timing", None) or []
+        if rec:
+            torch.cuda.synchronize()
+        out = [(i, nbytes, e0.elapsed_time(e1)) for i, nbytes, e0, e1 in rec]
+        if clear and getattr(self, "_comm_timing", None) is not None:
+            self._comm_timing = []
+        return out
+
     def forward(self, *inputs, **kwargs):
+        nvtx = torch.cuda.is_available() and torch.cuda.is_initialized()
+        if nvtx:
+            torch.cuda.nvtx.range_push("DistributedDataParallel.forward")
+        try:
+            return self._forward(*inputs, **kwargs)
+        finally:
+            if nvtx:
+                torch.cuda.nvtx.range_pop()
+
+    def _forward(self, *inputs, **kwargs):
         if self.world_size > 1:
             if torch.is_grad_enabled() and self.require_backward_grad_sync:
                 self._maybe_rebuild_buckets()

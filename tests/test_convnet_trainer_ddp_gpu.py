@@ -55,6 +55,18 @@ def _worker(rank, world, port):
     # rank r's buffer = momentum-blend of rank 0's previous buffer with rank r's own last batch statistics
     assert (rm - rm0).abs().max().item() < 1.0, (rm - rm0).abs().max().item()
     assert torch.isfinite(flat).all()
+
+    # the library reducer path (autograd hooks) with per-bucket collective timing switched on
+    torch.manual_seed(0)
+    net2 = dcp.models.ConvNet().to(dev).train()
+    ddp2 = dcp.DistributedDataParallel(net2, device_ids=[rank])
+    ddp2.enable_comm_timing()
+    for i in range(2):
+        ddp2.zero_grad()
+        ops.nll_loss(ddp2(xs[i]), ys[i]).backward()
+    rec = ddp2.comm_timings()
+    assert len(rec) >= 3 and all(ms >= 0.0 and nbytes > 0 for _, nbytes, ms in rec), rec       # 1 bucket in step 1, 2 after the rebuild
+    assert max(nb for _, nb, _ in rec) >= 4725288        # the big bucket (fc1.weight & co.) went through the timed path
     dist.barrier()
     dist.destroy_process_group()
 
