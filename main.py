@@ -106,9 +106,16 @@ def proc(rank, world_size, opt, use_cuda):
     optimizer = ops.Adadelta(model.parameters(), lr=opt.lr)
     scheduler = ops.StepLR(optimizer, step_size=1, gamma=opt.gamma)
 
-    from distributed_compute_pytorch_b200.utils import Tracer
+    from distributed_compute_pytorch_b200.utils import Tracer, load_model, load_training_state, save_training_state
     tracer = Tracer(rank=rank)                 # DCP_TRACE=<prefix> writes <prefix>_rank<r>.json (chrome://tracing) at the end
-    for epoch in range(opt.epochs):
+    start_epoch = 0
+    if opt.resume and os.path.exists(opt.checkpoint):      # not in the reference (save-only): model file + optimizer / schedule / epoch sidecar
+        load_model(opt.checkpoint, model)
+        if os.path.exists(opt.checkpoint + ".state"):
+            start_epoch = int(load_training_state(opt.checkpoint + ".state", optimizer, scheduler).get("epoch") or 0)
+        if rank == 0:
+            print(f"resumed from {opt.checkpoint} at epoch {start_epoch}")
+    for epoch in range(start_epoch, opt.epochs):
         t0 = time.time()
         with tracer.range(f"train epoch {epoch}"):
             train(opt, model, rank, train_loader, optimizer, epoch, device)
@@ -119,8 +126,10 @@ def proc(rank, world_size, opt, use_cuda):
     if tracer.enabled:
         tracer.export_chrome(f"{os.environ['DCP_TRACE']}_rank{rank}.json")
     if rank == 0:
-        torch.save(model.state_dict(), opt.checkpoint)
+        torch.save(model.state_dict(), opt.checkpoint)      # rank 0 only (every rank writes the same file in the reference, ref:main.py:133)
     dist.barrier()
+    if opt.resume:
+        save_training_state(opt.checkpoint + ".state", optimizer, scheduler, epoch=opt.epochs)
     cleanup()
 
 
@@ -142,6 +151,7 @@ def build_parser():
     parser.add_argument('--backend', default=None, help="gloo|nccl|b200|cpu (default: GPU backend iff CUDA)")
     parser.add_argument('--max-steps', type=int, default=0, help="stop each epoch pass after this many batches (0 = all)")
     parser.add_argument('--checkpoint', default="mnist.pt")
+    parser.add_argument('--resume', action='store_true', help="continue from --checkpoint (+ .state sidecar) and write the sidecar at the end")
     return parser
 
 

@@ -59,3 +59,34 @@ def test_tracer_cpu(tmp_path):
     with off.range("x"):
         pass
     assert off.summary() == {}
+
+
+def test_checkpoint_helpers_roundtrip(tmp_path):
+    """utils.checkpoint: reference-format model file (module.* prefix handling both ways) + training-state sidecar."""
+    import torch
+    import distributed_compute_pytorch_b200 as dcp
+    from distributed_compute_pytorch_b200 import ops
+    from distributed_compute_pytorch_b200.utils import save_model, load_model, save_training_state, load_training_state
+    torch.manual_seed(0)
+    m = dcp.models.ConvNet()
+    opt = ops.Adadelta(m.parameters(), lr=0.5); sch = ops.StepLR(opt, 1, 0.7)
+    x = torch.randn(4, 1, 28, 28); y = torch.randint(0, 10, (4,))
+    ops.nll_loss(m(x), y).backward(); opt.step(); sch.step()
+    path = str(tmp_path / "mnist.pt")
+    save_model(path, m); save_training_state(path + ".state", opt, sch, epoch=1)
+    sd = torch.load(path)
+    assert list(sd.keys())[0] == "conv1.weight" and len(sd) == 13 and tuple(sd["fc1.weight"].shape) == (128, 9216)
+    # load into a "DDP-shaped" wrapper (module.* keys) and back into a plain model
+    class Wrap(torch.nn.Module):
+        def __init__(self, mod):
+            super().__init__(); self.module = mod
+    w = Wrap(dcp.models.ConvNet()); load_model(path, w)
+    assert torch.equal(w.module.fc2.weight, m.fc2.weight)
+    torch.save(w.state_dict(), path)                       # module.* keys, as the reference writes under DDP
+    m2 = dcp.models.ConvNet(); load_model(path, m2)
+    assert torch.equal(m2.conv2.weight, m.conv2.weight)
+    opt2 = ops.Adadelta(m2.parameters(), lr=0.5); sch2 = ops.StepLR(opt2, 1, 0.7)
+    st = load_training_state(path + ".state", opt2, sch2)
+    assert st["epoch"] == 1 and sch2.last_epoch == sch.last_epoch
+    a = opt.state_dict()["state"][0]["square_avg"]; b = opt2.state_dict()["state"][0]["square_avg"]
+    assert torch.equal(a, b)
