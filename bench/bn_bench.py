@@ -1,5 +1,6 @@
-import sys, torch
-sys.path.insert(0, '/root/repo')
+"""Isolated timing of the BatchNorm kernels (dcp_bn_stats / apply / bwd) on ResNet-50 shaped activations."""
+import os, sys, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from distributed_compute_pytorch_b200.ops import cuda as K
 L = K.lib(); s = K._stream
 def t(fn, n=20):

@@ -1,6 +1,6 @@
 """Isolated timing of dcp_fused_rs_opt_ag (AdamW) on a 32 M-element bucket; world size = number of spawned ranks."""
 import ctypes as C, os, sys, torch
-sys.path.insert(0, '/root/repo')
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import distributed_compute_pytorch_b200 as dcp
 from tests.helpers import free_port, init
 

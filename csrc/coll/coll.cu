@@ -114,7 +114,18 @@ __global__ void __launch_bounds__(kThreads) k_allreduce_twoshot(DcpDevCtx c, con
   const size_t v0 = s.begin + ((tid + stride - (s.begin % stride)) % stride);
   if constexpr (kNvls && NvlsOk<T>::value) {
     char* mc = c.mc + off;
-    for (size_t v = v0; v < s.end; v += stride) {
+    // four independent in-switch reductions in flight per thread before the (posted) multicast stores: one multimem.ld_reduce
+    // is a full round trip through NVSwitch, so the loop is latency-bound unless several overlap - with them the kernel needs
+    // a quarter of the CTAs for the same time, which is what lets a gradient bucket hide under the backward pass
+    size_t v = v0;
+    for (; v + 3 * stride < s.end; v += 4 * stride) {
+      uint4 r0 = multimem_ld_reduce_add<T>(mc + v * 16), r1 = multimem_ld_reduce_add<T>(mc + (v + stride) * 16);
+      uint4 r2 = multimem_ld_reduce_add<T>(mc + (v + 2 * stride) * 16), r3 = multimem_ld_reduce_add<T>(mc + (v + 3 * stride) * 16);
+      if (op == DCP_AVG) { r0 = vec_scale<T>(r0, scale); r1 = vec_scale<T>(r1, scale); r2 = vec_scale<T>(r2, scale); r3 = vec_scale<T>(r3, scale); }
+      multimem_st16(mc + v * 16, r0); multimem_st16(mc + (v + stride) * 16, r1);
+      multimem_st16(mc + (v + 2 * stride) * 16, r2); multimem_st16(mc + (v + 3 * stride) * 16, r3);
+    }
+    for (; v < s.end; v += stride) {
       uint4 r = multimem_ld_reduce_add<T>(mc + v * 16);
       if (op == DCP_AVG) r = vec_scale<T>(r, scale);
       multimem_st16(mc + v * 16, r);
@@ -372,7 +383,6 @@ __global__ void __launch_bounds__(kThreads) k_send(DcpDevCtx c, const char* __re
   copy_bytes(slot + lo, in + lo, hi - lo, threadIdx.x, blockDim.x, true);
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
     st_release_sys(p2p_word(c.peer[dst], DcpHeapLayout::kP2PFlagOff, c.rank, b), seq);
     *seqp = seq;
   }
@@ -392,7 +402,6 @@ __global__ void __launch_bounds__(kThreads) k_recv(DcpDevCtx c, char* __restrict
   copy_bytes(out + lo, slot + lo, hi - lo, threadIdx.x, blockDim.x, false);
   __syncthreads();
   if (threadIdx.x == 0) {
-    __threadfence_system();
     st_release_sys(p2p_word(c.peer[src], DcpHeapLayout::kP2PAckOff, c.rank, b), seq);
     *seqp = seq;
   }

@@ -145,7 +145,8 @@ __device__ __forceinline__ void dcp_barrier(const DcpDevCtx& c, int chan) {
   const uint32_t e = *((volatile uint32_t*)ep) + 1;
   if (threadIdx.x < c.world) {
     const int peer = threadIdx.x;
-    __threadfence_system();
+    // the release store is cumulative over everything the CTA wrote before the __syncthreads() above: no separate fence
+    // (st.release.sys already costs one system-scope drain; a second __threadfence_system() in front doubled it)
     st_release_sys(dcp_sig(c.peer[peer], chan, blockIdx.x, c.rank), e);
     wait_ge(c, dcp_sig(me, chan, blockIdx.x, peer), e);
   }
@@ -158,10 +159,7 @@ __device__ __forceinline__ uint32_t dcp_signal_all(const DcpDevCtx& c, int chan)
   __syncthreads();
   char* me = c.peer[c.rank];
   const uint32_t e = *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x)) + 1;
-  if (threadIdx.x < c.world) {
-    __threadfence_system();
-    st_release_sys(dcp_sig(c.peer[threadIdx.x], chan, blockIdx.x, c.rank), e);
-  }
+  if (threadIdx.x < c.world) st_release_sys(dcp_sig(c.peer[threadIdx.x], chan, blockIdx.x, c.rank), e);
   return e;
 }
 __device__ __forceinline__ void dcp_wait_all(const DcpDevCtx& c, int chan, uint32_t e) {

@@ -29,7 +29,7 @@ struct FlatConvParams {
   float* out; const float* bias; const float* mask;
   int tiles;
   int use_base_offset;
-  long long* dbg;         // optional: per-CTA clock64 trace (CTA 0 only), see scratch/dbg_flat_trace.py
+  long long* dbg;         // optional: per-CTA clock64 trace (CTA 0 only); -DDCP_TRACE builds only
 };
 
 namespace {
@@ -92,7 +92,11 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *((volatile uint32_t*)&bars->tmem_base);
+#ifdef DCP_TRACE      // clock64 trace of CTA 0 (build with DCP_NVCC_EXTRA=-DDCP_TRACE); compiled out of the production library
   long long* dbg = (p.dbg && blockIdx.x == 0) ? p.dbg : nullptr;
+#else
+  constexpr long long* dbg = nullptr;
+#endif
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   const int my_tiles = (p.tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
 
@@ -271,8 +275,12 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   for (int t = 0; t < taps; ++t) { p.off[t] = off[t]; mn = off[t] < mn ? off[t] : mn; mx = off[t] > mx ? off[t] : mx; }
   p.min_off = mn; p.span = mx - mn;
   p.tiles = (int)((P + kBM - 1) / kBM);
-  { const char* e = getenv("DCP_FLAT_BASEOFF"); p.use_base_offset = e ? atoi(e) : 0; }
+  { static const int base_off = [] { const char* e = getenv("DCP_FLAT_BASEOFF"); return e ? atoi(e) : 0; }(); p.use_base_offset = base_off; }
+#ifdef DCP_TRACE
   { const char* e = getenv("DCP_FLAT_DBG_PTR"); p.dbg = e ? (long long*)strtoull(e, nullptr, 0) : nullptr; }
+#else
+  p.dbg = nullptr;
+#endif
   const int halo_rows = (kBM + p.span + 7) / 8 * 8;
   if (halo_rows > 256) { dcp_set_error("flat conv: halo of %d rows exceeds one TMA box", halo_rows); return -1; }
   const int cch = Cin / 32;

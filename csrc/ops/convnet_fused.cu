@@ -11,7 +11,9 @@
 //   conv1_wgrad    dz1[N*676, 32], x -> dw1[32, 9], db1[32] (per-CTA partials, last CTA sums)  (backward of K1)
 #include <cstdlib>
 
+#include "ops/dp_push.cuh"
 #include "ops/ops_common.cuh"
+#include "ops/optim_math.cuh"
 
 namespace {
 
@@ -147,13 +149,53 @@ struct C1AllReduce {
   DcpDevCtx c;
 };
 
+// Low-latency exchange + optimizer update inside the last CTA (ll.on): the 320 sums go to every rank as 8-byte {value, step}
+// words - the flag travels WITH the data (an aligned 8-byte store is single-copy atomic), so there is no fence, no separate
+// signal and no kernel boundary between "gradient ready" and "gradient averaged": the CTA stores, polls the W words of each
+// element until they carry this step's number, averages, writes dw1 / db1 and applies the optimizer update of conv1's
+// parameters on the spot.  Block layout at heap offset `off` on every rank: [2 halves][W source ranks][320] x {f32, u32}.
+struct C1LL {
+  int on, kind;
+  size_t off;
+  const long long* step;
+  const DcpOptEntry* rows;    // [0] conv1.weight (288 elements), [1] conv1.bias (32)
+  const float* hp;
+  DcpDevCtx c;
+};
+// one aligned 64-bit scalar access each way: value in the low word, flag in the high word
+__device__ __forceinline__ void st_relaxed_sys_v2(void* p, uint32_t a, uint32_t b) {
+  const unsigned long long w = ((unsigned long long)b << 32) | a;
+  asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(w) : "memory");
+}
+__device__ __forceinline__ uint2 ld_relaxed_sys_v2(const void* p) {
+  unsigned long long w;
+  asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(w) : "l"(p) : "memory");
+  return make_uint2((uint32_t)w, (uint32_t)(w >> 32));
+}
+template <int KIND> __device__ __forceinline__ void c1_update(const DcpOptEntry& e, int i, float g, const float* hp) {
+  const OptHyper H = load_hyper<KIND>(hp);
+  float p = e.p[i], s1 = e.s1 ? e.s1[i] : 0.f, s2 = e.s2 ? e.s2[i] : 0.f;
+  opt_update_h<KIND>(p, g * hp[7], s1, s2, H);
+  e.p[i] = p;
+  if (e.s1) e.s1[i] = s1;
+  if (e.s2) e.s2[i] = s2;
+}
+
+// ws_part / ws_ticket: caller-owned partial table ([gridDim.x][320] floats) and ticket word (zero between launches); null = the
+// library's own device-resident pair (one per GPU: launches that use it must not overlap).
+// dp.on: instead of writing dw1 / db1 the last CTA pushes the 320 sums into its slot of every rank's payload block and
+// signals (ops/dp_push.cuh); the consumer kernel averages and writes the gradients.
 __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __restrict__ dz1, const float* __restrict__ x, float* __restrict__ dw1,
-                                                               float* __restrict__ db1, long total_pixels, const C1AllReduce ar) {
+                                                               float* __restrict__ db1, long total_pixels, const C1AllReduce ar,
+                                                               float* __restrict__ ws_part, unsigned* __restrict__ ws_ticket, const DpPush dp,
+                                                               const C1LL ll) {
   __shared__ float red[kC1Lanes][32][11];
   __shared__ float sx[784];
   __shared__ bool last;
   griddep_launch();
   griddep_wait();
+  float (*part_tab)[320] = ws_part ? reinterpret_cast<float (*)[320]>(ws_part) : g_c1w_part;
+  unsigned* ticket = ws_ticket ? ws_ticket : &g_c1w_ticket;
   const int c = threadIdx.x & 31, lane = threadIdx.x >> 5;       // c: lane in warp, lane: warp index ("pixel lane")
   // main loop: a thread owns 4 channels (16-byte loads, 8 threads cover the 32 channels of a pixel) of every 4th
   // pixel its warp takes; one warp instruction brings 4 pixels, kC1Fly of them are in flight
@@ -207,11 +249,11 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
     float s = 0.f;
 #pragma unroll
     for (int l = 0; l < kC1Lanes; ++l) s += red[l][cc][t];
-    g_c1w_part[blockIdx.x][threadIdx.x] = s;
+    part_tab[blockIdx.x][threadIdx.x] = s;
     __threadfence();
   }
   __syncthreads();
-  if (threadIdx.x == 0) last = atomicAdd(&g_c1w_ticket, 1u) == gridDim.x - 1;
+  if (threadIdx.x == 0) last = atomicAdd(ticket, 1u) == gridDim.x - 1;
   __syncthreads();
   if (!last) return;
   __threadfence();
@@ -222,7 +264,7 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
   for (int k = 0; k < 10; ++k) t10[k] = 0.f;
 #pragma unroll 5
   for (int b = lane; b < (int)gridDim.x; b += kC1Lanes) {
-    const float* part = &g_c1w_part[b][c];
+    const float* part = &part_tab[b][c];
 #pragma unroll
     for (int k = 0; k < 10; ++k) t10[k] += __ldcg(part + 32 * k);
   }
@@ -230,15 +272,65 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
 #pragma unroll
   for (int k = 0; k < 10; ++k) red2[lane * 320 + c + 32 * k] = t10[k];
   __syncthreads();
+  float tot = 0.f;
   if (threadIdx.x < 320) {
     const int cc = threadIdx.x / 10, t = threadIdx.x % 10;
-    float tot = 0.f;
 #pragma unroll
     for (int l = 0; l < kC1Lanes; ++l) tot += red2[l * 320 + threadIdx.x];
-    if (!ar.on) { if (t < 9) dw1[cc * 9 + t] = tot; else db1[cc] = tot; }
-    else red2[threadIdx.x] = tot;              // keep for the exchange below (row 0 of red2 is this thread's own column)
+    if (!ar.on && !dp.on && !ll.on) { if (t < 9) dw1[cc * 9 + t] = tot; else db1[cc] = tot; }
+    else if (ar.on) red2[threadIdx.x] = tot;   // keep for the exchange below (row 0 of red2 is this thread's own column)
   }
-  if (threadIdx.x == 0) g_c1w_ticket = 0;
+  if (threadIdx.x == 0) *ticket = 0;
+  if (ll.on) {
+    __syncthreads();
+    if (threadIdx.x < 320) { const int cc = threadIdx.x / 10, t = threadIdx.x % 10; red2[t < 9 ? cc * 9 + t : 288 + cc] = tot; }   // bucket order
+    __syncthreads();
+    if (threadIdx.x >= 320) return;
+    const DcpDevCtx& cx = ll.c;
+    const int W = cx.world, i = threadIdx.x;
+    const uint32_t epoch = (uint32_t)(*ll.step);
+    const size_t half_off = ll.off + (size_t)(epoch & 1u) * W * 320 * 8;
+    const float mine = red2[i];
+    for (int p = 0; p < W; ++p) st_relaxed_sys_v2(cx.peer[p] + half_off + ((size_t)cx.rank * 320 + i) * 8, __float_as_uint(mine), epoch);
+    const char* slots = cx.peer[cx.rank] + half_off + (size_t)i * 8;
+    float sum = 0.f;
+    bool ok = true;
+    const unsigned long long tw0 = i == 0 ? globaltimer_ns() : 0ull;
+    for (int p = 0; p < W && ok; ++p) {
+      const char* w = slots + (size_t)p * 320 * 8;
+      uint2 v = ld_relaxed_sys_v2(w);
+      if (v.y != epoch) {
+        const unsigned long long t0 = globaltimer_ns();
+        for (;;) {
+#pragma unroll 1
+          for (int k = 0; k < 64 && v.y != epoch; ++k) v = ld_relaxed_sys_v2(w);
+          if (v.y == epoch) break;
+          if (globaltimer_ns() - t0 > cx.timeout_ns) { if (cx.err) *((volatile int*)cx.err) = 1; ok = false; break; }
+        }
+      }
+      sum += __uint_as_float(v.x);
+    }
+    if (!ok) return;          // a peer never delivered: leave the parameters alone, the host sees the error flag
+    // bookkeeping for bench/step_ablation.py: total time element 0 spent waiting for the peers' words (= rank skew + NVLink flight)
+    if (i == 0) *reinterpret_cast<unsigned long long*>(ticket + 2) += globaltimer_ns() - tw0;
+    sum *= 1.f / (float)W;
+    const DcpOptEntry e = ll.rows[i < 288 ? 0 : 1];
+    const int j = i < 288 ? i : i - 288;
+    const_cast<float*>(static_cast<const float*>(e.g))[j] = sum;      // .grad holds the averaged gradient, as after DDP's all-reduce
+    if (ll.kind == 0) c1_update<0>(e, j, sum, ll.hp); else if (ll.kind == 1) c1_update<1>(e, j, sum, ll.hp); else c1_update<2>(e, j, sum, ll.hp);
+    return;
+  }
+  if (dp.on) {
+    // push-only tail: the sums go out in the order the gradient bucket stores them (dw1 [32][9], then db1 [32])
+    __syncthreads();
+    if (threadIdx.x < 320) { const int cc = threadIdx.x / 10, t = threadIdx.x % 10; red2[t < 9 ? cc * 9 + t : 288 + cc] = tot; }
+    __syncthreads();
+    const size_t slot_off = dp_slot_off(dp, (unsigned)(*dp.step) & 1u);
+    if (threadIdx.x < 80) dp_push4(dp, slot_off, (size_t)threadIdx.x * 4, *reinterpret_cast<const float4*>(red2 + threadIdx.x * 4));
+    __syncthreads();
+    dp_signal(dp);
+    return;
+  }
   if (!ar.on) return;
   // ---- all-reduce (AVG) of the 320 sums across the ranks, by this one CTA ----
   const DcpDevCtx& cx = ar.c;
@@ -254,7 +346,6 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
   }
   __syncthreads();
   if (threadIdx.x < W) {
-    __threadfence_system();
     st_release_sys(dcp_sig(cx.peer[threadIdx.x], ar.chan, ar.blk, cx.rank), s_epoch);
     wait_ge(cx, dcp_sig(me, ar.chan, ar.blk, threadIdx.x), s_epoch);
   }
@@ -293,7 +384,9 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
 // (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s) {
   C1AllReduce ar{};
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar)); return 0;
+  DpPush dp{};
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar,
+                                (float*)nullptr, (unsigned*)nullptr, dp, C1LL{})); return 0;
 }
 // The same kernel with the data-parallel all-reduce (AVG over the ranks of symmetric heap `h`) of dw1 / db1 fused into its last
 // CTA.  payload: a block of 2 * world * 320 floats INSIDE the symmetric heap, allocated in the same order on every rank and
@@ -312,7 +405,55 @@ int dcp_convnet_conv1_wgrad_allreduce(void* h, const float* dz1, const float* x,
   if (chan < 0 || chan >= DCP_NUM_CHANNELS || blk < 0 || blk >= DCP_MAX_BLOCKS) { dcp_set_error("conv1 wgrad + all-reduce: bad signal slot (%d, %d)", chan, blk); return -1; }
   C1AllReduce ar{};
   ar.on = c.world > 1; ar.chan = chan; ar.blk = blk; ar.pay_off = (size_t)(pay - base); ar.c = c;
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar)); return 0;
+  DpPush dp{};
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, dw1, db1, (long)N * P1, ar,
+                                (float*)nullptr, (unsigned*)nullptr, dp, C1LL{})); return 0;
+}
+// Push-only variant for the fused data-parallel tail (ops/dp_push.cuh, convnet_dp.cu): the 320 sums go into this rank's slot
+// (floats [elem_off, elem_off + 320) in bucket order: dw1 then db1) of every rank's payload block, followed by one signal per
+// rank on (chan, blk); dw1 / db1 are NOT written - dcp_dp_tail produces the averaged gradients.  ws: caller-owned scratch of
+// 4 + 148 * 320 floats (ticket word + per-CTA partial sums), zero before the first call; one per concurrent user.
+int dcp_convnet_conv1_wgrad_push(void* h, const float* dz1, const float* x, int N, void* payload, unsigned slot_elems, unsigned elem_off,
+                                 int chan, int blk, const void* step, void* ws, cudaStream_t s) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  const char* base = c.peer[c.rank];
+  const char* pay = static_cast<const char*>(payload);
+  if (pay < base || pay + (size_t)2 * c.world * slot_elems * 4 > base + dcp_symm_bytes(h) || ((pay - base) & 15) || (slot_elems & 3) || (elem_off & 3) ||
+      elem_off + 320 > slot_elems) {
+    dcp_set_error("conv1 wgrad push: the payload block must be a 16-byte aligned region of the symmetric heap holding 2 * world * slot_elems floats"); return -1;
+  }
+  if (chan < 0 || chan >= DCP_NUM_CHANNELS || blk < 0 || blk >= DCP_MAX_BLOCKS || !ws || !step) { dcp_set_error("conv1 wgrad push: bad arguments"); return -1; }
+  C1AllReduce ar{};
+  DpPush dp{};
+  dp.on = 1; dp.chan = chan; dp.blk = blk; dp.nvls = dp_use_nvls(c); dp.pay_off = (size_t)(pay - base); dp.slot_elems = slot_elems; dp.elem_off = elem_off;
+  dp.step = static_cast<const long long*>(step); dp.ticket = nullptr; dp.c = c;
+  unsigned* ticket = static_cast<unsigned*>(ws);
+  float* part = static_cast<float*>(ws) + 4;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, (float*)nullptr, (float*)nullptr,
+                                (long)N * P1, ar, part, ticket, dp, C1LL{})); return 0;
+}
+// conv1's weight-gradient, its data-parallel average and its optimizer update in ONE kernel (struct C1LL above).  ll_block: a
+// region of the symmetric heap holding 2 * world * 320 * 8 bytes, at the same offset on every rank, zeroed before first use and
+// used by nothing else; rows: two rows of the optimizer's device pointer table - conv1.weight, conv1.bias - whose grad pointers
+// receive the averaged gradient; hp / kind as for dcp_optim_step (dcp_optim_advance'd by the caller); step: device int64
+// counter holding the same (non-zero, increasing) value on every rank when the kernel runs; ws: 4 + 148 * 320 floats of
+// caller-owned scratch, zero before the first call.
+int dcp_convnet_conv1_wgrad_ll(void* h, const float* dz1, const float* x, int N, void* ll_block, const void* rows, const float* hp, int kind,
+                               const void* step, void* ws, cudaStream_t s) {
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  const char* base = c.peer[c.rank];
+  const char* blk = static_cast<const char*>(ll_block);
+  if (blk < base || blk + (size_t)2 * c.world * 320 * 8 > base + dcp_symm_bytes(h) || ((blk - base) & 15)) {
+    dcp_set_error("conv1 wgrad ll: ll_block must be a 16-byte aligned region of the symmetric heap holding 2 * world * 320 * 8 bytes"); return -1;
+  }
+  if (!rows || !hp || !step || !ws || kind < 0 || kind > 2) { dcp_set_error("conv1 wgrad ll: bad arguments"); return -1; }
+  C1LL ll{};
+  ll.on = 1; ll.kind = kind; ll.off = (size_t)(blk - base); ll.step = static_cast<const long long*>(step);
+  ll.rows = static_cast<const DcpOptEntry*>(rows); ll.hp = hp; ll.c = c;
+  unsigned* ticket = static_cast<unsigned*>(ws);
+  float* part = static_cast<float*>(ws) + 4;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_conv1_wgrad, dim3(N < kC1Blocks ? N : kC1Blocks), dim3(kC1Lanes * 32), 0, s, dz1, x, (float*)nullptr, (float*)nullptr,
+                                (long)N * P1, C1AllReduce{}, part, ticket, DpPush{}, ll)); return 0;
 }
 
 }  // extern "C"
@@ -335,6 +476,10 @@ constexpr int HF = 128, HC = 10, HMAXN = 128;
 constexpr int HCL = 8, HFL = HF / HCL;          // cluster size, features per CTA
 constexpr int HT = 512, HRG = HT / HFL, HR = HMAXN / HRG;   // threads, row groups (32), rows per thread (4)
 
+// Data-parallel BatchNorm buffers: `off` = heap offset of a block [running_mean 128][running_var 128][num_batches_tracked int64]
+// that exists at the same offset on every rank; run_mean / run_var / nbt of the launch point into this rank's copy.
+struct HeadBnPush { int on; size_t off; DcpDevCtx c; };
+
 struct __align__(16) HeadSmem {
   float xhat[HMAXN][HFL + 1];
   float h3[HMAXN][HFL + 1];
@@ -355,11 +500,6 @@ __device__ __forceinline__ float head_colsum(HeadSmem& S, float v, int slot, int
   return v;
 }
 
-// optional globaltimer trace of CTA 0 / thread 0 (env DCP_HEAD_DBG_PTR, scratch/dbg_head_trace.py)
-__device__ unsigned long long* g_head_dbg = nullptr;
-__device__ __forceinline__ void head_mark(int i) {
-  if (g_head_dbg && blockIdx.x == 0 && threadIdx.x == 0) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); g_head_dbg[i] = t; }
-}
 
 __global__ void __cluster_dims__(HCL, 1, 1) __launch_bounds__(HT, 1)
 k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ target, const float* __restrict__ gamma, const float* __restrict__ beta,
@@ -367,11 +507,11 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
                const float* __restrict__ b2, float* __restrict__ loss_out, float* __restrict__ logits_out, float* __restrict__ dh1,
                float* __restrict__ dgamma, float* __restrict__ dbeta, float* __restrict__ dw2, float* __restrict__ db2,
                float* __restrict__ dbias1, int N, float eps,
-               float momentum, float p2, unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training) {
+               float momentum, float p2, unsigned long long seed, unsigned long long stream, const long long* __restrict__ step, int training,
+               const HeadBnPush bp) {
   __shared__ HeadSmem S;
   griddep_launch();
   griddep_wait();
-  head_mark(0);
   cg::cluster_group cluster = cg::this_cluster();
   const int rank = (int)cluster.block_rank();
   const int tid = threadIdx.x, fl = tid & (HFL - 1), rg = tid >> 4, warp = tid >> 5, lane = tid & 31;
@@ -407,13 +547,28 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     S.stat[1][tid] = rsqrtf(var + eps);
     if (training && run_mean) {
       const float unbiased = N > 1 ? var * (float)N / (float)(N - 1) : var;
-      run_mean[f0 + tid] = (1.f - momentum) * run_mean[f0 + tid] + momentum * mu;
-      run_var[f0 + tid] = (1.f - momentum) * run_var[f0 + tid] + momentum * unbiased;
+      const float nm = (1.f - momentum) * run_mean[f0 + tid] + momentum * mu;
+      const float nv = (1.f - momentum) * run_var[f0 + tid] + momentum * unbiased;
+      if (!bp.on) { run_mean[f0 + tid] = nm; run_var[f0 + tid] = nv; }
+      else if (bp.c.rank == 0) {
+        // data-parallel buffer sync folded into the kernel: rank 0's running statistics are THE running statistics
+        // (DistributedDataParallel broadcasts rank 0's buffers before every forward); rank 0 writes them into every
+        // rank's copy, the other ranks leave theirs alone
+        for (int p = 0; p < bp.c.world; ++p) {
+          float* dst = reinterpret_cast<float*>(bp.c.peer[p] + bp.off);
+          dst[f0 + tid] = nm; dst[HF + f0 + tid] = nv;
+        }
+      }
     }
   }
-  if (rank == 0 && tid == 0 && training && nbt) *nbt += 1;
+  if (rank == 0 && tid == 0 && training && nbt) {
+    if (!bp.on) *nbt += 1;
+    else if (bp.c.rank == 0) {
+      const long long nb = *nbt + 1;
+      for (int p = 0; p < bp.c.world; ++p) *reinterpret_cast<long long*>(bp.c.peer[p] + bp.off + 2 * HF * sizeof(float)) = nb;
+    }
+  }
   __syncthreads();
-  head_mark(1);
   // ---- 2. normalise + affine + ReLU + dropout ----
   const float rstd = S.stat[1][fl];
   const bool drop = training && p2 > 0.f;
@@ -443,7 +598,6 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     S.h3[r][fl] = h;
   }
   __syncthreads();
-  head_mark(2);
   // ---- 3a. partial logits over this CTA's 16 features: thread (row r, q) computes classes q, q + 4, q + 8 ----
   {
     const int r = tid >> 2, q = tid & 3;
@@ -458,9 +612,7 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     S.part[r][q] = a0; S.part[r][q + 4] = a1;
     if (q < 2) S.part[r][q + 8] = a2;
   }
-  head_mark(3);
   cluster.sync();
-  head_mark(4);
   // ---- 3b. every CTA adds up the 8 partial-logit tables with coalesced 16-byte DSMEM loads (one table = 5 KB
   // contiguous), then 4 threads per row finish log-softmax + nll + dlogits from shared memory ----
   if (tid < HMAXN * HC / 4) {
@@ -504,7 +656,6 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     }
   }
   __syncthreads();
-  head_mark(5);
   if (rank == 0 && tid == 0) *loss_out = S.loss;
   // ---- 4. fc2 gradients (this CTA's 16 columns of dw2; db2 on CTA 0) ----
   float gw[HC];
@@ -548,7 +699,6 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     const float t = warp_sum(S.dlog[lane][j] + S.dlog[lane + 32][j] + S.dlog[lane + 64][j] + S.dlog[lane + 96][j]);
     if (lane == 0) db2[j] = t;
   }
-  head_mark(6);
   __syncthreads();                       // S.red is reused
   head_colsum(S, sb, 0, fl, warp);
   head_colsum(S, sg, 1, fl, warp);
@@ -572,9 +722,7 @@ k_convnet_head(const float* __restrict__ h1, const long long* __restrict__ targe
     __syncthreads();
     if (tid < HFL) { float t = 0.f; for (int w = 0; w < HRG / 2; ++w) t += S.red[w][tid][2]; dbias1[f0 + tid] = t; }
   }
-  head_mark(7);
   cluster.sync();                        // nobody leaves while a peer may still read its partial logits
-  head_mark(8);
 }
 }  // namespace
 
@@ -587,16 +735,35 @@ int dcp_convnet_head(const float* h1, const void* target, const float* gamma, co
                      float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed,
                      unsigned long long stream_id, const void* step, int training, cudaStream_t s) {
   if (N < 1 || N > HMAXN) { dcp_set_error("convnet head: batch %d not in [1, %d]", N, HMAXN); return -1; }
-  {
-    static bool dbg_set = false;
-    if (!dbg_set) {
-      dbg_set = true;
-      if (const char* e = getenv("DCP_HEAD_DBG_PTR")) { unsigned long long* ptr = (unsigned long long*)strtoull(e, nullptr, 0); DCP_CUDA_CHECK(cudaMemcpyToSymbol(g_head_dbg, &ptr, sizeof ptr)); }
-    }
-  }
+  HeadBnPush bp{};
   DCP_CUDA_CHECK(dcp_launch_pdl(k_convnet_head, dim3(HCL), dim3(HT), 0, s, h1, (const long long*)target, gamma, beta, run_mean, run_var,
                                 (long long*)nbt, w2, b2, loss, logits_out, dh1, dgamma, dbeta, dw2, db2, dbias1, N, eps, momentum, p2, seed,
-                                stream_id, (const long long*)step, training));
+                                stream_id, (const long long*)step, training, bp));
+  return 0;
+}
+// The same kernel inside a data-parallel job: `bn_block` is a 1032-byte block of symmetric heap `h` laid out
+// [running_mean 128 f32][running_var 128 f32][num_batches_tracked i64], allocated at the same offset on every rank.  Rank 0
+// computes the new running statistics from its batch and writes them into EVERY rank's block (peer stores over NVLink from
+// inside the kernel); the other ranks do not touch theirs.  That is what DistributedDataParallel's per-forward buffer
+// broadcast from rank 0 amounts to - without a collective launch, a side stream or a join in front of the head.
+// A rank may read the block after any later cross-rank synchronisation of the step (the gradient exchange is one).
+int dcp_convnet_head_dp(void* h, const float* h1, const void* target, const float* gamma, const float* beta, void* bn_block,
+                        const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2,
+                        float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed,
+                        unsigned long long stream_id, const void* step, int training, cudaStream_t s) {
+  if (N < 1 || N > HMAXN) { dcp_set_error("convnet head: batch %d not in [1, %d]", N, HMAXN); return -1; }
+  const DcpDevCtx& c = *dcp_symm_ctx(h);
+  char* base = c.peer[c.rank];
+  char* blk = static_cast<char*>(bn_block);
+  if (blk < base || blk + 2 * HF * 4 + 8 > base + dcp_symm_bytes(h) || ((blk - base) & 15)) {
+    dcp_set_error("convnet head (data-parallel): bn_block must be a 16-byte aligned region of the symmetric heap"); return -1;
+  }
+  HeadBnPush bp{};
+  bp.on = c.world > 1; bp.off = (size_t)(blk - base); bp.c = c;
+  float* rm = reinterpret_cast<float*>(blk);
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_convnet_head, dim3(HCL), dim3(HT), 0, s, h1, (const long long*)target, gamma, beta, rm, rm + HF,
+                                reinterpret_cast<long long*>(blk + 2 * HF * 4), w2, b2, loss, logits_out, dh1, dgamma, dbeta, dw2, db2, dbias1, N,
+                                eps, momentum, p2, seed, stream_id, (const long long*)step, training, bp));
   return 0;
 }
 }  // extern "C"

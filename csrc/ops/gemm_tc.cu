@@ -32,7 +32,7 @@ struct TcGemmParams {
   // epilogue
   void* out; long ldc; const void* bias; int relu, atomic, out_bf16, bias_bf16;
   long partial_stride;      // > 0: split z writes its partial tile to out + z * partial_stride with plain stores (reduced by dcp_splitk_reduce)
-  long long* dbg;           // optional clock64 trace of CTA (0,0,0) (env DCP_GEMM_DBG_PTR, see scratch/dbg_gemm_trace.py)
+  long long* dbg;           // optional clock64 trace of CTA (0,0,0) (-DDCP_TRACE builds only)
 };
 
 namespace {
@@ -62,7 +62,11 @@ k_tc_gemm(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUt
   const int nstages = p.stages;
   Pipe* pipe = reinterpret_cast<Pipe*>(smem + nstages * stage_bytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
+#ifdef DCP_TRACE      // clock64 trace of CTA (0,0,0) (build with DCP_NVCC_EXTRA=-DDCP_TRACE); compiled out of the production library
   long long* dbg = (p.dbg && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0) ? p.dbg : nullptr;
+#else
+  constexpr long long* dbg = nullptr;
+#endif
   if (dbg && threadIdx.x == 0) dbg[0] = clock64();
   constexpr int kElem = kTF32 ? 4 : 2;
   constexpr int kBK = 128 / kElem;             // elements per K slab
@@ -394,7 +398,11 @@ template <bool kTF32, int kTmemCols> int launch(const CUtensorMap& ma, const CUt
     attr_set = true;
   }
   TcGemmParams q = p;
+#ifdef DCP_TRACE
   { const char* e = getenv("DCP_GEMM_DBG_PTR"); q.dbg = e ? (long long*)strtoull(e, nullptr, 0) : nullptr; }
+#else
+  q.dbg = nullptr;
+#endif
   q.stages = kStages;
   while (q.stages > 2 && smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) --q.stages;
   if (smem_bytes(q.stages, q.a_bytes, q.b_bytes, q.x3) > (size_t)kMaxSmem) { dcp_set_error("tc kernel: stage of %d bytes does not fit shared memory", q.a_bytes + q.b_bytes); return -1; }

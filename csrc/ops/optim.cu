@@ -7,7 +7,6 @@
 // strides over its elements.  Gradients may be f32 or bf16 (bucket dtype); params/state are f32.
 #include "ops/optim_math.cuh"
 
-struct DcpOptEntry { float* p; const void* g; float* s1; float* s2; long long n; };
 
 namespace {
 constexpr int kT = 256;

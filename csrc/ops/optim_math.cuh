@@ -4,6 +4,9 @@
 #pragma once
 #include "ops/ops_common.cuh"
 
+// One row of the device-resident pointer table the multi-tensor optimizer kernels walk (ops/cuda.py packs it as "QQQQq").
+struct DcpOptEntry { float* p; const void* g; float* s1; float* s2; long long n; };
+
 // hp layout: [0] lr [1..5] kind-specific [6] step (float, advanced on device) [7] grad_scale
 template <int KIND, typename G>
 __device__ __forceinline__ void opt_update(float& p, float g, float& s1, float& s2, const float* hp, float step) {

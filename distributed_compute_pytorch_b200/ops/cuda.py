@@ -69,6 +69,11 @@ def lib():
             "dcp_convnet_conv1_wgrad": [vp, vp, vp, vp, i, vp],
             "dcp_convnet_conv1_wgrad_allreduce": [vp, vp, vp, vp, vp, i, vp, i, i, vp],
             "dcp_convnet_head": [vp] * 17 + [i, f, f, f, ull, ull, vp, i, vp],
+            "dcp_convnet_head_dp": [vp] * 16 + [i, f, f, f, ull, ull, vp, i, vp],
+            "dcp_convnet_conv1_wgrad_push": [vp, vp, vp, i, vp, C.c_uint, C.c_uint, i, i, vp, vp, vp],
+            "dcp_convnet_conv1_wgrad_ll": [vp, vp, vp, i, vp, vp, vp, i, vp, vp, vp],
+            "dcp_splitk_reduce_push": [vp, vp, i, l, vp, C.c_uint, C.c_uint, i, i, vp, vp, i, vp],
+            "dcp_dp_tail": [vp, vp, i, C.c_longlong, vp, i, vp, vp, C.c_uint, i, vp, i, vp, vp, i, vp],
         }
         for name, args in sigs.items():
             fn = getattr(_lib, name)
@@ -633,7 +638,10 @@ def fused_optimizer_step(opt, gi: int, group: dict, items: List[Tuple[torch.Tens
     ent = cache.get(gi)
     dev = items[0][0].device
     gdt = items[0][1].dtype
-    key = tuple((p.data_ptr(), g.data_ptr()) for p, g, _ in items)
+    # the table bakes in parameter, gradient AND state pointers: load_state_dict() replaces the state tensors, so they are part of the key
+    def _key():
+        return tuple((p.data_ptr(), p.grad.data_ptr()) + tuple(t.data_ptr() for t in opt._state_tensors(st)) for p, _, st in items)
+    key = _key()
     if ent is None or ent["key"] != key:
         rows = []
         for p, g, st in items:
@@ -652,15 +660,15 @@ def fused_optimizer_step(opt, gi: int, group: dict, items: List[Tuple[torch.Tens
             s1 = sts[0].data_ptr() if len(sts) > 0 else 0
             s2 = sts[1].data_ptr() if len(sts) > 1 else 0
             rows.append(struct.pack("QQQQq", p.data_ptr(), g.data_ptr(), s1, s2, p.numel()))
-        key = tuple((p.data_ptr(), p.grad.data_ptr()) for p, _, _ in items)
+        key = _key()
         # pinned staging + async copy: legal inside CUDA-graph capture (becomes a memcpy node)
         host = torch.frombuffer(bytearray(b"".join(rows)), dtype=torch.uint8).pin_memory()
         table = torch.empty(host.numel(), dtype=torch.uint8, device=dev)
         table.copy_(host, non_blocking=True)
         first_step = items[0][2].get("step", 1)
         hp = ent["hp"] if ent is not None else torch.zeros(8, dtype=torch.float32, device=dev)
-        if ent is None:
-            hp[6] = float(int(first_step) - 1)
+        # (re)seed the device step counter from the optimizer state: first build, or a rebuild after load_state_dict()
+        hp[6] = float(int(first_step) - 1)
         ent = {"key": key, "table": table, "host": host, "hp": hp, "hyper": ent["hyper"] if ent else None, "n": len(items),
                "max": max(p.numel() for p, _, _ in items)}
         cache[gi] = ent

@@ -28,7 +28,7 @@ from ..ops import cuda as K
 from ..ops import tc
 from ..types import ReduceOp
 from .ddp import DistributedDataParallel
-from .p2p_backend import CH_DDP
+from .p2p_backend import CH_DDP, CH_TAIL
 
 READY_ORDER = ["fc2.bias", "fc2.weight", "batchnorm.weight", "batchnorm.bias", "fc1.bias", "fc1.weight",
                "conv2.weight", "conv2.bias", "conv1.weight", "conv1.bias"]
@@ -76,7 +76,7 @@ class FusedConvNetTrainer:
         self.bn_flat = None
         bn = net.batchnorm
         if self.be is not None and self.ddp is not None and self.ddp.broadcast_buffers and bn.track_running_stats:
-            flat = torch.zeros(258, **f32)
+            flat = self.be.empty_symmetric(258, torch.float32)    # symmetric: rank 0's head kernel writes every rank's copy
             flat[:128].copy_(bn.running_mean); flat[128:256].copy_(bn.running_var)
             nbt = flat[256:258].view(torch.int64)
             nbt.copy_(bn.num_batches_tracked.reshape(1))
@@ -115,6 +115,35 @@ class FusedConvNetTrainer:
         self.fuse_tail = self.be is not None and os.environ.get("DCP_FUSE_TAIL", "1") == "1"
         self.c1_payload = self.be.empty_symmetric(2 * self.world * 320, torch.float32) if self.fuse_tail else None
         self.side = self.be.comm_stream if self.be is not None else torch.cuda.Stream(device=dev)
+        # measurement switches (bench/step_ablation.py): drop one piece of the data-parallel machinery to see what it costs
+        # on the critical path.  The step is numerically WRONG with any of them set.
+        self.ablate = {a for a in os.environ.get("DCP_ABLATE", "").split(",") if a}
+        self.comm_ctas = int(os.environ.get("DCP_COMM_CTAS", self.comm_ctas))
+        # fused data-parallel tail (csrc/ops/dp_push.cuh): the producers of the last bucket's gradients (conv2 split-K reduce,
+        # conv1 weight-gradient) push their sums into every rank's payload block and signal; ONE kernel at the end of the step
+        # waits, averages and applies the optimizer update.  No all-reduce launch, no side stream, no join for that bucket.
+        self.dp_tail = (self.be is not None and self.ddp is not None and len(self.buckets) == 2 and self.flat_wgrad
+                        and os.environ.get("DCP_DP_TAIL", "1") == "1")
+        if self.dp_tail:
+            g = {n: q.grad for n, q in names.items()}
+            self.dp_tail = self._bucket1_split(g) > 0 and g["conv1.bias"].data_ptr() == g["conv1.weight"].data_ptr() + 4 * 288
+        if self.dp_tail:
+            self.dp_slot = self.buckets[1].numel()
+            self.dp_pay = self.be.empty_symmetric(2 * self.world * self.dp_slot, torch.float32)
+            self.dp_pay.zero_()
+            self.dp_ws = torch.zeros(16 + 148 * 320, **f32)
+            self.c1_ll = self.be.empty_symmetric(2 * self.world * 320 * 2, torch.float32)     # {value, step} words of conv1's exchange
+            self.c1_ll.zero_()
+            self.dp_blks = (C.c_int * 2)(0, 1)
+            self.side2 = torch.cuda.Stream(device=dev, priority=-1)
+            # every rank must see the same step number inside a step: the epoch of the exchange is the device step counter
+            chk = torch.stack([K.graph_step.double(), -K.graph_step.double()])
+            dist.all_reduce(chk, op=ReduceOp.MAX)
+            if chk[0].item() != -chk[1].item():
+                raise RuntimeError("FusedConvNetTrainer: the ranks disagree on the device step counter (they must have run the same "
+                                   "number of fused steps before this trainer was built)")
+        if self.be is not None:
+            dist.barrier()          # payload / buffer blocks are zeroed everywhere before any rank pushes into them
         self.launches_per_step = 0
         self.graph = None
         self._copy_stream = None
@@ -131,10 +160,17 @@ class FusedConvNetTrainer:
         step_ptr = K.graph_step.data_ptr()
         tr = int(self.training)
         ck(L.dcp_counter_advance(step_ptr, s()))
+        ab = self.ablate
+        self._conv2_tail = None
+        main = torch.cuda.current_stream(self.dev)
+        rows = self._opt_rows() if self.split_opt else None
+        dp_tail = self.dp_tail and rows is not None and "b1" not in ab
+        bn = net.batchnorm
+        bn_push = self.bn_flat is not None and tr and N <= 128 and self.fused_head and "bn" not in ab and "oldbn" not in ab
         ev_buf = None
-        if self.bn_flat is not None and tr:
+        if self.bn_flat is not None and tr and not bn_push and "bn" not in ab:
             # DDP forward semantics: rank 0's buffers win.  Runs on the side stream under conv1 / conv2.
-            self.side.wait_stream(torch.cuda.current_stream(self.dev))
+            self.side.wait_stream(main)
             self.be.broadcast(self.bn_flat, 0, stream=self.side, chan=CH_DDP)
             ev_buf = torch.cuda.Event(); ev_buf.record(self.side)
         # ---- forward
@@ -142,73 +178,173 @@ class FusedConvNetTrainer:
         ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
                               self.off_fwd, 26, 676, 24, 24, 0, 148, s()))
         ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
+        # the data-gradient's copy of conv2's filter (taps flipped, channels swapped) is taken here, while the filter is hot in L2:
+        # conv2.weight may then be updated by the optimizer while the data-gradient is still running
+        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         tc.linear_fwd(self.pooled, p["fc1.weight"], p["fc1.bias"], self.h1, False)
-        bn = net.batchnorm
         if ev_buf is not None:
-            torch.cuda.current_stream(self.dev).wait_event(ev_buf)
+            main.wait_event(ev_buf)
         if N <= 128 and self.fused_head:
             # BatchNorm + ReLU + dropout + fc2 + log_softmax/nll and ALL of their gradients (+ fc1's bias gradient): one 8-CTA cluster
-            ck(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
-                                  bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
-                                  self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
-                                  g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), g["fc1.bias"].data_ptr(),
-                                  N, bn.eps, bn.momentum, net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, tr, s()))
+            head_tail = [p["fc2.weight"].data_ptr(), p["fc2.bias"].data_ptr(),
+                         self.loss.data_ptr(), self.logits.data_ptr(), self.dh1.data_ptr(), g["batchnorm.weight"].data_ptr(),
+                         g["batchnorm.bias"].data_ptr(), g["fc2.weight"].data_ptr(), g["fc2.bias"].data_ptr(), g["fc1.bias"].data_ptr(),
+                         N, bn.eps, bn.momentum, net.dropout2.p if tr else 0.0, self.seed, 2, step_ptr, tr, s()]
+            if bn_push:
+                # data-parallel buffer sync inside the kernel: rank 0 writes its new running statistics into every rank's block
+                ck(L.dcp_convnet_head_dp(self.be.handle, self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(),
+                                         self.bn_flat.data_ptr(), *head_tail))
+            else:
+                ck(L.dcp_convnet_head(self.h1.data_ptr(), self.y.data_ptr(), bn.weight.data_ptr(), bn.bias.data_ptr(), bn.running_mean.data_ptr(),
+                                      bn.running_var.data_ptr(), bn.num_batches_tracked.data_ptr(), *head_tail))
         else:
             self._head_unfused(L, ck, s, p, g, bn, N, tr, step_ptr)
             ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
         tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
-        ev0 = self._reduce_bucket(0)
+        ar_late = "ar_late" in ab
+        ev0 = self._reduce_bucket(0) if ("b0" not in ab and not ar_late) else None
         tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+        if ar_late and "b0" not in ab:
+            ev0 = self._reduce_bucket(0)
         # fc1.weight has been read for the last time: the optimizer update of everything in bucket 0 (97 % of the
         # parameters) runs on the side stream, behind that bucket's all-reduce, underneath the convolution backward
-        rows = self._opt_rows() if self.split_opt else None
         ev_opt0 = None
         if rows is not None:
             ent, (r0, n0, m0), _ = rows
             K._push_hyper(self.opt, self.opt.param_groups[0], ent)
             ck(L.dcp_optim_advance(ent["hp"].data_ptr(), s()))
-            main = torch.cuda.current_stream(self.dev)
-            self.side.wait_stream(main)
-            ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, self.side.cuda_stream))
-            ev_opt0 = torch.cuda.Event(); ev_opt0.record(self.side)
+            opt_stream = main if "opt0main" in ab else self.side
+            if "opt0end" in ab and dp_tail:
+                opt_stream = None        # measurement: bucket 0's update at the very end of the main stream, between the last push and the wait
+            elif opt_stream is self.side:
+                self.side.wait_stream(main)
+            elif ev0 is not None:
+                main.wait_event(ev0); ev0 = None
+            if opt_stream is not None:
+                ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, opt_stream.cuda_stream))
+            if opt_stream is self.side:
+                ev_opt0 = torch.cuda.Event(); ev_opt0.record(self.side)
         # ---- backward: convolutional trunk
         ck(L.dcp_convnet_pool_bwd(self.dpooled.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), self.dy2.data_ptr(), N, net.dropout1.p,
                                   self.seed, 1, step_ptr, tr, s()))
-        split1, ev1a = 0, None
+        split1, ev1a, ev1 = 0, None, None
         if self.flat_wgrad:
             ck(L.dcp_conv_wgrad_flat_tc(self.a1.data_ptr(), self.dy2.data_ptr(), self.wg_scratch.data_ptr(), N * 676, 64, 26, self.wg_parts, s()))
-            ck(tc._lib.dcp_splitk_reduce2(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), g["conv2.bias"].data_ptr(), 64 * 288,
-                                          self.wg_parts, 64 * 289, s()))
-            # conv2's gradients (98 % of bucket 1) are final here: reduce that part of the bucket now, under the data-gradient
-            # and conv1's weight-gradient; only conv1's 320 values are left for the tail of the step
-            split1 = self._bucket1_split(g)
-            if split1:
-                ev1a = self.be.all_reduce_async(self.buckets[1][:split1], ReduceOp.AVG, max_ctas=self.comm_ctas)
+            if dp_tail:
+                # conv2's gradients leave for every rank's payload block straight from the split-K reduction, on a second side
+                # stream: the peer stores and their system-scope fences (~10 us) stay off the critical path, and nobody waits -
+                # the tail kernel finds them through the signal words, this rank's own included
+                ev_push = None
+                ll_ok = self._ll_rows(rows[2][0], rows[2][1]) is not None and "no_ll" not in ab and "opt0end" not in ab
+                pull = 0 if ("push" in ab or not ll_ok) else 1     # pull: conv2's sums stay local, the consumer reads the peers' copies
+                if "push_main" in ab or (pull and "pull_main" in ab):
+                    ps = main
+                else:
+                    ps = self.side2
+                    ps.wait_stream(main)
+                ck(L.dcp_splitk_reduce_push(self.be.handle, self.wg_scratch.data_ptr(), self.wg_parts, 64 * 289, self.dp_pay.data_ptr(), self.dp_slot, 0,
+                                            CH_TAIL, 0, step_ptr, self.dp_ws.data_ptr(), pull, ps.cuda_stream))
+                ll = self._ll_rows(rows[2][0], rows[2][1]) if ll_ok else None
+                self._conv2_tail = None
+                if ll is not None and pull and ps is main and "tail_early" not in ab:
+                    self._conv2_tail = ll           # issued after the data-gradient (below): by then the peers' signals have long arrived
+                elif ll is not None:
+                    # ... followed, on the same stream, by the kernel that waits for every rank's conv2 sums, averages them and applies
+                    # the optimizer update of conv2's parameters - all of it underneath the data-gradient (which reads its own copy
+                    # of the filter, taken in the forward pass)
+                    ent = rows[0]
+                    ck(L.dcp_dp_tail(self.be.handle, ent["table"].data_ptr() + 40 * ll[1], 2, 64 * 288, ent["hp"].data_ptr(), self.opt._kind,
+                                     self.buckets[1].data_ptr(), self.dp_pay.data_ptr(), self.dp_slot, CH_TAIL, self.dp_blks, 1,
+                                     (C.c_int * 2)(0, 0), step_ptr, pull, ps.cuda_stream))
+                if ps is not main:
+                    ev_push = torch.cuda.Event(); ev_push.record(ps)
+            else:
+                ck(tc._lib.dcp_splitk_reduce2(self.wg_scratch.data_ptr(), g["conv2.weight"].data_ptr(), g["conv2.bias"].data_ptr(), 64 * 288,
+                                              self.wg_parts, 64 * 289, s()))
+                # conv2's gradients (98 % of bucket 1) are final here: reduce that part of the bucket now, under the data-gradient
+                # and conv1's weight-gradient; only conv1's 320 values are left for the tail of the step
+                split1 = self._bucket1_split(g) if "b1" not in ab else 0
+                if split1:
+                    ev1a = self.be.all_reduce_async(self.buckets[1][:split1], ReduceOp.AVG, max_ctas=self.comm_ctas)
         else:
             tc.conv_wgrad_launch(self.dy2, self.a1, g["conv2.weight"], N, 26, 26, 32, 64, 3, 3, 0, 26, 26, 8, 4, 1, 148)
             ck(L.dcp_colsum(self.dy2.data_ptr(), g["conv2.bias"].data_ptr(), N * 676, 64, 0, s()))
-        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         ck(L.dcp_conv_flat_tc(self.dy2.data_ptr(), self.wt2.data_ptr(), self.dz1.data_ptr(), None, self.a1.data_ptr(), N * 676, 64, 32, 9,
                               self.off_bwd, 26, 676, 26, 26, 1, 148, s()))
+        if dp_tail and getattr(self, "_conv2_tail", None) is not None:
+            # conv2: wait for every rank's signal (sent a data-gradient ago), read the W copies of the sums - the peers' over NVLink -,
+            # average, write the gradients and apply the optimizer update
+            ent = rows[0]
+            ck(L.dcp_dp_tail(self.be.handle, ent["table"].data_ptr() + 40 * self._conv2_tail[1], 2, 64 * 288, ent["hp"].data_ptr(), self.opt._kind,
+                             self.buckets[1].data_ptr(), self.dp_pay.data_ptr(), self.dp_slot, CH_TAIL, self.dp_blks, 1,
+                             (C.c_int * 2)(0, 0), step_ptr, 1, s()))
+        if dp_tail:
+            ent, _, (r1, n1, m1) = rows
+            if self._ll_rows(r1, n1) is not None and "no_ll" not in ab and "opt0end" not in ab:
+                # conv1: weight-gradient, low-latency exchange ({value, step} words, no fence / signal / kernel boundary), average and
+                # optimizer update in ONE kernel - the last of the step; conv2's rows were updated on the second side stream
+                ck(L.dcp_convnet_conv1_wgrad_ll(self.be.handle, self.dz1.data_ptr(), self.x.data_ptr(), N, self.c1_ll.data_ptr(),
+                                                ent["table"].data_ptr() + 40 * self._ll_rows(r1, n1)[0], ent["hp"].data_ptr(), self.opt._kind,
+                                                step_ptr, self.dp_ws.data_ptr() + 16, s()))
+            else:
+                ck(L.dcp_convnet_conv1_wgrad_push(self.be.handle, self.dz1.data_ptr(), self.x.data_ptr(), N, self.dp_pay.data_ptr(), self.dp_slot,
+                                                  64 * 289, CH_TAIL, 1, step_ptr, self.dp_ws.data_ptr() + 16, s()))
+                if "opt0end" in ab:
+                    if ev0 is not None:
+                        main.wait_event(ev0); ev0 = None
+                    _, (r0, n0, m0), _ = rows
+                    ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, s()))
+                # the one kernel that waits: all producers of all ranks -> average -> gradients + optimizer update of bucket 1
+                ck(L.dcp_dp_tail(self.be.handle, ent["table"].data_ptr() + 40 * r1, n1, m1, ent["hp"].data_ptr(), self.opt._kind,
+                                 self.buckets[1].data_ptr(), self.dp_pay.data_ptr(), self.dp_slot, CH_TAIL, self.dp_blks, 2,
+                                 self._row_sig(r1, n1), step_ptr, 0, s()))
+            for ev in (ev0, ev_opt0, ev_push):   # joins AFTER the last kernel: the side streams only have to finish with the step
+                if ev is not None:
+                    main.wait_event(ev)
+            return
         if split1 and self.fuse_tail:
             ck(L.dcp_convnet_conv1_wgrad_allreduce(self.be.handle, self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(),
                                                    g["conv1.bias"].data_ptr(), N, self.c1_payload.data_ptr(), CH_DDP, 511, s()))
-            ev1 = None
         else:
             ck(L.dcp_convnet_conv1_wgrad(self.dz1.data_ptr(), self.x.data_ptr(), g["conv1.weight"].data_ptr(), g["conv1.bias"].data_ptr(), N, s()))
             if split1:
                 ev1 = self.be.all_reduce_async(self.buckets[1][split1:], ReduceOp.AVG, max_ctas=self.comm_ctas)
-            else:
+            elif "b1" not in ab:
                 ev1 = self._reduce_bucket(1)
-        for ev in (ev0, ev1a, ev1, ev_opt0):
-            if ev is not None:
-                torch.cuda.current_stream(self.dev).wait_event(ev)
         if rows is not None:
+            for ev in (ev1a, ev1):
+                if ev is not None:
+                    main.wait_event(ev)
             ent, _, (r1, n1, m1) = rows
             ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r1, n1, m1, ent["hp"].data_ptr(), self.opt._kind, 0, s()))
+            for ev in (ev0, ev_opt0):
+                if ev is not None:
+                    main.wait_event(ev)
         else:
+            for ev in (ev0, ev1a, ev1, ev_opt0):
+                if ev is not None:
+                    main.wait_event(ev)
             self.opt.step()
 
+    def _ll_rows(self, r1: int, n1: int):
+        """(row of conv1.weight, row of conv2.weight) in the optimizer table when (conv1.weight, conv1.bias) and (conv2.weight,
+        conv2.bias) are adjacent pairs there, else None."""
+        params = [q for q in self.opt.param_groups[0]["params"] if q.grad is not None]
+        ids = [id(params[r1 + i]) for i in range(n1)]
+        net = self.net
+        try:
+            a, b = ids.index(id(net.conv1.weight)), ids.index(id(net.conv2.weight))
+        except ValueError:
+            return None
+        if a + 1 >= n1 or b + 1 >= n1 or ids[a + 1] != id(net.conv1.bias) or ids[b + 1] != id(net.conv2.bias):
+            return None
+        return r1 + a, r1 + b
+
+    def _row_sig(self, r1: int, n1: int):
+        """For rows r1 .. r1 + n1 of the optimizer table: 0 = gradient comes from the conv2 split-K reduce, 1 = from conv1's weight-gradient."""
+        params = [q for q in self.opt.param_groups[0]["params"] if q.grad is not None]
+        c1 = {id(self.net.conv1.weight), id(self.net.conv1.bias)}
+        return (C.c_int * n1)(*[1 if id(params[r1 + i]) in c1 else 0 for i in range(n1)])
 
     def _bucket1_split(self, g) -> int:
         """Number of leading elements of bucket 1 that hold conv2's gradients (0: not splittable / no communication)."""

@@ -28,7 +28,7 @@ from ..types import ReduceOp, Work
 _DTYPE = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2, torch.int32: 3, torch.int64: 4, torch.float64: 5,
           torch.uint8: 6, torch.bool: 6, torch.int8: 6}
 
-CH_USER, CH_DDP, CH_BN, CH_OPT = 0, 1, 2, 3  # signal-pad channels (independent epoch streams)
+CH_USER, CH_DDP, CH_BN, CH_OPT, CH_TAIL = 0, 1, 2, 3, 4  # signal-pad channels (independent epoch streams)
 
 
 class _CudaBuf:
