@@ -452,9 +452,14 @@ int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, con
 //     (stream-ordered memset on the caller's stream) before the statistics kernel adds into them.
 //   * Two calls that can overlap on the GPU (different streams, or different host threads on different streams)
 //     race on the array and corrupt each other's statistics.  Issue them on one stream, or order them with events.
+//     Host threads that share ONE stream are safe: the clear and the two launches of a call are enqueued under a lock,
+//     so another thread's call cannot slip in between them.
 //   * The first call on each device looks up the array's device address (cudaGetSymbolAddress with that device
 //     current) and caches it; make that first call before starting any stream capture on that device.
-//   * The call itself performs no cudaMalloc / cudaFree and no allocating library call.
+//   * The call itself performs no cudaMalloc / cudaFree and no allocating library call.  With CUDA's default lazy module
+//     loading the FIRST call on a device is also when the runtime places this library's device image - the array included -
+//     on that GPU; a process that is about to give the whole GPU to its own arena makes one call per device before that
+//     (or sets CUDA_MODULE_LOADING=EAGER).
 // =====================================================================================================
 #include <mutex>
 
@@ -467,6 +472,7 @@ static __device__ __align__(256) double g_bn_noalloc_scratch[2 * DCP_BN_NOALLOC_
 namespace {
 double* g_bn_noalloc_ptr[DCP_BN_NOALLOC_MAX_DEVICES] = {};
 std::mutex g_bn_noalloc_mu;
+std::mutex g_bn_noalloc_issue_mu;     // held while one call enqueues its clear + two kernels
 
 // Device address of the scratch array on the current device (resolved once per device).
 int bn_noalloc_scratch(double** out) {
@@ -503,6 +509,7 @@ int dcp_bn_forward_noalloc(const void* x, void* y, const float* gamma, const flo
   }
   double* scratch = nullptr;
   if (bn_noalloc_scratch(&scratch) != 0) return -1;
+  std::lock_guard<std::mutex> issue(g_bn_noalloc_issue_mu);
   // the array still holds the previous call's sums: clear the part this call accumulates into
   DCP_CUDA_CHECK(cudaMemsetAsync(scratch, 0, sizeof(double) * 2 * (size_t)C, s));
   dim3 grid; long rpc; stats_grid(M, C, &grid, &rpc);

@@ -245,14 +245,16 @@ void dcp_symm_destroy(void* h);
 
 /* ---- hand-maintained additions ---- */
 
-/* Allocation-free BatchNorm forward.  This entry point has no counterpart in the reference (which never touches
- * device memory management; ref:main.py only calls nn.BatchNorm1d): it exists for hosts of THIS library that cannot
- * provide scratch memory - a C/C++ program linking libdcp_cuda.so without PyTorch's caching allocator, or a process
- * whose own arena already owns the whole GPU so that cudaMalloc would fail (and would stall the device anyway).
+/* Allocation-free BatchNorm forward.  This entry point has no counterpart in the reference.  It exists for hosts of THIS
+ * library that cannot provide scratch memory - a C/C++ program linking libdcp_cuda.so without PyTorch's caching allocator,
+ * or a process whose own arena already owns the whole GPU so that cudaMalloc would fail (and would stall the device anyway).
  * The per-channel accumulators live in a 32 KiB __device__ array inside the library (one copy per GPU, kept until
  * exit), so: C <= DCP_BN_NOALLOC_MAX_C (2048) or the call is refused; the array is shared by every call and
- * cleared at the start of each, hence calls that may overlap on the GPU race - keep them on one stream; the first
- * call on a device resolves the array's address (cudaGetSymbolAddress) and should come before any stream capture.
+ * cleared at the start of each, hence calls that may overlap on the GPU race - keep them on one stream (the library
+ * serialises the host side of concurrent callers, not the device side); the first call on a device resolves the array's
+ * address (cudaGetSymbolAddress) and should come before any stream capture.  That first call is also the moment the CUDA
+ * runtime loads the library's device image - array included - onto that GPU: a process that hands the whole GPU to its own
+ * arena must make one call per device BEFORE it does so (or run with CUDA_MODULE_LOADING=EAGER).
  * Same results as dcp_bn_stats + dcp_bn_apply(training=1). */
 #define DCP_BN_NOALLOC_MAX_C 2048
 int dcp_bn_forward_noalloc(const void* x, void* y, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt,
