@@ -31,7 +31,9 @@ def parse():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=50)
-    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference", "reference-graphed"],
+                    help="reference-graphed is a DIAGNOSTIC arm (not the headline comparison): the reference's ConvNet and the body of its "
+                         "train() loop captured with torch.cuda.graphs, to separate kernel quality from eager launch overhead")
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch (the reference's --batch_size default, ref:main.py:139)")
     ap.add_argument("--lr", type=float, default=0.001)
     ap.add_argument("--no-graph", action="store_true", help="ours: eager DDP path instead of the CUDA-graph step")
@@ -266,10 +268,99 @@ def run_reference(opt, rank, local_rank, world):
     tdist.destroy_process_group()
 
 
+def run_reference_graphed(opt, rank, local_rank, world):
+    """Diagnostic: the reference model + the body of its training loop (ref:main.py:58-63) replayed as ONE CUDA graph on the stock
+    PyTorch stack (cuDNN / cuBLAS / ATen, torch.optim.Adadelta capturable, torch DDP + NCCL when world > 1).  The reference itself
+    runs eagerly; this arm only answers "how much of the gap is launch overhead"."""
+    ref, why = load_reference()
+    if ref is None:
+        if rank == 0:
+            print(json.dumps({"impl": "reference-graphed", "unavailable": why}), flush=True)
+        return
+    import torch.distributed as tdist
+    import torch.nn.functional as F
+    from torch import optim
+    from distributed_compute_pytorch_b200.utils import ClockSampler
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29535")
+    tdist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    torch.manual_seed(0)
+    model = ref.ConvNet().to(local_rank)
+    if world > 1:
+        model = ref.DistributedDataParallel(model, device_ids=[local_rank])
+    optimizer = optim.Adadelta(model.parameters(), lr=opt.lr, capturable=True)
+    xs, ys = make_pool(opt.batch, dev, pinned=False, seed=100 + rank)
+    sx, sy = xs[0].clone(), ys[0].clone()
+
+    def body():
+        optimizer.zero_grad(set_to_none=True)
+        loss = F.nll_loss(model(sx), sy)
+        loss.backward()
+        optimizer.step()
+        return loss
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side), warnings_off():
+            for _ in range(12):          # DDP needs >= 11 eager iterations before capture
+                body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph), warnings_off():
+            static_loss = body()
+    except Exception as e:
+        if rank == 0:
+            print(json.dumps({"impl": "reference-graphed", "unavailable": f"capture failed: {type(e).__name__}: {str(e)[:200]}"}), flush=True)
+        tdist.destroy_process_group()
+        return
+
+    def timed(n):
+        start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        tdist.barrier(); torch.cuda.synchronize()
+        start.record()
+        for i in range(n):
+            sx.copy_(xs[i % POOL_BATCHES], non_blocking=True); sy.copy_(ys[i % POOL_BATCHES], non_blocking=True)
+            graph.replay()
+        end.record()
+        tdist.barrier(); torch.cuda.synchronize()
+        return start.elapsed_time(end)
+    timed(opt.warmup)
+    with ClockSampler(local_rank, period_s=0.05) as clocks:
+        ms = timed(opt.steps)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+    ms = t.item()
+    gb = opt.batch * world
+    if rank == 0:
+        print(json.dumps({"metric": "images/sec", "value": gb * opt.steps / (ms / 1e3), "unit": "images/s", "n_gpus": world, "steps": opt.steps,
+                          "warmup": opt.warmup, "ms_per_step": ms / opt.steps, "higher_is_better": True, "scaling": "weak", "impl": "reference-graphed",
+                          "diagnostic": True, "dtype": "fp32 (cuDNN default allow_tf32 for conv)", "data": "synthetic MNIST-shaped, random-init weights",
+                          "config": {"model": "ConvNet (baseline/_ref/main.py) + body of its train() loop in one torch.cuda.graphs capture",
+                                     "global_batch": gb, "per_gpu_batch": opt.batch, "parallelism": f"dp{world}",
+                                     "optimizer": "torch.optim.Adadelta(capturable=True)", "l2": f"rotating pool of {POOL_BATCHES} batches"},
+                          "clocks": clocks.summary(), "last_loss": float(static_loss)}), flush=True)
+    tdist.destroy_process_group()
+
+
+@contextlib.contextmanager
+def warnings_off():
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        yield
+
+
+def _pick(opt):
+    return {"reference": run_reference, "reference-graphed": run_reference_graphed}.get(opt.impl, run_ours)
+
+
 def _entry(rank, world, port, opt):
     os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
     os.environ["RANK"], os.environ["LOCAL_RANK"], os.environ["WORLD_SIZE"] = str(rank), str(rank), str(world)
-    (run_reference if opt.impl == "reference" else run_ours)(opt, rank, rank, world)
+    _pick(opt)(opt, rank, rank, world)
 
 
 def main():
@@ -277,11 +368,11 @@ def main():
     er = env_rank()
     if er is not None:
         rank, local_rank, world = er
-        (run_reference if opt.impl == "reference" else run_ours)(opt, rank, local_rank, world)
+        _pick(opt)(opt, rank, local_rank, world)
         return
     if opt.gpus <= 1:
         os.environ.setdefault("MASTER_PORT", str(29500 + os.getpid() % 400))
-        (run_reference if opt.impl == "reference" else run_ours)(opt, 0, 0, 1)
+        _pick(opt)(opt, 0, 0, 1)
         return
     import socket
     import distributed_compute_pytorch_b200 as dcp
