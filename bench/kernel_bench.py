@@ -44,11 +44,13 @@ def library_rows(N, dev, measure):
         add(f"cuDNN conv1 wgrad + bias grad ({fmt_name})", "conv1_wgrad (SIMT)",
             lambda: cb(dz1, x1, w1, [32], [1, 1], [0, 0], [1, 1], False, [0, 0], 1, [False, True, True]))
         add(f"ATen max_pool2d + dropout2d fwd ({fmt_name})", "pool_fwd+dropout", lambda: F.dropout2d(F.max_pool2d(F.relu(a2), 2), 0.25, True))
-        a2r = a2.clone().requires_grad_(True)
-        pooled = F.dropout2d(F.max_pool2d(F.relu(a2r), 2), 0.25, True)
+        rl = F.relu(a2)
+        pooled, idx = F.max_pool2d(rl, 2, return_indices=True)
+        mask = (torch.rand(N, 64, 1, 1, device=dev) >= 0.25).float() / 0.75
         gp = torch.randn_like(pooled)
-        add(f"ATen relu + max_pool2d + dropout2d bwd ({fmt_name})", "pool_bwd (+relu/dropout bwd)",
-            lambda: torch.autograd.grad(pooled, a2r, gp, retain_graph=True))
+        add(f"ATen dropout2d + max_pool2d + relu bwd ({fmt_name})", "pool_bwd (+relu/dropout bwd)",
+            lambda: torch.ops.aten.threshold_backward(
+                torch.ops.aten.max_pool2d_with_indices_backward(gp * mask, rl, [2, 2], [2, 2], [0, 0], [1, 1], False, idx), rl, 0))
     xf = torch.randn(N, 9216, **f32); wf = torch.randn(128, 9216, **f32); bf = torch.randn(128, **f32); dh = torch.randn(N, 128, **f32)
     for tf32 in (False, True):
         torch.backends.cuda.matmul.allow_tf32 = tf32

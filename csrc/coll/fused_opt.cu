@@ -11,16 +11,32 @@
 //   3. pushes the new parameter values into every peer's parameter buffer (NVLink stores)        (all_gather)
 // so the transfer of one vector overlaps the math of the others and nothing is staged.  One barrier before (all
 // gradients written) and one after (all pushes landed); epochs on the CH_OPT signal channel.  With NVLS the pull
-// becomes multimem.ld_reduce and the push multimem.st.
-#include "coll/coll_common.cuh"
+// becomes multimem.ld_reduce and the push multimem.st.  The gradient copies of a thread's NEXT vector are requested before
+// the current one is processed, so two NVLink round trips per thread overlap the update math and the stores.
+#include "coll/coll_launch.cuh"
 #include "ops/optim_math.cuh"
 
 namespace {
-constexpr int kThreads = 512;
+constexpr int kThreads = kCollThreads;
 
 template <int KIND, typename G, bool kNvls>
-__global__ void __launch_bounds__(kThreads) k_fused_rs_opt_ag(DcpDevCtx c, size_t goff, size_t poff, float* __restrict__ s1, float* __restrict__ s2,
-                                                               size_t n, const float* __restrict__ hp, int chan) {
+struct FusedRsOptAgBody {
+  static constexpr int kThreads = kCollThreads;
+  struct Args { size_t goff; size_t poff; float* s1; float* s2; size_t n; const float* hp; int chan; };
+  // the W copies (or their in-switch sum) of gradient vector v
+  static __device__ __forceinline__ void fetch(const DcpDevCtx& c, size_t goff, size_t v, uint4 (&raw)[DCP_MAX_RANKS]) {
+    if constexpr (kNvls && (std::is_same<G, float>::value || std::is_same<G, __nv_bfloat16>::value)) {
+      raw[0] = multimem_ld_reduce_add<G>(c.mc + goff + v * 16);
+    } else {
+#pragma unroll
+      for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < c.world) raw[p] = ld16_stream(c.peer[p] + goff + v * 16);
+    }
+  }
+  static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
+  const size_t goff = a.goff, poff = a.poff, n = a.n;
+  float* __restrict__ s1 = a.s1; float* __restrict__ s2 = a.s2;
+  const float* __restrict__ hp = a.hp;
+  const int chan = a.chan;
   constexpr int GV = 16 / sizeof(G);           // gradient elements per 16-byte vector
   const int W = c.world;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
@@ -31,16 +47,16 @@ __global__ void __launch_bounds__(kThreads) k_fused_rs_opt_ag(DcpDevCtx c, size_
   const OptHyper H = load_hyper<KIND>(hp);
   const float gs = hp[7], inv_w = 1.f / (float)W;
   dcp_barrier(c, chan);
+  uint4 raw[DCP_MAX_RANKS], nxt[DCP_MAX_RANKS];
+  if (vb + tid < ve) fetch(c, goff, vb + tid, raw);
   for (size_t v = vb + tid; v < ve; v += stride) {
+    if (v + stride < ve) fetch(c, goff, v + stride, nxt);      // next vector's round trip starts now
     float g[GV];
     if constexpr (kNvls && (std::is_same<G, float>::value || std::is_same<G, __nv_bfloat16>::value)) {
-      Vec<G> x; x.u = multimem_ld_reduce_add<G>(c.mc + goff + v * 16);
+      Vec<G> x; x.u = raw[0];
 #pragma unroll
       for (int i = 0; i < GV; ++i) g[i] = ElemTraits<G>::up(x.e[i]) * inv_w;
     } else {
-      uint4 raw[DCP_MAX_RANKS];
-#pragma unroll
-      for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = ld16_stream(c.peer[p] + goff + v * 16);
 #pragma unroll
       for (int i = 0; i < GV; ++i) g[i] = 0.f;
 #pragma unroll
@@ -95,9 +111,12 @@ __global__ void __launch_bounds__(kThreads) k_fused_rs_opt_ag(DcpDevCtx c, size_
         for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) st16_stream(c.peer[p] + poff + (e0 + i) * 4, out);
       }
     }
+#pragma unroll
+    for (int p = 0; p < DCP_MAX_RANKS; ++p) raw[p] = nxt[p];
   }
   dcp_barrier(c, chan);
-}
+  }
+};
 }  // namespace
 
 extern "C" {
@@ -131,7 +150,7 @@ int dcp_fused_rs_opt_ag(void* h, const void* grads, float* params, float* s1, fl
   if (max_ctas <= 0) max_ctas = 148;        // the shard is streamed once (5-7 arrays): every SM has to pull (measured: 32 CTAs 753 us, 148 222 us, 296 238 us for 32 M elements)
   if (grid > max_ctas) grid = max_ctas;
   if (grid > DCP_MAX_BLOCKS) grid = DCP_MAX_BLOCKS;
-#define LAUNCH(K, G, NV) k_fused_rs_opt_ag<K, G, NV><<<(int)grid, kThreads, 0, stream>>>(c, goff, poff, s1, s2, n, hp, chan)
+#define LAUNCH(K, G, NV) coll_launch<FusedRsOptAgBody<K, G, NV>>(h, c, {goff, poff, s1, s2, n, hp, chan}, (int)grid, stream)
 #define BY_KIND(G, NV) do { if (kind == 0) LAUNCH(0, G, NV); else if (kind == 1) LAUNCH(1, G, NV); else LAUNCH(2, G, NV); } while (0)
   if (grad_dtype == DCP_F32) { if (nvls) BY_KIND(float, true); else BY_KIND(float, false); }
   else { if (nvls) BY_KIND(__nv_bfloat16, true); else BY_KIND(__nv_bfloat16, false); }

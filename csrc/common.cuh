@@ -74,8 +74,10 @@ struct DcpHeapLayout {
   static constexpr size_t kCallsBytes = kEpochBytes;
   static constexpr size_t kSendSeqOff = kCallsOff + kCallsBytes;                         // u32 [dst][block]
   static constexpr size_t kRecvSeqOff = kSendSeqOff + kP2PFlagBytes;                     // u32 [src][block]
+  static constexpr size_t kGCallsOff = kRecvSeqOff + kP2PFlagBytes;                      // u32 [chan][2]: launches completed, CTA ticket
+  static constexpr size_t kGCallsBytes = (size_t)DCP_NUM_CHANNELS * 2 * 4;
   static constexpr size_t kCtlBytes = 1u << 20;                                          // control region, zeroed at init
-  static_assert(kRecvSeqOff + kP2PFlagBytes <= kCtlBytes, "control region overflow");
+  static_assert(kGCallsOff + kGCallsBytes <= kCtlBytes, "control region overflow");
 };
 
 // Passed by value to every collective kernel.
@@ -132,6 +134,21 @@ __device__ __forceinline__ uint32_t* dcp_epoch(char* heap, int chan, int block) 
 }
 __device__ __forceinline__ uint32_t* dcp_calls(char* heap, int chan, int block) {
   return reinterpret_cast<uint32_t*>(heap + DcpHeapLayout::kCallsOff) + (size_t)chan * DCP_MAX_BLOCKS + block;
+}
+
+// Launch counter of a channel (local control memory): the same value in every CTA of a launch and - because all ranks
+// issue the same sequence of collectives - on every rank.  Staged kernels whose copy-in and reduce partitions differ pick
+// their bounce half from its parity.  dcp_gcalls_finish() is called by every CTA as its last action: the CTA that draws the
+// last ticket advances the counter, i.e. only after every CTA of the launch has read it.
+__device__ __forceinline__ uint32_t dcp_gcalls(char* heap, int chan) {
+  return *((volatile uint32_t*)(heap + DcpHeapLayout::kGCallsOff) + chan * 2);
+}
+__device__ __forceinline__ void dcp_gcalls_finish(char* heap, int chan) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* w = reinterpret_cast<uint32_t*>(heap + DcpHeapLayout::kGCallsOff) + chan * 2;
+    if (atomicAdd(w + 1, 1u) == gridDim.x - 1) { w[1] = 0; __threadfence(); *((volatile uint32_t*)w) = *((volatile uint32_t*)w) + 1; }
+  }
 }
 
 // Barrier between the CTAs with this blockIdx.x on every rank.  All threads of the CTA must call it.

@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "coll/coll_launch.cuh"
 #include "common.cuh"
 
 static thread_local char g_err[1024] = "";
@@ -104,7 +105,19 @@ struct Symm {
   int* err_host = nullptr;  // pinned, mapped
   int* err_dev = nullptr;
   DcpDevCtx ctx{};
+  struct EmuGroup* emu = nullptr;   // member of an emulated world (all ranks on this GPU): collective launches are recorded, not executed
 };
+
+// An emulated world: W heaps on ONE GPU in ONE process, wired to each other as "peers".  Collectives issued on its members are
+// queued per rank; dcp_emu_flush() launches slot i of every rank as one cooperative kernel (coll_launch.cuh).
+struct EmuGroup {
+  int world = 0, device = 0;
+  std::vector<Symm*> members;
+  std::vector<std::vector<DcpEmuRecord>> pending;   // [rank][slot]
+  DcpDevCtx* cs_dev = nullptr;
+  unsigned char* args_dev = nullptr;                // kEmuSlots x world x kEmuMaxArgBytes
+};
+constexpr int kEmuSlots = 64;
 
 int set_access(CUdeviceptr va, size_t bytes, int device) {
   CUmemAccessDesc acc{};
@@ -310,6 +323,107 @@ void dcp_symm_destroy(void* h) {
   }
   if (s->err_host) cudaFreeHost(s->err_host);
   delete s;
+}
+
+}  // extern "C"
+
+// ---- emulated world (single-GPU test tier) -----------------------------------------------------------
+bool dcp_emu_record(void* h, const DcpEmuRecord& r) {
+  auto* s = static_cast<Symm*>(h);
+  if (s->emu == nullptr) return false;
+  s->emu->pending[s->rank].push_back(r);
+  return true;
+}
+
+extern "C" {
+
+// Create `world` heaps of heap_bytes each on `device`, every one seeing the others as its peers (plain device pointers: same
+// process, same GPU), no multicast.  Returns the group; dcp_emu_rank(group, r) is an ordinary heap handle for every other
+// entry point of this library - except that collectives issued on it are deferred until dcp_emu_flush().
+void* dcp_emu_create(int world, int device, size_t heap_bytes, double timeout_s, size_t p2p_slot_bytes, size_t staging_bytes) {
+  if (world < 1 || world > DCP_MAX_RANKS) { dcp_set_error("emulated world size %d not in [1, %d]", world, DCP_MAX_RANKS); return nullptr; }
+  auto* g = new EmuGroup;
+  g->world = world; g->device = device;
+  g->pending.resize(world);
+  for (int r = 0; r < world; ++r) {
+    auto* s = static_cast<Symm*>(dcp_symm_create(r, world, device, heap_bytes, 1));
+    if (!s) { for (auto* m : g->members) dcp_symm_destroy(m); delete g; return nullptr; }
+    g->members.push_back(s);
+  }
+  std::vector<DcpDevCtx> cs(world);
+  for (int r = 0; r < world; ++r) {
+    Symm* s = g->members[r];
+    for (int p = 0; p < world; ++p) s->peer_va[p] = g->members[p]->peer_va[p];
+    if (dcp_symm_finalize(s, timeout_s, p2p_slot_bytes, staging_bytes, 0) != 0) { for (auto* m : g->members) dcp_symm_destroy(m); delete g; return nullptr; }
+    s->emu = g;
+    cs[r] = s->ctx;
+  }
+  if (cudaMalloc((void**)&g->cs_dev, sizeof(DcpDevCtx) * world) != cudaSuccess ||
+      cudaMalloc((void**)&g->args_dev, (size_t)kEmuSlots * world * kEmuMaxArgBytes) != cudaSuccess ||
+      cudaMemcpy(g->cs_dev, cs.data(), sizeof(DcpDevCtx) * world, cudaMemcpyHostToDevice) != cudaSuccess) {
+    dcp_set_error("emulated world: device allocation failed"); return nullptr;
+  }
+  return g;
+}
+
+void* dcp_emu_rank(void* group, int r) {
+  auto* g = static_cast<EmuGroup*>(group);
+  return (r >= 0 && r < g->world) ? g->members[r] : nullptr;
+}
+
+int dcp_emu_pending(void* group) {
+  auto* g = static_cast<EmuGroup*>(group);
+  size_t n = 0;
+  for (auto& q : g->pending) n = q.size() > n ? q.size() : n;
+  return (int)n;
+}
+
+// Launch everything the ranks have queued: slot i of every rank becomes ONE cooperative kernel of (grid, world) CTAs on
+// `stream`.  The ranks must have queued the same collectives in the same order (same kernel, same grid) - as they would have
+// to on N GPUs; point-to-point slots may be empty on ranks that take no part.  Returns -1 (and drops the queue) on a mismatch.
+int dcp_emu_flush(void* group, cudaStream_t stream) {
+  auto* g = static_cast<EmuGroup*>(group);
+  const int W = g->world;
+  const int n = dcp_emu_pending(group);
+  int rc = 0;
+  std::vector<unsigned char> host((size_t)W * kEmuMaxArgBytes);
+  for (int i = 0; i < n && rc == 0; ++i) {
+    const DcpEmuRecord* ref = nullptr;
+    for (int r = 0; r < W; ++r) if ((int)g->pending[r].size() > i) { ref = &g->pending[r][i]; break; }
+    std::fill(host.begin(), host.end(), 0);
+    for (int r = 0; r < W && rc == 0; ++r) {
+      if ((int)g->pending[r].size() <= i) {
+        if (!ref->idle_ok) { dcp_set_error("emulated world: rank %d issued %zu collectives, another rank at least %d", r, g->pending[r].size(), i + 1); rc = -1; }
+        continue;
+      }
+      const DcpEmuRecord& q = g->pending[r][i];
+      if (q.launch != ref->launch || q.grid != ref->grid || q.arg_bytes != ref->arg_bytes) {
+        dcp_set_error("emulated world: the ranks issued different collectives in slot %d (kernel or grid differ)", i); rc = -1; continue;
+      }
+      memcpy(host.data() + (size_t)r * q.arg_bytes, q.args, q.arg_bytes);
+    }
+    if (rc != 0) break;
+    if (i > 0 && i % kEmuSlots == 0) cudaStreamSynchronize(stream);       // the argument ring is about to wrap
+    unsigned char* dst = g->args_dev + (size_t)(i % kEmuSlots) * W * kEmuMaxArgBytes;
+    if (cudaMemcpyAsync(dst, host.data(), (size_t)W * ref->arg_bytes, cudaMemcpyHostToDevice, stream) != cudaSuccess) { dcp_set_error("emulated world: argument upload failed"); rc = -1; break; }
+    cudaError_t e = ref->launch(g->cs_dev, dst, ref->grid, W, stream);
+    if (e != cudaSuccess) { dcp_set_error("emulated world: cooperative launch failed: %s", cudaGetErrorString(e)); rc = -1; }
+  }
+  for (auto& q : g->pending) q.clear();
+  return rc;
+}
+
+void dcp_emu_destroy(void* group) {
+  auto* g = static_cast<EmuGroup*>(group);
+  cudaSetDevice(g->device);
+  cudaDeviceSynchronize();
+  for (auto* m : g->members) {
+    for (int p = 0; p < g->world; ++p) if (p != m->rank) m->peer_va[p] = 0;     // peers belong to their own handles
+    dcp_symm_destroy(m);
+  }
+  if (g->cs_dev) cudaFree(g->cs_dev);
+  if (g->args_dev) cudaFree(g->args_dev);
+  delete g;
 }
 
 }  // extern "C"

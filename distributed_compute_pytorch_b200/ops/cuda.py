@@ -667,8 +667,10 @@ def fused_optimizer_step(opt, gi: int, group: dict, items: List[Tuple[torch.Tens
         table.copy_(host, non_blocking=True)
         first_step = items[0][2].get("step", 1)
         hp = ent["hp"] if ent is not None else torch.zeros(8, dtype=torch.float32, device=dev)
-        # (re)seed the device step counter from the optimizer state: first build, or a rebuild after load_state_dict()
-        hp[6] = float(int(first_step) - 1)
+        # (re)seed the device step counter from the optimizer state: first build, or a rebuild because load_state_dict() replaced
+        # the state tensors (a rebuild for new gradient pointers - e.g. under graph capture - keeps the running counter)
+        if ent is None or [k[2:] for k in ent["key"]] != [k[2:] for k in key]:
+            hp[6] = float(int(first_step) - 1)
         ent = {"key": key, "table": table, "host": host, "hp": hp, "hyper": ent["hyper"] if ent else None, "n": len(items),
                "max": max(p.numel() for p, _, _ in items)}
         cache[gi] = ent

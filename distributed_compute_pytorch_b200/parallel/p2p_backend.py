@@ -87,6 +87,7 @@ class P2PBackend:
         self.comm_stream = torch.cuda.Stream(device=self._torch_dev, priority=-1)
         self._algo_override = int(os.environ.get("DCP_ALLREDUCE_ALGO", "0"))
         self.launches = 0
+        self.default_max_ctas = 0        # 0: the native side sizes the grid from the message
         store.barrier("p2p_ready", rank, world_size, timeout)
 
     # ------------------------------------------------------------------ bring-up -----------------
@@ -276,7 +277,7 @@ class P2PBackend:
         nbytes = t.numel() * t.element_size()
         algo = algo or self.pick_allreduce_algo(t, op, nbytes)
         if max_ctas <= 0:
-            max_ctas = 16 if nbytes <= (1 << 20) else (64 if nbytes <= (32 << 20) else 148)
+            max_ctas = self.default_max_ctas or (16 if nbytes <= (1 << 20) else (64 if nbytes <= (32 << 20) else 148))
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_all_reduce(self._h, t.data_ptr(), t.numel(), self._code(t), int(op), algo, chan, max_ctas, self._stream(stream))
         self._check(rc, "all_reduce")
@@ -297,7 +298,7 @@ class P2PBackend:
         if self.world == 1:
             return
         with torch.cuda.device(self._torch_dev):
-            rc = self.lib.dcp_broadcast(self._h, t.data_ptr(), t.numel() * t.element_size(), src, chan, 0, self._stream(stream))
+            rc = self.lib.dcp_broadcast(self._h, t.data_ptr(), t.numel() * t.element_size(), src, chan, self.default_max_ctas, self._stream(stream))
         self._check(rc, "broadcast")
         if back:
             tensor.detach().copy_(t)
@@ -308,7 +309,7 @@ class P2PBackend:
             return
         out = t if self.rank == dst else t  # non-root output is never written
         with torch.cuda.device(self._torch_dev):
-            rc = self.lib.dcp_reduce_scatter(self._h, t.data_ptr(), out.data_ptr(), t.numel(), self._code(t), int(op), dst, CH_USER, 0, self._stream(stream))
+            rc = self.lib.dcp_reduce_scatter(self._h, t.data_ptr(), out.data_ptr(), t.numel(), self._code(t), int(op), dst, CH_USER, self.default_max_ctas, self._stream(stream))
         self._check(rc, "reduce")
         if back and self.rank == dst:
             tensor.detach().copy_(t)
@@ -322,7 +323,7 @@ class P2PBackend:
             out.view(-1).copy_(t.view(-1))
             return
         with torch.cuda.device(self._torch_dev):
-            rc = self.lib.dcp_all_gather(self._h, t.data_ptr(), out.data_ptr(), t.numel() * t.element_size(), -1, CH_USER, 0, self._stream(stream))
+            rc = self.lib.dcp_all_gather(self._h, t.data_ptr(), out.data_ptr(), t.numel() * t.element_size(), -1, CH_USER, self.default_max_ctas, self._stream(stream))
         self._check(rc, "all_gather")
 
     def all_gather(self, outputs: List[torch.Tensor], tensor: torch.Tensor) -> None:
@@ -339,7 +340,7 @@ class P2PBackend:
             return
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_all_gather(self._h, t.data_ptr(), flat.data_ptr() if flat is not None else None,
-                                         t.numel() * t.element_size(), dst, CH_USER, 0, self._stream())
+                                         t.numel() * t.element_size(), dst, CH_USER, self.default_max_ctas, self._stream())
         self._check(rc, "gather")
         if self.rank == dst:
             for r, o in enumerate(gather_list):
@@ -353,7 +354,7 @@ class P2PBackend:
         flat = torch.cat([s.detach().reshape(-1) for s in scatter_list]) if self.rank == src else None
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_scatter(self._h, flat.data_ptr() if flat is not None else None, out.data_ptr(),
-                                      out.numel() * out.element_size(), src, CH_USER, 0, self._stream())
+                                      out.numel() * out.element_size(), src, CH_USER, self.default_max_ctas, self._stream())
         self._check(rc, "scatter")
         if back:
             tensor.detach().copy_(out)
@@ -367,7 +368,7 @@ class P2PBackend:
             output.detach().copy_(inp.view(output.shape))
             return
         with torch.cuda.device(self._torch_dev):
-            rc = self.lib.dcp_reduce_scatter(self._h, inp.data_ptr(), out.data_ptr(), out.numel(), self._code(out), int(op), -1, CH_USER, 0,
+            rc = self.lib.dcp_reduce_scatter(self._h, inp.data_ptr(), out.data_ptr(), out.numel(), self._code(out), int(op), -1, CH_USER, self.default_max_ctas,
                                              self._stream(stream))
         self._check(rc, "reduce_scatter")
         if back:
