@@ -30,23 +30,79 @@ def cleanup():
     dist.destroy_process_group()
 
 
-def train(opt, model, rank, train_loader, optimizer, epoch, device=None):
+class _LossPrinter:
+    """The reference's every-10th-batch line (ref:main.py:64-68: all_reduce(SUM) of the batch loss, printed on rank 0) without
+    stalling the GPU: the reduced value travels to pinned host memory behind an event and is printed once it has arrived - at
+    the next print step or at the end of the pass - in the same order and with the same text."""
+
+    def __init__(self, rank, device):
+        self.rank, self.pending = rank, []
+        self.cuda = torch.device(device).type == "cuda" if not isinstance(device, int) else True
+
+    def submit(self, loss, epoch, b, total):
+        red = loss.detach().clone()
+        dist.all_reduce(red, op=dist.ReduceOp.SUM)
+        if self.rank != 0:
+            return
+        if not self.cuda:
+            self._emit(epoch, b, total, red.item()); return
+        host = torch.empty((), dtype=red.dtype).pin_memory()
+        host.copy_(red, non_blocking=True)
+        ev = torch.cuda.Event(); ev.record()
+        self.pending.append((ev, host, epoch, b, total))
+        self.drain(block=False)
+
+    def drain(self, block=True):
+        while self.pending and (block or self.pending[0][0].query()):
+            ev, host, epoch, b, total = self.pending.pop(0)
+            ev.synchronize()
+            self._emit(epoch, b, total, host.item())
+
+    @staticmethod
+    def _emit(epoch, b, total, value):
+        print(f"epoch: {epoch} [{b}/{total} \
+          ({100. * b/total}%)]\t Loss:{value}")
+
+
+def _make_engine(opt, model, optimizer, device):
+    """--engine: 'eager' = layer-by-layer autograd (the reference's loop body), 'graph' = the same body captured once in a CUDA
+    graph (any model), 'fused' = the hand-scheduled flagship step (parallel.FusedConvNetTrainer: ~19 kernels, one graph,
+    gradient exchange fused into the kernels).  'auto' picks the fastest one the run is eligible for."""
+    dev = torch.device(device) if not isinstance(device, int) else torch.device("cuda", device)
+    want = opt.engine
+    if dev.type != "cuda" or want == "eager":
+        return None
+    net = model.module if hasattr(model, "module") else model
+    fused_ok = isinstance(net, ConvNet) and opt.batch_size % 32 == 0 and 32 <= opt.batch_size <= 128
+    if want in ("auto", "fused") and fused_ok:
+        from distributed_compute_pytorch_b200.parallel.convnet_trainer import FusedConvNetTrainer
+        return FusedConvNetTrainer(model, optimizer, opt.batch_size)
+    if want == "fused":
+        raise SystemExit("--engine fused needs the ConvNet model and a batch size that is a multiple of 32 in [32, 128]")
+    from distributed_compute_pytorch_b200.parallel.engine import GraphedTrainStep
+    x = torch.zeros(opt.batch_size, 1, 28, 28, device=dev); y = torch.zeros(opt.batch_size, dtype=torch.int64, device=dev)
+    return GraphedTrainStep(model, optimizer, lambda o, t: ops.nll_loss(o, t), x, y, device=dev)
+
+
+def train(opt, model, rank, train_loader, optimizer, epoch, device=None, engine=None):
     device = rank if device is None else device
     model.train()
+    printer = _LossPrinter(rank, device)
     for b, (img, label) in enumerate(train_loader):
-        img, label = img.to(device), label.to(device)
-        optimizer.zero_grad()
-        out = model(img)
-        loss = ops.nll_loss(out, label)
-        loss.backward()
-        optimizer.step()
+        if engine is not None and len(img) == opt.batch_size:
+            loss = engine(img, label)          # pinned host batch -> staged H2D copy -> one graph replay
+        else:                                  # eager path: also takes the (smaller) last batch of a pass
+            img, label = img.to(device), label.to(device)
+            optimizer.zero_grad()
+            out = model(img)
+            loss = ops.nll_loss(out, label)
+            loss.backward()
+            optimizer.step()
         if b % 10 == 0:
-            dist.all_reduce(loss, op=dist.ReduceOp.SUM)
-            if rank == 0:
-                print(f"epoch: {epoch} [{b}/{len(train_loader)} \
-          ({100. * b/len(train_loader)}%)]\t Loss:{loss.item()}")
+            printer.submit(loss, epoch, b, len(train_loader))
         if opt.max_steps and b + 1 >= opt.max_steps:
             break
+    printer.drain()
 
 
 def test(opt, model, rank, test_loader, optimizer, epoch, device=None):
@@ -106,8 +162,11 @@ def proc(rank, world_size, opt, use_cuda):
     optimizer = ops.Adadelta(model.parameters(), lr=opt.lr)
     scheduler = ops.StepLR(optimizer, step_size=1, gamma=opt.gamma)
 
-    from distributed_compute_pytorch_b200.utils import Tracer, load_model, load_training_state, save_training_state
+    from distributed_compute_pytorch_b200.utils import Tracer, load_model, load_training_state, save_model, save_training_state
     tracer = Tracer(rank=rank)                 # DCP_TRACE=<prefix> writes <prefix>_rank<r>.json (chrome://tracing) at the end
+    if opt.no_dropout:
+        net = model.module if hasattr(model, "module") else model
+        net.dropout1.p = net.dropout2.p = 0.0
     start_epoch = 0
     if opt.resume and os.path.exists(opt.checkpoint):      # not in the reference (save-only): model file + optimizer / schedule / epoch sidecar
         load_model(opt.checkpoint, model)
@@ -115,21 +174,21 @@ def proc(rank, world_size, opt, use_cuda):
             start_epoch = int(load_training_state(opt.checkpoint + ".state", optimizer, scheduler).get("epoch") or 0)
         if rank == 0:
             print(f"resumed from {opt.checkpoint} at epoch {start_epoch}")
+    engine = _make_engine(opt, model, optimizer, device)      # built after --resume: it captures the optimizer's state pointers
     for epoch in range(start_epoch, opt.epochs):
         t0 = time.time()
         with tracer.range(f"train epoch {epoch}"):
-            train(opt, model, rank, train_loader, optimizer, epoch, device)
+            train(opt, model, rank, train_loader, optimizer, epoch, device, engine)
         with tracer.range(f"eval epoch {epoch}"):
             test(opt, model, rank, train_loader, optimizer, epoch, device)   # the reference evaluates on the train loader (ref:main.py:130)
         scheduler.step()
         print(f"time to complete this epoch: {time.time() - t0} seconds")
     if tracer.enabled:
         tracer.export_chrome(f"{os.environ['DCP_TRACE']}_rank{rank}.json")
-    if rank == 0:
-        torch.save(model.state_dict(), opt.checkpoint)      # rank 0 only (every rank writes the same file in the reference, ref:main.py:133)
-    dist.barrier()
-    if opt.resume:
-        save_training_state(opt.checkpoint + ".state", optimizer, scheduler, epoch=opt.epochs)
+    # rank 0 only, temp file + rename, then a barrier (every rank writes the same file in the reference, ref:main.py:133).  The
+    # optimizer / schedule / epoch sidecar goes first, so a model file never sits next to an older sidecar.
+    save_training_state(opt.checkpoint + ".state", optimizer, scheduler, epoch=opt.epochs)
+    save_model(opt.checkpoint, model)
     cleanup()
 
 
@@ -151,6 +210,9 @@ def build_parser():
     parser.add_argument('--backend', default=None, help="gloo|nccl|b200|cpu (default: GPU backend iff CUDA)")
     parser.add_argument('--max-steps', type=int, default=0, help="stop each epoch pass after this many batches (0 = all)")
     parser.add_argument('--checkpoint', default="mnist.pt")
+    parser.add_argument('--engine', default="auto", choices=["auto", "eager", "graph", "fused"],
+                        help="training-step engine on CUDA: eager autograd, the same step in one CUDA graph, or the fused flagship step")
+    parser.add_argument('--no-dropout', action='store_true', help="p = 0 for both dropout layers (deterministic runs / engine comparisons)")
     parser.add_argument('--resume', action='store_true', help="continue from --checkpoint (+ .state sidecar) and write the sidecar at the end")
     return parser
 

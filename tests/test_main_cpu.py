@@ -90,3 +90,22 @@ def test_checkpoint_helpers_roundtrip(tmp_path):
     assert st["epoch"] == 1 and sch2.last_epoch == sch.last_epoch
     a = opt.state_dict()["state"][0]["square_avg"]; b = opt2.state_dict()["state"][0]["square_avg"]
     assert torch.equal(a, b)
+
+
+def test_resume_continues_epoch_and_lr(tmp_path, free_port):
+    """A first run always leaves the optimizer / schedule / epoch sidecar next to the checkpoint (written before the model
+    file); --resume picks both up: the second run starts at the stored epoch with the decayed learning rate."""
+    ck = tmp_path / "mnist.pt"
+    base = [sys.executable, os.path.join(ROOT, "main.py"), "--batch_size", "16", "--data-size", "64", "--no-cuda", "True",
+            "--checkpoint", str(ck), "--lr", "1.0", "--gamma", "0.5"]
+    env = dict(os.environ, MASTER_PORT=str(free_port), MASTER_ADDR="127.0.0.1", PYTHONPATH=ROOT)
+    r = subprocess.run(base + ["--epochs", "1"], capture_output=True, text=True, timeout=600, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout + r.stderr
+    state = torch.load(str(ck) + ".state", weights_only=False)
+    assert state["epoch"] == 1 and abs(state["optimizer"]["param_groups"][0]["lr"] - 0.5) < 1e-12
+    r = subprocess.run(base + ["--epochs", "3", "--resume"], capture_output=True, text=True, timeout=600, env=env, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "resumed from" in r.stdout and "at epoch 1" in r.stdout
+    assert "epoch: 1 [0/2" in r.stdout and "epoch: 2 [0/2" in r.stdout and "epoch: 0 [" not in r.stdout
+    state = torch.load(str(ck) + ".state", weights_only=False)
+    assert state["epoch"] == 3 and abs(state["optimizer"]["param_groups"][0]["lr"] - 0.125) < 1e-12
