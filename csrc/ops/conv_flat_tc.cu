@@ -26,8 +26,12 @@ struct FlatConvParams {
   int min_off, span;      // min(off), max(off) - min(off)
   int W, HW, Hv, Wv;      // row pitch, pixels per image, valid output extent (mode 0)
   int mode;               // 0: out = valid ? relu(acc + bias) : 0      1: out = mask > 0 ? acc : 0
+                          // 2: relu(acc + bias) -> 2x2 max-pool -> channel dropout, written as pooled[N][Cout][Hv/2][Wv/2] + argmax bytes
   float* out; const float* bias; const float* mask;
   int tiles;
+  int tiles_per_img, tile_rows;   // mode 2: a tile = 4 image rows (tile_rows = 4 W flat pixels), tiles_per_img = Hv / 4; else 0 / kBM
+  uint8_t* arg;                   // mode 2: position (0..3) of the maximum inside each 2x2 window
+  float drop_p; unsigned long long seed, stream; const long long* step; int training;   // mode 2: Philox channel dropout (ops_common.cuh)
   int use_base_offset;
   long long* dbg;         // optional: per-CTA clock64 trace (CTA 0 only); -DDCP_TRACE builds only
 };
@@ -50,7 +54,14 @@ struct __align__(16) Bars {
   uint32_t adelta[72], wdelta[72];     // per-MMA start-address increments (16-byte units) of the A / W descriptors
   alignas(16) float bias[64];
   alignas(16) float stage_out[8][32][36];          // per-epilogue-warp transpose buffer: coalesced 128-byte row stores
+                                                   // (mode 2: one [Cout][kPoolPitch] tile of activations shared by the 8 epilogue warps)
+  float keep[64];                                  // mode 2: dropout factor of each channel of the tile's image
 };
+constexpr int kPoolPitch = 105;                    // 4 x 26 pixels + 1: consecutive lanes (pixels) hit consecutive banks
+static_assert(64 * kPoolPitch <= 8 * 32 * 36, "pool tile must fit in the transpose buffers");
+__device__ __forceinline__ long flat_tile_start(const FlatConvParams& p, long tile) {
+  return p.tiles_per_img ? (tile / p.tiles_per_img) * (long)p.HW + (tile % p.tiles_per_img) * (long)p.tile_rows : tile * (long)128;
+}
 
 template <int kMode>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -112,7 +123,7 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
     __syncwarp();
     for (int i = 0; i < my_tiles; ++i) {
       const int st = i % stages, ph = (i / stages) & 1;
-      const long p0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM;
+      const long p0 = flat_tile_start(p, blockIdx.x + (long)i * gridDim.x);
       mbar_wait(&bars->empty[st], ph ^ 1);
       if (lane == 0) {
         mbar_expect_tx(&bars->full[st], stage_bytes);
@@ -172,7 +183,7 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
     for (int j = 0; j < 8; ++j) bias4[j] = *reinterpret_cast<const float4*>(&bars->bias[c0 + 4 * j]);
     for (int i = 0; i < my_tiles; ++i) {
       const int ab = i & 1, aph = (i >> 1) & 1;
-      const long tile0 = (long)(blockIdx.x + (long)i * gridDim.x) * kBM;
+      const long tile0 = flat_tile_start(p, blockIdx.x + (long)i * gridDim.x);
       float vm = 1.f;
       if (kMode == 0) {
         const int q = (int)((tile0 + row) % p.HW);
@@ -197,6 +208,46 @@ k_conv_flat(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) mbar_arrive(&bars->acc_empty[ab]);
       if (dbg && i < 8 && warp == 2 && lane == 0) dbg[8 + i * 8 + 5] = clock64();
+      if (kMode == 2) {
+        // ---- fused 2x2 max-pool + channel dropout: the tile is 4 image rows (2 pooled rows) of one image.
+        // phase 1: every epilogue warp drops relu(acc + bias) of its 32 pixels x 32 channels into the shared [channel][pixel] tile
+        float* pt = &bars->stage_out[0][0][0];
+        const int e = (warp - 2) * 32 + lane;                 // 0 .. 255 over the 8 epilogue warps
+        const int img = (int)(tile0 / p.HW);
+        if (row < p.tile_rows) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float b = reinterpret_cast<const float*>(bias4)[j];
+            pt[(c0 + j) * kPoolPitch + row] = fmaxf(__uint_as_float(r[j]) + b, 0.f);
+          }
+        }
+        if (e < p.Cout) {
+          float k = 1.f;
+          if (p.training && p.drop_p > 0.f) {
+            const unsigned long long st = p.stream + (p.step ? (unsigned long long)(*p.step) * 0x10000ull : 0ull);
+            k = philox_uniform(p.seed, st, (unsigned long long)(img * p.Cout + e)) >= p.drop_p ? 1.f / (1.f - p.drop_p) : 0.f;
+          }
+          bars->keep[e] = k;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        // phase 2: per channel the two pooled rows of the tile are 2 * (Wv / 2) CONTIGUOUS outputs in the NCHW-flattened layout fc1 reads
+        const int pwn = p.Wv >> 1, per_c = 2 * pwn, hp = p.Hv >> 1;
+        const int rb = (int)((tile0 % p.HW) / p.tile_rows);   // row block of this tile inside its image
+        for (int it = e; it < p.Cout * per_c; it += 256) {
+          const int c = it / per_c, q = it % per_c, pr = q / pwn, pw = q % pwn;
+          const float* src = pt + c * kPoolPitch + (2 * pr) * p.W + 2 * pw;
+          const float v0 = src[0], v1 = src[1], v2 = src[p.W], v3 = src[p.W + 1];
+          float m = v0; int a = 0;
+          if (v1 > m) { m = v1; a = 1; }
+          if (v2 > m) { m = v2; a = 2; }
+          if (v3 > m) { m = v3; a = 3; }
+          const long o = (((long)img * p.Cout + c) * hp + (rb * 2 + pr)) * pwn + pw;
+          p.out[o] = m * bars->keep[c];
+          p.arg[o] = (uint8_t)a;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");        // the tile is reused by the next iteration
+        continue;
+      }
       // lane = row: bias / ReLU / validity, then transpose through shared memory
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -264,8 +315,8 @@ extern "C" {
 
 // in: [P, Cin] fp32 flat pixels (pitch W, HW pixels per image); wmat: [Cout][taps*Cin] fp32 (tap-major columns);
 // off[t]: flat row shift of tap t.  mode 0: out = (h < Hv && w < Wv) ? relu(acc + bias) : 0;  mode 1: out = mask > 0 ? acc : 0.
-int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps,
-                     const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, cudaStream_t s) {
+static int conv_flat_launch(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps,
+                            const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, const FlatConvParams* extra, cudaStream_t s) {
   if ((Cin != 32 && Cin != 64) || (Cout != 32 && Cout != 64) || taps < 1 || taps > 9) { dcp_set_error("flat conv: unsupported Cin/Cout/taps %d/%d/%d", Cin, Cout, taps); return -1; }
   if (taps < kIssuers) { dcp_set_error("flat conv: needs at least %d filter taps (one per issuing warp)", kIssuers); return -1; }
   FlatConvParams p{};
@@ -275,6 +326,13 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   for (int t = 0; t < taps; ++t) { p.off[t] = off[t]; mn = off[t] < mn ? off[t] : mn; mx = off[t] > mx ? off[t] : mx; }
   p.min_off = mn; p.span = mx - mn;
   p.tiles = (int)((P + kBM - 1) / kBM);
+  p.tile_rows = kBM;
+  if (mode == 2) {
+    // a tile = 4 image rows: the 2x2 windows of two pooled rows live inside one accumulator tile
+    if ((Hv & 3) || (Wv & 1) || 4 * W > kBM || Cout != 64 || P % HW) { dcp_set_error("flat conv + pool: needs Hv %% 4 == 0, even Wv, 4 * W <= %d, Cout == 64", kBM); return -1; }
+    p.tiles_per_img = Hv / 4; p.tile_rows = 4 * W; p.tiles = (int)(P / HW) * p.tiles_per_img;
+    p.arg = extra->arg; p.drop_p = extra->drop_p; p.seed = extra->seed; p.stream = extra->stream; p.step = extra->step; p.training = extra->training;
+  }
   { static const int base_off = [] { const char* e = getenv("DCP_FLAT_BASEOFF"); return e ? atoi(e) : 0; }(); p.use_base_offset = base_off; }
 #ifdef DCP_TRACE
   { const char* e = getenv("DCP_FLAT_DBG_PTR"); p.dbg = e ? (long long*)strtoull(e, nullptr, 0) : nullptr; }
@@ -295,6 +353,7 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   if (!attr) {
     DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
     DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_conv_flat<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, budget));
     attr = true;
   }
   CUtensorMap mi, mw;
@@ -303,9 +362,29 @@ int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float
   if (num_ctas <= 0) num_ctas = 148;
   if (num_ctas > p.tiles) num_ctas = p.tiles;
   if (mode == 0) DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<0>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
-  else DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<1>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
+  else if (mode == 1) DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<1>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
+  else DCP_CUDA_CHECK(dcp_launch_pdl(k_conv_flat<2>, dim3(num_ctas), dim3(kThreads), smem, s, mi, mw, p, stages, halo_rows));
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
+}
+
+int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps,
+                     const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, cudaStream_t s) {
+  if (mode != 0 && mode != 1) { dcp_set_error("flat conv: mode must be 0 or 1 (the pooling epilogue is dcp_conv_flat_pool_tc)"); return -1; }
+  return conv_flat_launch(in, wmat, out, bias, mask, P, Cin, Cout, taps, off, W, HW, Hv, Wv, mode, num_ctas, nullptr, s);
+}
+
+// Convolution + bias + ReLU + 2x2 max-pool + channel dropout in ONE kernel (K3-K6 of the reference model, ref:main.py:34-37): the
+// conv output never reaches memory.  pooled: [N][Cout][Hv/2][Wv/2] fp32 (the NCHW-flattened order fc1 consumes, ref:main.py:38-39),
+// arg: one byte per pooled element = position of the maximum in its window (for the backward pass).  Dropout drops whole channels
+// of an image with probability drop_p (scaled by 1/(1-p)), Philox stream `stream` + step counter, regenerated - not stored - in
+// backward.  Needs Hv % 4 == 0, Wv even, 4 * W <= 128 flat pixels, Cout == 64.
+int dcp_conv_flat_pool_tc(const float* in, const float* wmat, float* pooled, void* arg, const float* bias, long P, int Cin, int Cout, int taps,
+                          const int* off, int W, int HW, int Hv, int Wv, float drop_p, unsigned long long seed, unsigned long long stream,
+                          const void* step, int training, int num_ctas, cudaStream_t s) {
+  FlatConvParams e{};
+  e.arg = static_cast<uint8_t*>(arg); e.drop_p = drop_p; e.seed = seed; e.stream = stream; e.step = static_cast<const long long*>(step); e.training = training;
+  return conv_flat_launch(in, wmat, pooled, bias, nullptr, P, Cin, Cout, taps, off, W, HW, Hv, Wv, 2, num_ctas, &e, s);
 }
 
 }  // extern "C"

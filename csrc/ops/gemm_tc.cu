@@ -452,6 +452,13 @@ int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, in
   if (ksplit > 1 && (relu || out_bf16)) { dcp_set_error("tc gemm: split-K needs an fp32 output and no ReLU"); return -1; }
   TcGemmParams p{};
   p.M = M; p.N = N; p.k_stages = K / bk; p.BN = pick_bn(N); p.a_mn = a_mn; p.b_mn = b_mn;
+  {
+    // wide, shallow problems (fc1's weight / data gradient: 128 x 9216, K = 128) are pure streaming: with 128-column tiles only
+    // 72 CTAs exist and half the SMs (and their share of the memory system) idle; 64-column tiles double the CTAs
+    static const int narrow = [] { const char* e = getenv("DCP_GEMM_NARROW"); return e ? atoi(e) : 1; }();
+    const long tiles = (long)((M + kBM - 1) / kBM) * ((N + p.BN - 1) / p.BN) * (ksplit < 1 ? 1 : ksplit);
+    if (narrow && p.BN == 128 && tiles < 100) p.BN = narrow >= 2 ? 32 : 64;
+  }
   p.b_bytes = b_stage_bytes(p.BN, b_mn, es); p.a_bytes = kABytes; p.groups = 1; p.x3 = (x3 && dtype == DCP_F32) ? 1 : 0;
   p.out = out; p.ldc = ldc; p.bias = bias; p.relu = relu; p.atomic = ksplit > 1 && !partial; p.out_bf16 = out_bf16; p.bias_bf16 = bias_bf16;
   p.partial_stride = partial ? (long)M * ldc : 0;

@@ -62,6 +62,7 @@ def lib():
             "dcp_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
             "dcp_gelu_fwd": [vp, vp, l, i, vp], "dcp_gelu_bwd": [vp, vp, vp, l, i, vp],
             "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
+            "dcp_conv_flat_pool_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, f, ull, ull, vp, i, i, vp],
             "dcp_conv_wgrad_flat_tc": [vp, vp, vp, l, i, i, i, vp],
             "dcp_convnet_conv1_fwd": [vp, vp, vp, vp, i, vp],
             "dcp_convnet_pool_fwd": [vp, vp, vp, i, f, ull, ull, vp, i, vp],

@@ -101,6 +101,7 @@ class FusedConvNetTrainer:
         self.wg_parts = min(148, -(-P // 128))
         self.wg_scratch = torch.empty(self.wg_parts * 64 * 289, **f32)
         self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
+        self.pool_fused = os.environ.get("DCP_POOL_FUSED", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
         self.off_bwd = (C.c_int * 9)(*[-((2 - r) * 26 + (2 - s)) for r in range(3) for s in range(3)])
         self.seed = int(torch.initial_seed() if seed is None else seed) & 0xFFFFFFFFFFFFFFFF
@@ -175,9 +176,15 @@ class FusedConvNetTrainer:
             ev_buf = torch.cuda.Event(); ev_buf.record(self.side)
         # ---- forward
         ck(L.dcp_convnet_conv1_fwd(self.x.data_ptr(), p["conv1.weight"].data_ptr(), p["conv1.bias"].data_ptr(), self.a1.data_ptr(), N, s()))
-        ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
-                              self.off_fwd, 26, 676, 24, 24, 0, 148, s()))
-        ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
+        if self.pool_fused:
+            # conv2 + bias + ReLU + 2x2 max-pool + channel dropout in one kernel: the 22 MB conv2 activation never reaches memory
+            ck(L.dcp_conv_flat_pool_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(),
+                                       p["conv2.bias"].data_ptr(), N * 676, 32, 64, 9, self.off_fwd, 26, 676, 24, 24, net.dropout1.p, self.seed, 1,
+                                       step_ptr, tr, 148, s()))
+        else:
+            ck(L.dcp_conv_flat_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.a2.data_ptr(), p["conv2.bias"].data_ptr(), None, N * 676, 32, 64, 9,
+                                  self.off_fwd, 26, 676, 24, 24, 0, 148, s()))
+            ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
         # the data-gradient's copy of conv2's filter (taps flipped, channels swapped) is taken here, while the filter is hot in L2:
         # conv2.weight may then be updated by the optimizer while the data-gradient is still running
         ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
@@ -413,8 +420,18 @@ class FusedConvNetTrainer:
             return None
         return self.be.all_reduce_async(self.buckets[idx], ReduceOp.AVG, max_ctas=self.comm_ctas)
 
-    def _capture(self) -> None:
+    def _capture(self, restore_state: bool = True) -> None:
+        """Warm up (optimizer state, pointer tables, allocator) and capture the step.  The warm-up and the capture itself EXECUTE
+        training steps on whatever the static input buffers hold; with ``restore_state`` the parameters, buffers and optimizer
+        state are put back afterwards, so building a trainer does not train (main.py --engine fused relies on it)."""
         dev = self.dev
+        opt, net = self.opt, self.net
+        snap = None
+        if restore_state:
+            snap = {"p": [q.detach().clone() for q in net.parameters()], "b": [b.detach().clone() for b in net.buffers()],
+                    "st": {q: {k: (v.detach().clone() if torch.is_tensor(v) else v) for k, v in st.items()} for q, st in opt.state.items()}}
+            cache = opt.__dict__.get("_dcp_cache") or {}
+            snap["hp6"] = {gi: ent["hp"][6].item() for gi, ent in cache.items()}
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
         with torch.cuda.stream(side):
@@ -428,6 +445,24 @@ class FusedConvNetTrainer:
             self._issue()
         self.launches_per_step = K.launch_count + (self.be.launches if self.be else 0) - before
         torch.cuda.synchronize(dev)
+        if snap is not None:
+            with torch.no_grad():
+                for q, v in zip(net.parameters(), snap["p"]):
+                    q.copy_(v)
+                for b, v in zip(net.buffers(), snap["b"]):
+                    b.copy_(v)
+                for q, st in opt.state.items():
+                    old = snap["st"].get(q)
+                    for k, v in st.items():
+                        if torch.is_tensor(v):
+                            v.copy_(old[k]) if old is not None and k in old else v.zero_()     # same tensors: the captured pointers stay valid
+                        elif k == "step":
+                            st[k] = old[k] if old is not None and k in old else 0
+                for gi, ent in (opt.__dict__.get("_dcp_cache") or {}).items():
+                    ent["hp"][6] = float(snap["hp6"].get(gi, 0.0))
+            if self.be is not None:
+                dist.barrier()
+            torch.cuda.synchronize(dev)
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """One optimisation step on batch (x, y); returns the (device, static) mean NLL loss of the batch."""

@@ -62,11 +62,22 @@ def test_gradients_and_update_match_cpu_reference(use_graph):
             assert p.grad.abs().max().item() < 1e-5
             continue
         assert _relerr(p.grad, ref_grads[n]) < 6e-2, (n, _relerr(p.grad, ref_grads[n]))
-    # the parameter update itself is covered by test_fused_optimizers_match_torch; here: it moved, and finitely
+    # the update: Adadelta's rule (torch/optim/adadelta.py) applied in fp64 to the gradients the kernels produced must give the
+    # parameters and the state the fused optimizer kernels left behind (first step: both accumulators start at zero)
+    lr, rho, eps = 0.5, 0.9, 1e-6
     for n, p in gpu.named_parameters():
-        assert torch.isfinite(p).all() and (n == "fc1.bias" or not torch.equal(p, before[n])), n
-    assert _relerr(gpu.batchnorm.running_mean, cpu.batchnorm.running_mean) < 5e-3 or use_graph
-    assert gpu.batchnorm.num_batches_tracked.item() >= 1
+        g = p.grad.double()
+        sq = (1 - rho) * g * g
+        delta = torch.sqrt(torch.full_like(g, eps)) / torch.sqrt(sq + eps) * g
+        exp_p = before[n].double() - lr * delta
+        assert torch.allclose(p.detach().double(), exp_p, rtol=1e-5, atol=1e-6), (n, (p.detach().double() - exp_p).abs().max().item())
+        st = opt.state[p]
+        assert torch.allclose(st["square_avg"].double(), sq, rtol=1e-5, atol=1e-12), n
+        assert torch.allclose(st["acc_delta"].double(), (1 - rho) * delta * delta, rtol=1e-4, atol=1e-12), n
+        assert torch.isfinite(p).all()
+    assert _relerr(gpu.batchnorm.running_mean, cpu.batchnorm.running_mean) < 5e-3
+    assert _relerr(gpu.batchnorm.running_var, cpu.batchnorm.running_var) < 5e-3
+    assert gpu.batchnorm.num_batches_tracked.item() == 1
 
 
 def test_training_reduces_loss_with_dropout_and_graph():
@@ -150,3 +161,35 @@ def test_split_optimizer_and_steplr_across_graph_replays():
         results.append({n: p.detach().clone() for n, p in net.named_parameters()})
     for n in results[0]:
         assert _relerr(results[1][n], results[0][n]) < 1e-5, (n, _relerr(results[1][n], results[0][n]))
+
+
+@pytest.mark.parametrize("N,training", [(32, 1), (128, 1), (64, 0)])
+def test_conv2_with_fused_pool_epilogue_matches_conv_then_pool(N, training):
+    """dcp_conv_flat_pool_tc (conv2 + bias + ReLU + 2x2 max-pool + channel dropout in the tcgen05 epilogue) against the two-kernel
+    path (dcp_conv_flat_tc then dcp_convnet_pool_fwd): same accumulators, same Philox stream -> identical pooled values and
+    argmax bytes; and both against a plain PyTorch fp32 conv / relu / max_pool2d of the same input (tf32 tolerance)."""
+    import ctypes as C
+    from distributed_compute_pytorch_b200.ops import cuda as K
+    L = K.lib()
+    dev = torch.device("cuda", 0)
+    g = torch.Generator(device=dev).manual_seed(N)
+    x = torch.randn(N, 26, 26, 32, device=dev, generator=g)                      # flat pixels [N*676, 32] (NHWC)
+    w = torch.randn(64, 3, 3, 32, device=dev, generator=g) * 0.1                 # [Cout][taps*Cin], tap-major
+    b = torch.randn(64, device=dev, generator=g) * 0.1
+    off = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
+    step = torch.full((), 3, dtype=torch.int64, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    a2 = torch.empty(N * 676, 64, device=dev)
+    p_ref = torch.full((N, 9216), float("nan"), device=dev); a_ref = torch.full((N * 9216,), 255, dtype=torch.uint8, device=dev)
+    p_new = torch.full((N, 9216), float("nan"), device=dev); a_new = torch.full((N * 9216,), 255, dtype=torch.uint8, device=dev)
+    assert L.dcp_conv_flat_tc(x.data_ptr(), w.data_ptr(), a2.data_ptr(), b.data_ptr(), None, N * 676, 32, 64, 9, off, 26, 676, 24, 24, 0, 148, st) == 0
+    assert L.dcp_convnet_pool_fwd(a2.data_ptr(), p_ref.data_ptr(), a_ref.data_ptr(), N, 0.25, 1234, 1, step.data_ptr(), training, st) == 0
+    rc = L.dcp_conv_flat_pool_tc(x.data_ptr(), w.data_ptr(), p_new.data_ptr(), a_new.data_ptr(), b.data_ptr(), N * 676, 32, 64, 9, off, 26, 676, 24, 24,
+                                 0.25, 1234, 1, step.data_ptr(), training, 148, st)
+    assert rc == 0, L.dcp_last_error()
+    torch.cuda.synchronize()
+    assert torch.equal(p_new, p_ref), (p_new - p_ref).abs().max().item()
+    assert torch.equal(a_new, a_ref)
+    if not training:
+        ref = torch.nn.functional.max_pool2d(torch.relu(torch.nn.functional.conv2d(x.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), b)), 2)
+        assert torch.allclose(p_new.view(N, 64, 12, 12), ref, rtol=2e-2, atol=2e-2)
