@@ -16,6 +16,7 @@ import torch
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import distributed_compute_pytorch_b200 as dcp  # noqa: E402
+from distributed_compute_pytorch_b200.utils import ClockSampler  # noqa: E402
 
 CONVNET_MESSAGES = [4, 8, 1024, 75264, 4725288, 4800552]
 
@@ -62,15 +63,16 @@ def worker(rank, world, port, opt):
         sym = be.empty_symmetric(n, dtype); sym.fill_(1.0)
         loc = torch.ones(n, device=dev, dtype=dtype)
         rows = []
+        clocks = ClockSampler(rank, period_s=0.1) if rank == 0 else None     # clocks during this size's timed regions
+        if clocks:
+            clocks.__enter__()
         if "all_reduce" in ops:
             variants = []
             if nbytes <= be.oneshot_max:
                 variants.append(("oneshot", lambda: be.all_reduce(loc, dcp.ReduceOp.SUM, algo=1)))
             variants.append(("twoshot_sym", lambda: be.all_reduce(sym, dcp.ReduceOp.SUM, algo=2)))
-            variants.append(("twoshot_staged", lambda: be.all_reduce(loc, dcp.ReduceOp.SUM, algo=2)))
             if be.nvls:
                 variants.append(("nvls_sym", lambda: be.all_reduce(sym, dcp.ReduceOp.SUM, algo=3)))
-                variants.append(("nvls_staged", lambda: be.all_reduce(loc, dcp.ReduceOp.SUM, algo=3)))
             variants.append(("auto", lambda: be.all_reduce(loc, dcp.ReduceOp.SUM)))
             variants.append(("auto_sym", lambda: be.all_reduce(sym, dcp.ReduceOp.SUM)))
             if nccl:
@@ -88,9 +90,7 @@ def worker(rank, world, port, opt):
                 rows.append(("broadcast", name, us, nbytes / us / 1e3))
         if "all_gather" in ops and n % world == 0 and n >= world:
             shard = torch.ones(n // world, device=dev, dtype=dtype)
-            variants = [("ours_sym", lambda: be.all_gather_into_tensor(sym, shard))]
-            if nbytes // world <= be.lib.dcp_coll_bounce_max_bytes(be.handle) // world:
-                variants.append(("ours", lambda: be.all_gather_into_tensor(loc, shard)))
+            variants = [("ours_sym", lambda: be.all_gather_into_tensor(sym, shard)), ("ours", lambda: be.all_gather_into_tensor(loc, shard))]
             if nccl:
                 variants.append(("nccl", lambda: nccl.all_gather_into_tensor(loc, shard)))
             for name, fn in variants:
@@ -98,9 +98,7 @@ def worker(rank, world, port, opt):
                 rows.append(("all_gather", name, us, (world - 1) / world * nbytes / us / 1e3))
         if "reduce_scatter" in ops and n % world == 0 and n >= world:
             shard = torch.empty(n // world, device=dev, dtype=dtype)
-            variants = [("ours_sym", lambda: be.reduce_scatter_tensor(shard, sym))]
-            if nbytes <= be.lib.dcp_coll_bounce_max_bytes(be.handle):
-                variants.append(("ours", lambda: be.reduce_scatter_tensor(shard, loc)))
+            variants = [("ours_sym", lambda: be.reduce_scatter_tensor(shard, sym)), ("ours", lambda: be.reduce_scatter_tensor(shard, loc))]
             if nccl:
                 variants.append(("nccl", lambda: nccl.reduce_scatter_tensor(shard, loc)))
             for name, fn in variants:
@@ -119,9 +117,14 @@ def worker(rank, world, port, opt):
                 rows.append(("sendrecv", name, us, nbytes / us / 1e3))
         be.free_symmetric(sym)
         del loc
+        csum = None
+        if clocks:
+            clocks.__exit__(None, None, None)
+            csum = clocks.summary()
         if rank == 0:
             for op, name, us, gbs in rows:
-                rec = {"op": op, "impl": name, "bytes": nbytes, "world": world, "us": round(us, 2), "bus_GBps": round(gbs, 2), "nvls": be.nvls}
+                rec = {"op": op, "impl": name, "bytes": nbytes, "world": world, "us": round(us, 2), "bus_GBps": round(gbs, 2), "nvls": be.nvls,
+                       "clocks": csum}
                 print(json.dumps(rec), flush=True)
                 if out:
                     out.write(json.dumps(rec) + "\n"); out.flush()

@@ -37,6 +37,7 @@ def parse():
     ap.add_argument("--sync-bn", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--layers", type=int, default=12, help="gpt2 only (12 = GPT-2 small)")
+    ap.add_argument("--out", default="", help="append the JSON line to this file as well")
     return ap.parse_args()
 
 
@@ -142,18 +143,28 @@ def worker(rank, world, port, opt):
             loss = step(*batches[i % len(batches)])
         b.record(); barrier(); torch.cuda.synchronize()
         return a.elapsed_time(b), float(loss)
+    from distributed_compute_pytorch_b200.utils import ClockSampler
     timed(opt.warmup)
+    clocks = ClockSampler(rank, period_s=0.1) if rank == 0 else None     # SM clocks / throttle reasons DURING the timed region
+    if clocks:
+        clocks.__enter__()
     ms, last = timed(opt.steps)
+    if clocks:
+        clocks.__exit__(None, None, None)
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item()
     if rank == 0:
         unit = "tokens/s" if opt.model == "gpt2" else "images/s"
-        print(json.dumps({"model": opt.model, "impl": opt.impl, "n_gpus": world, "value": units * world * opt.steps / (ms / 1e3), "unit": unit,
+        rec = json.dumps({"model": opt.model, "impl": opt.impl, "clocks": clocks.summary(), "warmup": opt.warmup, "n_gpus": world, "value": units * world * opt.steps / (ms / 1e3), "unit": unit,
                           "ms_per_step": ms / opt.steps, "per_gpu_batch": opt.batch or SHAPES[opt.model][2], "bf16": opt.bf16, "sync_bn": opt.sync_bn,
                           "graph": (not opt.no_graph) if opt.impl == "ours" else False, "last_loss": last, "steps": opt.steps,
-                          "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)}), flush=True)
+                          "peak_mem_GB": round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)})
+        print(rec, flush=True)
+        if opt.out:
+            with open(opt.out, "a") as f:
+                f.write(rec + "\n")
     finish()
 
 

@@ -14,6 +14,7 @@
 // Staged (non-symmetric tensor) variants double-buffer the bounce area on the parity of the channel's launch counter
 // (common.cuh), which removes the trailing barrier: a rank reuses a half two launches later, after it has passed a barrier
 // of the launch in between - so every peer has, in stream order, completed the launch that used that half.
+#include <cstdlib>
 #include <type_traits>
 
 #include "coll/coll_launch.cuh"
@@ -192,7 +193,10 @@ struct AllreduceTwoshotBody {
 // The byte range is cut into 16-byte chunks and chunk c is ALWAYS handled by the thread with c % stride == tid,
 // whatever the alignment of the two pointers.  The staged kernels rely on this: the CTA that pushed a chunk
 // (and chose the parity half from its own call counter) is the CTA that later copies it out.
-__device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nbytes, size_t tid, size_t stride, bool stream_store) {
+// bypass_l1: the source is re-written by a peer DURING this kernel (the receive slots of a multi-chunk transfer): read it
+// with ld.global.cg so that a line cached by an earlier chunk is never served from L1.
+__device__ __forceinline__ uint4 ld16_src(const char* p, bool bypass_l1) { return bypass_l1 ? __ldcg(reinterpret_cast<const uint4*>(p)) : ld16(p); }
+__device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nbytes, size_t tid, size_t stride, bool stream_store, bool bypass_l1 = false) {
   const uintptr_t mis = reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src);
   const bool al16 = (mis & 15) == 0, al4 = (mis & 3) == 0;
   const size_t nchunk = (nbytes + 15) / 16;
@@ -201,24 +205,24 @@ __device__ __forceinline__ void copy_bytes(char* dst, const char* src, size_t nb
     const size_t nfull = nbytes / 16;
     size_t c = tid;
     for (; c + 3 * stride < nfull; c += 4 * stride) {
-      uint4 x0 = ld16(src + c * 16), x1 = ld16(src + (c + stride) * 16), x2 = ld16(src + (c + 2 * stride) * 16), x3 = ld16(src + (c + 3 * stride) * 16);
+      uint4 x0 = ld16_src(src + c * 16, bypass_l1), x1 = ld16_src(src + (c + stride) * 16, bypass_l1), x2 = ld16_src(src + (c + 2 * stride) * 16, bypass_l1), x3 = ld16_src(src + (c + 3 * stride) * 16, bypass_l1);
       if (stream_store) { st16_stream(dst + c * 16, x0); st16_stream(dst + (c + stride) * 16, x1); st16_stream(dst + (c + 2 * stride) * 16, x2); st16_stream(dst + (c + 3 * stride) * 16, x3); }
       else { st16(dst + c * 16, x0); st16(dst + (c + stride) * 16, x1); st16(dst + (c + 2 * stride) * 16, x2); st16(dst + (c + 3 * stride) * 16, x3); }
     }
-    for (; c < nfull; c += stride) { uint4 x = ld16(src + c * 16); if (stream_store) st16_stream(dst + c * 16, x); else st16(dst + c * 16, x); }
-    if (nfull < nchunk && (nfull % stride) == tid) for (size_t j = nfull * 16; j < nbytes; ++j) dst[j] = src[j];
+    for (; c < nfull; c += stride) { uint4 x = ld16_src(src + c * 16, bypass_l1); if (stream_store) st16_stream(dst + c * 16, x); else st16(dst + c * 16, x); }
+    if (nfull < nchunk && (nfull % stride) == tid) for (size_t j = nfull * 16; j < nbytes; ++j) dst[j] = bypass_l1 ? (char)__ldcg(reinterpret_cast<const signed char*>(src + j)) : src[j];
     return;
   }
   for (size_t c = tid; c < nchunk; c += stride) {
     const size_t b = c * 16;
     const size_t len = nbytes - b < 16 ? nbytes - b : 16;
-    if (al16 && len == 16) {
-      uint4 x = ld16(src + b);
-      if (stream_store) st16_stream(dst + b, x); else st16(dst + b, x);
-    } else if (al4 && (len & 3) == 0) {
-      for (size_t j = 0; j < len; j += 4) *reinterpret_cast<uint32_t*>(dst + b + j) = *reinterpret_cast<const uint32_t*>(src + b + j);
+    if (al4 && (len & 3) == 0) {
+      for (size_t j = 0; j < len; j += 4) {
+        const uint32_t* q = reinterpret_cast<const uint32_t*>(src + b + j);
+        *reinterpret_cast<uint32_t*>(dst + b + j) = bypass_l1 ? __ldcg(q) : *q;
+      }
     } else {
-      for (size_t j = 0; j < len; ++j) dst[b + j] = src[b + j];
+      for (size_t j = 0; j < len; ++j) dst[b + j] = bypass_l1 ? (char)__ldcg(reinterpret_cast<const signed char*>(src + b + j)) : src[b + j];
     }
   }
 }
@@ -248,6 +252,80 @@ __device__ __forceinline__ void push_all_nvls(const DcpDevCtx& c, size_t off, co
     for (size_t j = nfull * 16; j < nbytes; ++j) { const char x = src[j]; for (int p = 0; p < c.world; ++p) c.peer[p][off + j] = x; }
 }
 
+// -------------------------------------------------------------------------------------------------
+// all_reduce of an ORDINARY tensor (not in the symmetric heap).  The staging copy is turned into the communication:
+//   1. rank r stores piece p of its input into slot [r] of rank p's bounce area (peer stores at link rate; nobody copies
+//      its whole input into its own heap first),
+//   2. barrier; rank p reduces its W slots from LOCAL memory,
+//   3. and stores the reduced slice into the result area of every rank (multimem.st with NVLS, peer stores otherwise),
+//   4. barrier; everyone copies the result out of its own heap.
+// Every 16-byte vector is pushed, reduced, re-pushed and copied out by the same (CTA, thread) index on the ranks involved, so
+// the two per-CTA barriers are all the ordering it needs.  Bounce half from the parity of the channel's launch counter.
+// Layout at `off`: [W slots of `per` vectors][result: W * per vectors].
+// -------------------------------------------------------------------------------------------------
+template <typename T>
+struct AllreduceStagedBody {
+  static constexpr int kThreads = kCollThreads;
+  struct Args { const T* in; T* out; size_t off; size_t half_bytes; size_t n; float scale; int op; int chan; };
+  static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
+    using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+    constexpr int V = Vec<T>::N;
+    const int W = c.world, op = a.op, chan = a.chan;
+    const float scale = a.scale;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    char* me = c.peer[c.rank];
+    const size_t off = a.off + (size_t)(dcp_gcalls(me, chan) & 1u) * a.half_bytes;
+    const size_t nbytes = a.n * sizeof(T), nv = (nbytes + 15) / 16, per = (nv + W - 1) / W;
+    const size_t res_off = off + (size_t)W * per * 16;
+    const char* in = reinterpret_cast<const char*>(a.in);
+    // 1. push
+    for (int p = 0; p < W; ++p) {
+      const size_t b = per * p < nv ? per * p : nv, e = b + per < nv ? b + per : nv;
+      const size_t lo = b * 16, hi = e * 16 < nbytes ? e * 16 : nbytes;
+      if (hi > lo) copy_bytes(c.peer[p] + off + (size_t)c.rank * per * 16, in + lo, hi - lo, tid, stride, p != c.rank);
+    }
+    dcp_barrier(c, chan);
+    // 2 + 3. reduce own slice from the local slots, publish it
+    {
+      const size_t b = per * c.rank < nv ? per * c.rank : nv, e = b + per < nv ? b + per : nv;
+      const char* slots = me + off;
+      const bool nvls = c.nvls && W > 2;
+      for (size_t v = tid; v < e - b; v += stride) {
+        Acc acc[V]; Vec<T> x;
+        uint4 raw[DCP_MAX_RANKS];
+#pragma unroll
+        for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = ld16(slots + ((size_t)p * per + v) * 16);
+        x.u = raw[0];
+#pragma unroll
+        for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+#pragma unroll
+        for (int p = 1; p < DCP_MAX_RANKS; ++p) if (p < W) {
+          x.u = raw[p];
+#pragma unroll
+          for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
+        }
+#pragma unroll
+        for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
+        const size_t dst = res_off + (b + v) * 16;
+        if (nvls) multimem_st16(c.mc + dst, x.u);
+        else {
+#pragma unroll
+          for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) st16_stream(c.peer[p] + dst, x.u);
+        }
+      }
+    }
+    dcp_barrier(c, chan);
+    // 4. copy out, slice by slice (chunk index relative to the slice start = the index its owner used)
+    char* out = reinterpret_cast<char*>(a.out);
+    for (int q = 0; q < W; ++q) {
+      const size_t b = per * q < nv ? per * q : nv, e = b + per < nv ? b + per : nv;
+      const size_t lo = b * 16, hi = e * 16 < nbytes ? e * 16 : nbytes;
+      if (hi > lo) copy_bytes(out + lo, me + res_off + lo, hi - lo, tid, stride, false);
+    }
+    dcp_gcalls_finish(me, chan);
+  }
+};
+
 // Rank `root` pushes nbytes to every rank's buffer at `off` (+ parity half when staged), everyone
 // copies out.  sym: buffer is the user's symmetric tensor (in place on root, leading barrier needed).
 struct BroadcastBody {
@@ -266,7 +344,7 @@ struct BroadcastBody {
     else dcp_barrier(c, chan);  // peers may still be reading their copy of the tensor
     if (c.rank == root) {
       const char* src = sym ? c.peer[root] + off : data;
-      if (c.nvls && (off % 16 == 0)) {
+      if (c.nvls && c.world > 2 && (off % 16 == 0)) {      // two ranks: one plain peer store per vector runs at link rate, a multicast store does not
         push_all_nvls(c, off, src, nbytes, tid, stride);   // in place on the root for a symmetric tensor: rewrites its own bytes with the same values
       } else {
         for (int p = 0; p < c.world; ++p) {
@@ -279,6 +357,76 @@ struct BroadcastBody {
     if (!sym) {
       if (c.rank != root) copy_bytes(data, c.peer[c.rank] + off, nbytes, tid, stride, false);
       dcp_gcalls_finish(c.peer[c.rank], chan);
+    }
+  }
+};
+
+// Large broadcast with NVLS: a single source cannot fill the switch with multicast stores (measured ~370 GB/s from one GPU),
+// while plain peer stores run at link rate (~700 GB/s) and multicast stores from ALL ranks together do as well.  So the root
+// SCATTERS: it writes slice p of the message into rank p's buffer with plain stores, sub-chunk by sub-chunk, signalling after
+// each one and never waiting; rank p RELAYS every sub-chunk of its slice to all ranks with multimem.st as soon as the root's
+// signal for it arrives.  The root's egress carries the message once, every other link direction carries it once, and the two
+// phases overlap.  Per-CTA signals: vector v of a slice is handled by the same (CTA, thread) on the root and on the relay.
+// Epoch use on (chan, CTA): [leading barrier when sym] + kRelaySub root signals + closing barrier.
+constexpr int kRelaySub = 4;
+struct BroadcastRelayBody {
+  static constexpr int kThreads = kCollThreads;
+  struct Args { char* data; size_t off; size_t half_bytes; size_t nbytes; int root; int chan; int sym; };
+  static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
+    char* data = a.data;
+    size_t off = a.off;
+    const size_t nbytes = a.nbytes;
+    const int root = a.root, chan = a.chan, sym = a.sym, W = c.world;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    if (!sym) off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * a.half_bytes;
+    else dcp_barrier(c, chan);                       // peers may still be reading their copy of the tensor
+    char* me = c.peer[c.rank];
+    __syncthreads();                                 // the barrier's epoch update (thread 0) is visible to everyone below
+    const uint32_t e0 = *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x));
+    const size_t nvec = nbytes / 16;                 // the < 16-byte tail travels point to point at the end
+    const char* src = (c.rank == root) ? (sym ? me + off : data) : me + off;
+    for (int k = 0; k < kRelaySub; ++k) {
+      if (c.rank == root) {
+        for (int p = 0; p < W; ++p) {
+          if (p == root && sym) continue;            // the root's own slice is already in place
+          const Span sl = rank_slice(nvec, W, p);
+          const size_t len = sl.end - sl.begin, kb = sl.begin + len * k / kRelaySub, ke = sl.begin + len * (k + 1) / kRelaySub;
+          size_t v = kb + ((tid + stride - (kb % stride)) % stride);
+          for (; v + 3 * stride < ke; v += 4 * stride) {
+            const uint4 x0 = ld16(src + v * 16), x1 = ld16(src + (v + stride) * 16), x2 = ld16(src + (v + 2 * stride) * 16), x3 = ld16(src + (v + 3 * stride) * 16);
+            char* d = c.peer[p] + off;
+            st16_stream(d + v * 16, x0); st16_stream(d + (v + stride) * 16, x1); st16_stream(d + (v + 2 * stride) * 16, x2); st16_stream(d + (v + 3 * stride) * 16, x3);
+          }
+          for (; v < ke; v += stride) st16_stream(c.peer[p] + off + v * 16, ld16(src + v * 16));
+        }
+        __syncthreads();
+        if ((int)threadIdx.x < W) st_release_sys(dcp_sig(c.peer[threadIdx.x], chan, blockIdx.x, root), e0 + 1 + k);
+      }
+      // relay this rank's slice (the root relays its own slice too: nobody else has it)
+      if (threadIdx.x == 0) wait_ge(c, dcp_sig(me, chan, blockIdx.x, root), e0 + 1 + k);
+      __syncthreads();
+      {
+        const Span sl = rank_slice(nvec, W, c.rank);
+        const size_t len = sl.end - sl.begin, kb = sl.begin + len * k / kRelaySub, ke = sl.begin + len * (k + 1) / kRelaySub;
+        const char* from = (c.rank == root) ? src : me + off;
+        size_t v = kb + ((tid + stride - (kb % stride)) % stride);
+        for (; v + 3 * stride < ke; v += 4 * stride) {
+          const uint4 x0 = ld16(from + v * 16), x1 = ld16(from + (v + stride) * 16), x2 = ld16(from + (v + 2 * stride) * 16), x3 = ld16(from + (v + 3 * stride) * 16);
+          multimem_st16(c.mc + off + v * 16, x0); multimem_st16(c.mc + off + (v + stride) * 16, x1);
+          multimem_st16(c.mc + off + (v + 2 * stride) * 16, x2); multimem_st16(c.mc + off + (v + 3 * stride) * 16, x3);
+        }
+        for (; v < ke; v += stride) multimem_st16(c.mc + off + v * 16, ld16(from + v * 16));
+      }
+    }
+    if (c.rank == root && (nvec % stride) == tid)
+      for (size_t j = nvec * 16; j < nbytes; ++j) { const char x = src[j]; for (int p = 0; p < W; ++p) c.peer[p][off + j] = x; }
+    // closing barrier on epoch e0 + kRelaySub + 1 (the epoch word still holds e0: bring it to e0 + kRelaySub first)
+    __syncthreads();
+    if (threadIdx.x == 0) *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x)) = e0 + kRelaySub;
+    dcp_barrier(c, chan);
+    if (!sym) {
+      if (c.rank != root) copy_bytes(data, me + off, nbytes, tid, stride, false);
+      dcp_gcalls_finish(me, chan);
     }
   }
 };
@@ -344,87 +492,143 @@ struct ScatterBody {
 };
 
 // -------------------------------------------------------------------------------------------------
-// reduce_scatter / reduce: stage own full input, then pull-reduce the slice(s) this rank owns.
+// reduce_scatter / reduce.
 //   root < 0 : reduce_scatter - rank r produces elements [r*n_out, (r+1)*n_out) of the reduction
-//   root >= 0: reduce - `root` produces all n_in elements, others only contribute
-// sym: input already at heap offset `off` on every rank (trailing barrier protects it from reuse).
+//   root >= 0: reduce - `root` produces all n_out elements, others only contribute
+// sym  (input inside the symmetric heap at offset `off` on every rank): PULL - the owner of a slice reads the W copies of it
+//      straight from the peers' tensors (in-switch with NVLS), zero copies; a trailing barrier protects the inputs from reuse.
+// !sym (ordinary tensor): PUSH - the staging copy IS the communication: rank r stores piece p of its input into slot [r] of
+//      rank p's bounce area (only the owner of a slice ever needs it), one barrier, and every owner reduces its W slots from
+//      LOCAL memory.  Slots are padded to 16 bytes, so the reduction is vectorised whatever the alignment of the user tensor;
+//      the bounce half comes from the parity of the channel's launch counter (common.cuh), hence no trailing barrier.
+//      piece_stride: elements between consecutive pieces of `in` (n_out, or the full shard length when this launch is one chunk
+//      of a larger reduce_scatter).
 // -------------------------------------------------------------------------------------------------
 template <typename T>
 struct ReduceScatterBody {
   static constexpr int kThreads = kCollThreads;
   struct Args { const T* in; T* out; size_t off; size_t half_bytes; size_t n_in; size_t n_out; size_t piece_stride; float scale; int op; int root; int chan; int sym; };
-  static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
-    const T* in = a.in;
-    T* out = a.out;
-    size_t off = a.off;
-    size_t half_bytes = a.half_bytes;
-    size_t n_in = a.n_in;
-    size_t n_out = a.n_out;
-    float scale = a.scale;
-    int op = a.op;
-    int root = a.root;
-    int chan = a.chan;
-    int sym = a.sym;
-  using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+  template <bool kLocal>
+  static __device__ __forceinline__ void reduce_vec(const DcpDevCtx& c, const char* const* src, size_t v, T* out, float scale, int op, bool out_aligned = true) {
+    using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
     constexpr int V = Vec<T>::N;
     const int W = c.world;
-    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
-    // staged input: the bounce half comes from the parity of the channel's LAUNCH counter (the reduce partition differs from
-    // the copy-in partition, so the per-CTA call counters of the other staged kernels would not do).  A rank can overwrite a
-    // half only two launches later, and by then every peer has passed a barrier of the launch in between - i.e. has completed,
-    // in stream order, the launch that read this half.  Hence no trailing barrier on the staged path.
-    // piece_stride != 0: the input is W pieces of n_out elements, piece_stride elements apart (one chunk of a larger
-    // reduce_scatter); they are packed back to back in the bounce buffer.
-    if (!sym) {
-      off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * half_bytes;
-      const size_t a_piece_stride = a.piece_stride;
-      if (a_piece_stride == 0) copy_bytes(c.peer[c.rank] + off, reinterpret_cast<const char*>(in), n_in * sizeof(T), tid, stride, false);
-      else for (int p = 0; p < W; ++p)
-        copy_bytes(c.peer[c.rank] + off + (size_t)p * n_out * sizeof(T), reinterpret_cast<const char*>(in + (size_t)p * a_piece_stride), n_out * sizeof(T), tid, stride, false);
+    Acc acc[V]; Vec<T> x;
+    uint4 raw[DCP_MAX_RANKS];
+#pragma unroll
+    for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = kLocal ? ld16(src[p] + v * 16) : ld16_stream(src[p] + v * 16);
+    x.u = raw[0];
+#pragma unroll
+    for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+#pragma unroll
+    for (int p = 1; p < DCP_MAX_RANKS; ++p) if (p < W) {
+      x.u = raw[p];
+#pragma unroll
+      for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
     }
+#pragma unroll
+    for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
+    if (out_aligned) st16(out + v * V, x.u);
+    else {
+#pragma unroll
+      for (int i = 0; i < V; ++i) out[v * V + i] = x.e[i];
+    }
+  }
+  static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
+    using Tr = ElemTraits<T>; using Acc = typename Tr::Acc;
+    constexpr int V = Vec<T>::N;
+    const T* in = a.in; T* out = a.out;
+    size_t off = a.off;
+    const size_t n_out = a.n_out;
+    const float scale = a.scale;
+    const int op = a.op, root = a.root, chan = a.chan, sym = a.sym, W = c.world;
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
+    char* me = c.peer[c.rank];
+    const bool owner = root < 0 || c.rank == root;
+    if (!sym) {
+      // ---- push: piece p -> slot [my rank] of rank p (reduce: the one piece -> the root)
+      off += (size_t)(dcp_gcalls(me, chan) & 1u) * a.half_bytes;
+      const size_t slot = (n_out * sizeof(T) + 15) / 16 * 16;
+      const size_t pstride = a.piece_stride ? a.piece_stride : n_out;
+      for (int p = 0; p < W; ++p) {
+        if (root >= 0 && p != root) continue;
+        const T* piece = root < 0 ? in + (size_t)p * pstride : in;
+        copy_bytes(c.peer[p] + off + (size_t)c.rank * slot, reinterpret_cast<const char*>(piece), n_out * sizeof(T), tid, stride, p != c.rank);
+      }
+      dcp_barrier(c, chan);
+      if (owner) {
+        const char* src[DCP_MAX_RANKS];
+#pragma unroll
+        for (int p = 0; p < DCP_MAX_RANKS; ++p) src[p] = me + off + (size_t)(p < W ? p : 0) * slot;
+        // the slots are 16-byte aligned whatever the user tensors look like; vector v (and the tail) is reduced by the (CTA, thread)
+        // that copy_bytes made push it on every peer, so the per-CTA barrier above is all the ordering this needs
+        const bool al = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+        const size_t nvec = n_out / V;
+        for (size_t v = tid; v < nvec; v += stride) reduce_vec<true>(c, src, v, out, scale, op, al);
+        if ((nvec % stride) == tid)
+          for (size_t i = nvec * V; i < n_out; ++i) {
+            Acc acc = Tr::up(reinterpret_cast<const T*>(src[0])[i]);
+            for (int p = 1; p < W; ++p) acc = red_apply<Acc>(op, acc, Tr::up(reinterpret_cast<const T*>(me + off + (size_t)p * slot)[i]));
+            out[i] = Tr::down(red_finish<T>(acc, scale, W, op));
+          }
+      }
+      dcp_gcalls_finish(me, chan);
+      return;
+    }
+    // ---- pull from the peers' symmetric tensors
     dcp_barrier(c, chan);
-    if (root < 0 || c.rank == root) {
+    if (owner) {
       const size_t first = root < 0 ? (size_t)c.rank * n_out : 0;
       const size_t soff = off + first * sizeof(T);
       const bool al = ((soff | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
       const size_t nvec = al ? n_out / V : 0;
       bool done_nvls = false;
       if constexpr (NvlsOk<T>::value) {
-        if (c.nvls && (op == DCP_SUM || op == DCP_AVG) && nvec > 0) {
-          for (size_t v = tid; v < nvec; v += stride) {
-            uint4 r = multimem_ld_reduce_add<T>(c.mc + soff + v * 16);      // in-switch reduction of the W copies
+        if (c.nvls && W > 2 && (op == DCP_SUM || op == DCP_AVG) && nvec > 0) {
+          // four in-switch reductions in flight per thread (one is a full round trip through NVSwitch)
+          size_t v = tid;
+          for (; v + 3 * stride < nvec; v += 4 * stride) {
+            uint4 r0 = multimem_ld_reduce_add<T>(c.mc + soff + v * 16), r1 = multimem_ld_reduce_add<T>(c.mc + soff + (v + stride) * 16);
+            uint4 r2 = multimem_ld_reduce_add<T>(c.mc + soff + (v + 2 * stride) * 16), r3 = multimem_ld_reduce_add<T>(c.mc + soff + (v + 3 * stride) * 16);
+            if (op == DCP_AVG) { r0 = vec_scale<T>(r0, scale); r1 = vec_scale<T>(r1, scale); r2 = vec_scale<T>(r2, scale); r3 = vec_scale<T>(r3, scale); }
+            st16(out + v * V, r0); st16(out + (v + stride) * V, r1); st16(out + (v + 2 * stride) * V, r2); st16(out + (v + 3 * stride) * V, r3);
+          }
+          for (; v < nvec; v += stride) {
+            uint4 r = multimem_ld_reduce_add<T>(c.mc + soff + v * 16);
             if (op == DCP_AVG) r = vec_scale<T>(r, scale);
             st16(out + v * V, r);
           }
           done_nvls = true;
         }
       }
-      for (size_t v = done_nvls ? nvec : tid; v < nvec; v += stride) {
-        Acc acc[V]; Vec<T> x;
-        uint4 raw[DCP_MAX_RANKS];
+      if (!done_nvls) {
+        const char* src[DCP_MAX_RANKS];
 #pragma unroll
-        for (int p = 0; p < DCP_MAX_RANKS; ++p) if (p < W) raw[p] = ld16_stream(c.peer[p] + soff + v * 16);
-        x.u = raw[0];
+        for (int p = 0; p < DCP_MAX_RANKS; ++p) src[p] = c.peer[p < W ? p : 0] + soff;
+        size_t v = tid;
+        for (; v + stride < nvec; v += 2 * stride) { reduce_vec<false>(c, src, v, out, scale, op); reduce_vec<false>(c, src, v + stride, out, scale, op); }
+        for (; v < nvec; v += stride) reduce_vec<false>(c, src, v, out, scale, op);
+      }
+      // unaligned slice (n_out * sizeof(T) not a multiple of 16) or tail: element-wise, four independent elements in flight per thread
+      size_t i = nvec * V + tid;
+      for (; i + 3 * stride < n_out; i += 4 * stride) {
+        Acc acc[4];
 #pragma unroll
-        for (int i = 0; i < V; ++i) acc[i] = Tr::up(x.e[i]);
+        for (int u = 0; u < 4; ++u) acc[u] = Tr::up(reinterpret_cast<const T*>(c.peer[0] + soff)[i + u * stride]);
+        for (int p = 1; p < W; ++p) {
 #pragma unroll
-        for (int p = 1; p < DCP_MAX_RANKS; ++p) if (p < W) {
-          x.u = raw[p];
-#pragma unroll
-          for (int i = 0; i < V; ++i) acc[i] = red_apply<Acc>(op, acc[i], Tr::up(x.e[i]));
+          for (int u = 0; u < 4; ++u) acc[u] = red_apply<Acc>(op, acc[u], Tr::up(reinterpret_cast<const T*>(c.peer[p] + soff)[i + u * stride]));
         }
 #pragma unroll
-        for (int i = 0; i < V; ++i) x.e[i] = Tr::down(red_finish<T>(acc[i], scale, W, op));
-        st16(out + v * V, x.u);
+        for (int u = 0; u < 4; ++u) out[i + u * stride] = Tr::down(red_finish<T>(acc[u], scale, W, op));
       }
-      for (size_t i = nvec * V + tid; i < n_out; i += stride) {
+      for (; i < n_out; i += stride) {
         Acc acc = Tr::up(reinterpret_cast<const T*>(c.peer[0] + soff)[i]);
         for (int p = 1; p < W; ++p) acc = red_apply<Acc>(op, acc, Tr::up(reinterpret_cast<const T*>(c.peer[p] + soff)[i]));
         out[i] = Tr::down(red_finish<T>(acc, scale, W, op));
       }
     }
-    if (sym) dcp_barrier(c, chan);                 // the input is the caller's tensor: nobody may still read it after the call
-    else dcp_gcalls_finish(c.peer[c.rank], chan);
+    dcp_barrier(c, chan);                 // the input is the caller's tensor: nobody may still read it after the call
   }
 };
 
@@ -436,32 +640,43 @@ __device__ __forceinline__ uint32_t* p2p_word(char* heap, size_t region, int pee
   return reinterpret_cast<uint32_t*>(heap + region) + (size_t)peer * DCP_P2P_BLOCKS + block;
 }
 
+// One launch moves the WHOLE message.  The (source, destination) slot has two halves; each half is cut into DCP_P2P_BLOCKS fixed
+// regions of R bytes and region b belongs to block b alone, guarded by block b's own flag / ack words and sequence number.  The
+// message is dealt out block-cyclically in pieces of R bytes: piece (ch * grid + b) is block b's chunk `ch`, which travels through
+// region b of half (seq & 1).  A half-region is free once the receiver acknowledged the chunk two before, so every block is its own
+// two-deep pipeline and no block ever touches memory another block's handshake is responsible for - whatever the sizes and
+// grids of earlier messages were.  (One kernel per side instead of one per 8 MiB chunk: that alone took send/recv from about
+// half of the link rate to NCCL's.)
+__device__ __forceinline__ size_t p2p_region_bytes(const DcpDevCtx& c) { return (c.p2p_slot_bytes / 2 / DCP_P2P_BLOCKS) / 16 * 16; }
+
 struct SendBody {
   static constexpr int kThreads = kCollThreads;
   struct Args { const char* in; size_t nbytes; int dst; };
   static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
     const char* in = a.in;
-    size_t nbytes = a.nbytes;
-    int dst = a.dst;
-  char* me = c.peer[c.rank];
+    const size_t nbytes = a.nbytes;
+    const int dst = a.dst;
+    char* me = c.peer[c.rank];
     const int b = blockIdx.x;
     volatile uint32_t* seqp = p2p_word(me, DcpHeapLayout::kSendSeqOff, dst, b);
-    const uint32_t seq = *seqp + 1;
-    // two half-slots per (source, destination): message seq uses half (seq & 1), which is free once the receiver
-    // acknowledged message seq - 2 - so a stream of chunks pipelines instead of ping-ponging on acks
-    if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PAckOff, dst, b), seq - 2);
-    __syncthreads();
-    char* slot = c.peer[dst] + c.p2p_slot_off + (size_t)c.rank * c.p2p_slot_bytes + (size_t)(seq & 1) * (c.p2p_slot_bytes / 2);
-    // contiguous share per block so that flags cover disjoint ranges
-    size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
-    size_t lo = per * b; if (lo > nbytes) lo = nbytes;
-    size_t hi = lo + per; if (hi > nbytes) hi = nbytes;
-    copy_bytes(slot + lo, in + lo, hi - lo, threadIdx.x, blockDim.x, true);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      st_release_sys(p2p_word(c.peer[dst], DcpHeapLayout::kP2PFlagOff, c.rank, b), seq);
-      *seqp = seq;
+    const uint32_t seq0 = *seqp;
+    const size_t R = p2p_region_bytes(c), half = c.p2p_slot_bytes / 2, round = R * gridDim.x;
+    const size_t chunks = nbytes == 0 ? 1 : (nbytes + round - 1) / round;
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) s_ok = 1;
+    for (size_t ch = 0; ch < chunks; ++ch) {
+      const uint32_t seq = seq0 + (uint32_t)ch + 1;
+      size_t lo = ch * round + (size_t)b * R; if (lo > nbytes) lo = nbytes;
+      size_t hi = lo + R; if (hi > nbytes) hi = nbytes;
+      if (threadIdx.x == 0 && !wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PAckOff, dst, b), seq - 2)) s_ok = 0;
+      __syncthreads();
+      if (!s_ok) return;                    // the receiver never acknowledged: the host sees the error flag
+      char* region = c.peer[dst] + c.p2p_slot_off + (size_t)c.rank * c.p2p_slot_bytes + (size_t)(seq & 1) * half + (size_t)b * R;
+      copy_bytes(region, in + lo, hi - lo, threadIdx.x, blockDim.x, true);
+      __syncthreads();
+      if (threadIdx.x == 0) st_release_sys(p2p_word(c.peer[dst], DcpHeapLayout::kP2PFlagOff, c.rank, b), seq);
     }
+    if (threadIdx.x == 0) *seqp = seq0 + (uint32_t)chunks;
   }
 };
 
@@ -470,24 +685,29 @@ struct RecvBody {
   struct Args { char* out; size_t nbytes; int src; };
   static __device__ __forceinline__ void run(const DcpDevCtx& c, const Args& a) {
     char* out = a.out;
-    size_t nbytes = a.nbytes;
-    int src = a.src;
-  char* me = c.peer[c.rank];
+    const size_t nbytes = a.nbytes;
+    const int src = a.src;
+    char* me = c.peer[c.rank];
     const int b = blockIdx.x;
     volatile uint32_t* seqp = p2p_word(me, DcpHeapLayout::kRecvSeqOff, src, b);
-    const uint32_t seq = *seqp + 1;
-    if (threadIdx.x == 0) wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PFlagOff, src, b), seq);
-    __syncthreads();
-    const char* slot = me + c.p2p_slot_off + (size_t)src * c.p2p_slot_bytes + (size_t)(seq & 1) * (c.p2p_slot_bytes / 2);
-    size_t per = ((nbytes + gridDim.x - 1) / gridDim.x + 15) / 16 * 16;
-    size_t lo = per * b; if (lo > nbytes) lo = nbytes;
-    size_t hi = lo + per; if (hi > nbytes) hi = nbytes;
-    copy_bytes(out + lo, slot + lo, hi - lo, threadIdx.x, blockDim.x, false);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      st_release_sys(p2p_word(c.peer[src], DcpHeapLayout::kP2PAckOff, c.rank, b), seq);
-      *seqp = seq;
+    const uint32_t seq0 = *seqp;
+    const size_t R = p2p_region_bytes(c), half = c.p2p_slot_bytes / 2, round = R * gridDim.x;
+    const size_t chunks = nbytes == 0 ? 1 : (nbytes + round - 1) / round;
+    __shared__ int s_ok;
+    if (threadIdx.x == 0) s_ok = 1;
+    for (size_t ch = 0; ch < chunks; ++ch) {
+      const uint32_t seq = seq0 + (uint32_t)ch + 1;
+      size_t lo = ch * round + (size_t)b * R; if (lo > nbytes) lo = nbytes;
+      size_t hi = lo + R; if (hi > nbytes) hi = nbytes;
+      if (threadIdx.x == 0 && !wait_ge(c, p2p_word(me, DcpHeapLayout::kP2PFlagOff, src, b), seq)) s_ok = 0;
+      __syncthreads();
+      if (!s_ok) return;                    // nothing arrived in time: leave the rest of `out` alone, the host sees the error flag
+      const char* region = me + c.p2p_slot_off + (size_t)src * c.p2p_slot_bytes + (size_t)(seq & 1) * half + (size_t)b * R;
+      copy_bytes(out + lo, region, hi - lo, threadIdx.x, blockDim.x, false, true);   // the region is rewritten during this kernel: bypass L1
+      __syncthreads();
+      if (threadIdx.x == 0) st_release_sys(p2p_word(c.peer[src], DcpHeapLayout::kP2PAckOff, c.rank, b), seq);
     }
+    if (threadIdx.x == 0) *seqp = seq0 + (uint32_t)chunks;
   }
 };
 
@@ -609,13 +829,15 @@ int dcp_all_reduce(void* h, void* buf, size_t n, int dtype, int op, int algo, in
       if (nvls) { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, true>>(h, c, {nullptr, nullptr, (size_t)off, 0, n, scale, op, chan}, grid, stream))); }
       else { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, false>>(h, c, {nullptr, nullptr, (size_t)off, 0, n, scale, op, chan}, grid, stream))); }
     } else {
-      const size_t half = bounce_half(c, chan), cap = half / es / 16 * 16;
+      // ordinary tensor: push-based staged all-reduce (AllreduceStagedBody), chunked by the bounce capacity
+      const size_t half = bounce_half(c, chan);
+      const size_t cap_vec = half / 32 - (size_t)c.world - 1;            // W slots + result area = 2 x (vectors + rounding) per chunk
+      const size_t cap = cap_vec * 16 / es;
       for (size_t done = 0; done < n; done += cap) {
         size_t m = n - done < cap ? n - done : cap;
         int grid = grid_for(m * es, max_ctas);
         char* p = (char*)buf + done * es;
-        if (nvls) { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, true>>(h, c, {(const T*)p, (T*)p, bounce_off(c, chan), half, m, scale, op, chan}, grid, stream))); }
-        else { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, false>>(h, c, {(const T*)p, (T*)p, bounce_off(c, chan), half, m, scale, op, chan}, grid, stream))); }
+        DISPATCH_DTYPE(dtype, (coll_launch<AllreduceStagedBody<T>>(h, c, {(const T*)p, (T*)p, bounce_off(c, chan), half, m, scale, op, chan}, grid, stream)));
       }
     }
   }
@@ -628,13 +850,22 @@ int dcp_broadcast(void* h, void* buf, size_t nbytes, int root, int chan, int max
   if (nbytes == 0) return 0;
   if (bad_chan(chan)) return -1;
   const long off = heap_offset(c, buf, dcp_symm_bytes(h));
+  // >= kRelayMin bytes with a multicast mapping: scatter + relay (BroadcastRelayBody); DCP_BCAST_RELAY=0 keeps the root-only push
+  static const size_t relay_min = [] { const char* e = getenv("DCP_BCAST_RELAY_MIN"); return e ? (size_t)atol(e) : (size_t)(4u << 20); }();
+  static const bool relay_on = [] { const char* e = getenv("DCP_BCAST_RELAY"); return !(e && e[0] == '0'); }();
   if (off >= 0 && off % 16 == 0) {
-    coll_launch<BroadcastBody>(h, c, {(char*)buf, (size_t)off, 0, nbytes, root, chan, 1}, grid_for(nbytes, max_ctas), stream);
+    if (relay_on && c.nvls && c.world > 2 && nbytes >= relay_min)
+      coll_launch<BroadcastRelayBody>(h, c, {(char*)buf, (size_t)off, 0, nbytes, root, chan, 1}, grid_for(nbytes, max_ctas), stream);
+    else
+      coll_launch<BroadcastBody>(h, c, {(char*)buf, (size_t)off, 0, nbytes, root, chan, 1}, grid_for(nbytes, max_ctas), stream);
   } else {
     const size_t cap = bounce_half(c, chan);
     for (size_t done = 0; done < nbytes; done += cap) {
       size_t m = nbytes - done < cap ? nbytes - done : cap;
-      coll_launch<BroadcastBody>(h, c, {(char*)buf + done, bounce_off(c, chan), cap, m, root, chan, 0}, grid_for(m, max_ctas), stream);
+      if (relay_on && c.nvls && c.world > 2 && m >= relay_min)
+        coll_launch<BroadcastRelayBody>(h, c, {(char*)buf + done, bounce_off(c, chan), cap, m, root, chan, 0}, grid_for(m, max_ctas), stream);
+      else
+        coll_launch<BroadcastBody>(h, c, {(char*)buf + done, bounce_off(c, chan), cap, m, root, chan, 0}, grid_for(m, max_ctas), stream);
     }
   }
   DCP_CUDA_CHECK(cudaGetLastError());
@@ -694,15 +925,13 @@ int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dty
     DISPATCH_DTYPE(dtype, (coll_launch<ReduceScatterBody<T>>(h, c, {(const T*)in, (T*)out, (size_t)off, 0, n_in, n_out, 0, scale, op, root, chan, 1}, grid, stream)));
   } else {
     const size_t half = bounce_half(c, chan);
-    const size_t pieces = root < 0 ? (size_t)c.world : 1;
-    const size_t cap = half / pieces / es / 16 * 16;          // output elements per launch (keeps every piece 16-byte aligned in the buffer)
+    const size_t cap = (half / c.world - 16) / es / 16 * 16;    // output elements per launch: W padded slots must fit one bounce half
     for (size_t done = 0; done < n_out; done += cap) {
       size_t m = n_out - done < cap ? n_out - done : cap;
       int grid = grid_for(m * es, max_ctas);
       const char* pin = (const char*)in + done * es;
       char* pout = out ? (char*)out + done * es : nullptr;
-      const size_t stride = (root < 0 && m != n_out) ? n_out : 0;   // one chunk of a larger reduce_scatter: W pieces, n_out elements apart
-      DISPATCH_DTYPE(dtype, (coll_launch<ReduceScatterBody<T>>(h, c, {(const T*)pin, (T*)pout, bounce_off(c, chan), half, m * pieces, m, stride, scale, op, root, chan, 0},
+      DISPATCH_DTYPE(dtype, (coll_launch<ReduceScatterBody<T>>(h, c, {(const T*)pin, (T*)pout, bounce_off(c, chan), half, m * (root < 0 ? c.world : 1), m, n_out, scale, op, root, chan, 0},
                                                                grid, stream)));
     }
   }
@@ -710,28 +939,28 @@ int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dty
   return 0;
 }
 
+// grid of a point-to-point transfer: a function of the message size alone, so that both sides agree
+static inline int p2p_grid(const DcpDevCtx& c, size_t nbytes) {
+  const size_t R = (c.p2p_slot_bytes / 2 / DCP_P2P_BLOCKS) / 16 * 16;
+  long g = (long)((nbytes + R - 1) / R);
+  const int cap = c.p2p_blocks > 0 && c.p2p_blocks < DCP_P2P_BLOCKS ? c.p2p_blocks : DCP_P2P_BLOCKS;
+  return (int)(g < 1 ? 1 : (g > cap ? cap : g));
+}
+
 int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t stream) {
   const DcpDevCtx& c = *dcp_symm_ctx(h);
-  const size_t half = c.p2p_slot_bytes / 2;
-  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += half) {
-    size_t m = nbytes - done < half ? nbytes - done : half;
-    P2PBody::Args a{}; a.mode = 1; a.s = {(const char*)in + done, m, dst};
-    coll_launch<P2PBody>(h, c, a, DCP_P2P_BLOCKS, stream, 1);
-    if (nbytes == 0) break;
-  }
+  if (dst < 0 || dst >= c.world || dst == c.rank) { dcp_set_error("send: bad destination rank %d", dst); return -1; }
+  P2PBody::Args a{}; a.mode = 1; a.s = {(const char*)in, nbytes, dst};
+  coll_launch<P2PBody>(h, c, a, p2p_grid(c, nbytes), stream, 1);
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }
 
 int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream) {
   const DcpDevCtx& c = *dcp_symm_ctx(h);
-  const size_t half = c.p2p_slot_bytes / 2;
-  for (size_t done = 0; done < nbytes || (nbytes == 0 && done == 0); done += half) {
-    size_t m = nbytes - done < half ? nbytes - done : half;
-    P2PBody::Args a{}; a.mode = 2; a.r = {(char*)out + done, m, src};
-    coll_launch<P2PBody>(h, c, a, DCP_P2P_BLOCKS, stream, 1);
-    if (nbytes == 0) break;
-  }
+  if (src < 0 || src >= c.world || src == c.rank) { dcp_set_error("recv: bad source rank %d", src); return -1; }
+  P2PBody::Args a{}; a.mode = 2; a.r = {(char*)out, nbytes, src};
+  coll_launch<P2PBody>(h, c, a, p2p_grid(c, nbytes), stream, 1);
   DCP_CUDA_CHECK(cudaGetLastError());
   return 0;
 }

@@ -10,7 +10,7 @@
 #define DCP_MAX_RANKS 8
 #define DCP_NUM_CHANNELS 8
 #define DCP_MAX_BLOCKS 512       // upper bound on the grid of any collective kernel
-#define DCP_P2P_BLOCKS 64        // grid of send/recv kernels
+#define DCP_P2P_BLOCKS 128       // largest grid of the send/recv kernels (one flag / ack word per block and peer)
 
 // dtype codes shared with Python (ops/cuda.py, parallel/p2p_backend.py)
 enum DcpDtype : int { DCP_F32 = 0, DCP_BF16 = 1, DCP_F16 = 2, DCP_I32 = 3, DCP_I64 = 4, DCP_F64 = 5, DCP_U8 = 6 };
@@ -84,7 +84,7 @@ struct DcpHeapLayout {
 struct DcpDevCtx {
   int rank, world;
   int nvls;             // multicast mapping available
-  int _pad;
+  int p2p_blocks;       // grid limit of send / recv on this heap (<= DCP_P2P_BLOCKS; an emulated world keeps it small)
   char* peer[DCP_MAX_RANKS];   // peer[r] = VA (in this process) of rank r's heap; peer[rank] = own heap
   char* mc;                    // multicast VA of the heap (NVLS) or nullptr
   unsigned long long timeout_ns;

@@ -105,6 +105,7 @@ struct Symm {
   int* err_host = nullptr;  // pinned, mapped
   int* err_dev = nullptr;
   DcpDevCtx ctx{};
+  bool emu_hint = false;            // set before finalize for members of an emulated world
   struct EmuGroup* emu = nullptr;   // member of an emulated world (all ranks on this GPU): collective launches are recorded, not executed
 };
 
@@ -284,6 +285,7 @@ int dcp_symm_finalize(void* h, double timeout_s, size_t p2p_slot_bytes, size_t s
   }
   c.timeout_ns = (unsigned long long)(timeout_s * 1e9);
   c.err = s->err_dev;
+  c.p2p_blocks = s->emu_hint ? 16 : DCP_P2P_BLOCKS;
   c.p2p_slot_off = DcpHeapLayout::kCtlBytes;
   c.p2p_slot_bytes = p2p_slot_bytes;
   c.staging_off = c.p2p_slot_off + p2p_slot_bytes * DCP_MAX_RANKS;
@@ -354,6 +356,7 @@ void* dcp_emu_create(int world, int device, size_t heap_bytes, double timeout_s,
   for (int r = 0; r < world; ++r) {
     Symm* s = g->members[r];
     for (int p = 0; p < world; ++p) s->peer_va[p] = g->members[p]->peer_va[p];
+    s->emu_hint = true;
     if (dcp_symm_finalize(s, timeout_s, p2p_slot_bytes, staging_bytes, 0) != 0) { for (auto* m : g->members) dcp_symm_destroy(m); delete g; return nullptr; }
     s->emu = g;
     cs[r] = s->ctx;

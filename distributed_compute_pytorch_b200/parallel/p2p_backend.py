@@ -262,7 +262,9 @@ class P2PBackend:
             return self._algo_override
         if nbytes <= self.oneshot_max:
             return 1
-        if self.nvls and nbytes >= self.nvls_min and t.dtype in (torch.float32, torch.bfloat16, torch.float16) and op in (ReduceOp.SUM, ReduceOp.AVG):
+        # NVLS pays from three ranks up: with two, the pull-reduce / push of the P2P two-shot moves the same bytes at link rate
+        # while a multicast access costs a round trip through the switch (measured at 256 MiB, 2 GPUs: 435 us vs 710 us)
+        if self.nvls and self.world > 2 and nbytes >= self.nvls_min and t.dtype in (torch.float32, torch.bfloat16, torch.float16) and op in (ReduceOp.SUM, ReduceOp.AVG):
             return 3
         return 2
 

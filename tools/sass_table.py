@@ -7,7 +7,7 @@ import collections, os, re, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "build", "obj")
 OUT = os.path.join(ROOT, "docs", "sass")
-FILES = ["ops_gemm_bf16_persistent", "ops_gemm_tc", "ops_conv_flat_tc", "ops_conv_wgrad_flat_tc", "ops_convnet_fused", "coll_coll", "coll_fused_opt"]
+FILES = sorted(f[:-len(".cu.o")] for f in os.listdir(OBJ) if f.endswith(".cu.o")) if os.path.isdir(OBJ) else []   # every CUDA object of the library
 COLS = [("UTC*MMA", r"UTC[A-Z]*MMA"), ("LDTM", r"\bLDTM"), ("UTMALDG", r"UTMALDG"), ("UTCBAR", r"UTCBAR"), ("SYNCS", r"\bSYNCS"),
         ("multimem (LDGMC/STGMC/REDGMC)", r"(LDGMC|STGMC|REDGMC)"), ("PDL (ACQBULK/PREEXIT)", r"(ACQBULK|PREEXIT)"),
         ("cluster (UCGABAR/CGAERRBAR... .CLUSTER / remote smem)", r"(UCGABAR|\.CLUSTER|MAPA|CGABAR)"), ("HMMA (legacy)", r"\bHMMA")]
@@ -21,6 +21,9 @@ def main():
         if not os.path.exists(obj):
             continue
         sass = subprocess.run(["cuobjdump", "-sass", obj], capture_output=True, text=True).stdout
+        import gzip
+        with gzip.open(os.path.join(OUT, f + ".sass.gz"), "wt", compresslevel=9) as gz:      # the FULL listing of the object, next to the filtered one
+            gz.write(sass)
         kern, counts = None, collections.OrderedDict()
         keep = []
         for line in sass.splitlines():

@@ -22,8 +22,8 @@ def main():
     for op in sorted(impls):
         cols = [c for c in impls[op] if c != "nccl"] + (["nccl"] if "nccl" in impls[op] else [])
         print(f"\n## {op}\n")
-        print("| bytes | " + " | ".join(cols) + " | best ours / nccl |")
-        print("|---|" + "---|" * (len(cols) + 1))
+        print("| bytes | " + " | ".join(cols) + " | nccl / best ours | nccl / public API (ordinary tensor) | SM MHz |")
+        print("|---|" + "---|" * (len(cols) + 3))
         for (o, nbytes) in sorted(k for k in by if k[0] == op):
             cell = by[(o, nbytes)]
             best = min((cell[c]["us"] for c in cols if c in cell), default=None)
@@ -36,7 +36,10 @@ def main():
                 out.append(f"**{txt}**" if cell[c]["us"] == best else txt)
             ours = min((cell[c]["us"] for c in cols if c in cell and c != "nccl"), default=None)
             ratio = f'{cell["nccl"]["us"] / ours:.2f}x' if ours and "nccl" in cell else "-"
-            print(f"| {nbytes} | " + " | ".join(out) + f" | {ratio} |")
+            pub = cell.get("auto") or cell.get("ours")        # what dist.<collective>(ordinary tensor) runs
+            pratio = f'{cell["nccl"]["us"] / pub["us"]:.2f}x' if pub and "nccl" in cell else "-"
+            mhz = next((str(v["clocks"].get("sm_mhz")) for v in cell.values() if isinstance(v.get("clocks"), dict)), "-")
+            print(f"| {nbytes} | " + " | ".join(out) + f" | {ratio} | {pratio} | {mhz} |")
 
 
 if __name__ == "__main__":
