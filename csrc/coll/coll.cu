@@ -368,7 +368,7 @@ struct BroadcastBody {
 // signal for it arrives.  The root's egress carries the message once, every other link direction carries it once, and the two
 // phases overlap.  Per-CTA signals: vector v of a slice is handled by the same (CTA, thread) on the root and on the relay.
 // Epoch use on (chan, CTA): [leading barrier when sym] + kRelaySub root signals + closing barrier.
-constexpr int kRelaySub = 4;
+constexpr int kRelaySub = 16;
 struct BroadcastRelayBody {
   static constexpr int kThreads = kCollThreads;
   struct Args { char* data; size_t off; size_t half_bytes; size_t nbytes; int root; int chan; int sym; };
@@ -829,8 +829,21 @@ int dcp_all_reduce(void* h, void* buf, size_t n, int dtype, int op, int algo, in
       if (nvls) { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, true>>(h, c, {nullptr, nullptr, (size_t)off, 0, n, scale, op, chan}, grid, stream))); }
       else { DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, false>>(h, c, {nullptr, nullptr, (size_t)off, 0, n, scale, op, chan}, grid, stream))); }
     } else {
-      // ordinary tensor: push-based staged all-reduce (AllreduceStagedBody), chunked by the bounce capacity
+      // ordinary tensor, chunked by the bounce capacity.  With a multicast mapping and more than two ranks: copy into the bounce
+      // area, in-switch two-shot there, copy out (measured on 8 GPUs: 928 us at 256 MiB against 1304 us for the push variant,
+      // whose W - 1 peer-store streams per rank fall short of the NVLS rate).  Otherwise: the push-based body.
       const size_t half = bounce_half(c, chan);
+      if (c.nvls && c.world > 2 && (dtype == DCP_F32 || dtype == DCP_BF16 || dtype == DCP_F16) && (op == DCP_SUM || op == DCP_AVG) && algo != 2) {
+        const size_t cap2 = half / es / 16 * 16;
+        for (size_t done = 0; done < n; done += cap2) {
+          size_t m = n - done < cap2 ? n - done : cap2;
+          int grid = grid_for(m * es, max_ctas);
+          char* p = (char*)buf + done * es;
+          DISPATCH_DTYPE(dtype, (coll_launch<AllreduceTwoshotBody<T, true>>(h, c, {(const T*)p, (T*)p, bounce_off(c, chan), half, m, scale, op, chan}, grid, stream)));
+        }
+        DCP_CUDA_CHECK(cudaGetLastError());
+        return 0;
+      }
       const size_t cap_vec = half / 32 - (size_t)c.world - 1;            // W slots + result area = 2 x (vectors + rounding) per chunk
       const size_t cap = cap_vec * 16 / es;
       for (size_t done = 0; done < n; done += cap) {
@@ -850,8 +863,9 @@ int dcp_broadcast(void* h, void* buf, size_t nbytes, int root, int chan, int max
   if (nbytes == 0) return 0;
   if (bad_chan(chan)) return -1;
   const long off = heap_offset(c, buf, dcp_symm_bytes(h));
-  // >= kRelayMin bytes with a multicast mapping: scatter + relay (BroadcastRelayBody); DCP_BCAST_RELAY=0 keeps the root-only push
-  static const size_t relay_min = [] { const char* e = getenv("DCP_BCAST_RELAY_MIN"); return e ? (size_t)atol(e) : (size_t)(4u << 20); }();
+  // >= 64 MiB (DCP_BCAST_RELAY_MIN) with a multicast mapping: scatter + relay (BroadcastRelayBody) - measured on 8 GPUs it loses to the
+  // root-only multicast push below that (its 16 signalled sub-chunks cost more than they overlap); DCP_BCAST_RELAY=0 turns it off
+  static const size_t relay_min = [] { const char* e = getenv("DCP_BCAST_RELAY_MIN"); return e ? (size_t)atol(e) : (size_t)(64u << 20); }();
   static const bool relay_on = [] { const char* e = getenv("DCP_BCAST_RELAY"); return !(e && e[0] == '0'); }();
   if (off >= 0 && off % 16 == 0) {
     if (relay_on && c.nvls && c.world > 2 && nbytes >= relay_min)
