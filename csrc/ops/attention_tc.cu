@@ -242,3 +242,25 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
 }
 
 }  // namespace
+
+extern "C" {
+
+// Causal self-attention forward for head dimension 64.  qkv: bf16 [B*T, 3*H*64] (the fused projection: q | k | v, heads inside
+// each third); out: bf16 [B*T, H*64]; lse: fp32 [B*H, T], log2-domain log-sum-exp of the scaled scores (consumed by
+// dcp_attn_bwd).  T must be a multiple of 128.  softmax scale = 1/sqrt(64).
+int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cudaStream_t s) {
+  if (T % kBQ != 0 || B < 1 || H < 1) { dcp_set_error("attention: T=%d must be a multiple of %d", T, kBQ); return -1; }
+  const int C = H * kD;
+  CUtensorMap map;
+  if (encode_bf16_2d(&map, qkv, (long)B * T, 3L * C, 3L * C, kD, kBQ)) return -1;
+  AttnFwdParams p{};
+  p.T = T; p.H = H; p.C = C; p.scale_log2 = 0.125f * 1.4426950408889634f;
+  p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
+  const size_t smem = (size_t)kTileBytes * (1 + kRing + 2) + sizeof(AttnBars) + 1024;
+  static bool attr = false;
+  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_fwd, dim3(T / kBQ, B * H), dim3(kAttnThreads), smem, s, map, p));
+  return 0;
+}
+
+}  // extern "C"
