@@ -53,6 +53,7 @@ def worker(rank, world, port, opt):
         tdist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port + 1}", rank=rank, world_size=world, device_id=dev)
         nccl = tdist
     sizes = sorted(set([1 << k for k in range(10, 31) if (1 << k) <= opt.max_mb << 20] + CONVNET_MESSAGES))
+    sizes = [b for b in sizes if b >= opt.min_kb << 10]
     ops = opt.ops.split(",")
     out = open(opt.out, "a") if rank == 0 and opt.out else None
     dtype = torch.float32
@@ -137,6 +138,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=2)
     ap.add_argument("--max-mb", type=int, default=1024)
+    ap.add_argument("--min-kb", type=int, default=0, help="skip messages below this size")
     ap.add_argument("--ops", default="all_reduce,broadcast,all_gather,reduce_scatter,sendrecv")
     ap.add_argument("--out", default="")
     ap.add_argument("--no-nccl", action="store_true")

@@ -451,7 +451,7 @@ struct AllgatherBody {
     if (!sym) off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * half_bytes;
     else dcp_barrier(c, chan);
     const size_t my = off + (size_t)c.rank * slot_stride;
-    if (c.nvls && root < 0 && (my % 16 == 0)) {
+    if (c.nvls && c.world > 2 && root < 0 && (my % 16 == 0)) {   // two ranks: one plain peer store per vector is the faster path
       push_all_nvls(c, my, in, nbytes, tid, stride);        // one store per 16 bytes instead of W: egress drops W-fold
     } else {
       for (int p = 0; p < c.world; ++p) {

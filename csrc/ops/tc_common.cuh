@@ -161,6 +161,12 @@ inline int encode_bf16_2d(CUtensorMap* m, const void* base, long rows, long cols
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // first call of this library on the thread (its runtime is linked statically): bind the primary context, then encode again
+    cudaFree(0);
+    r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) { dcp_set_error("cuTensorMapEncodeTiled(bf16 rows=%ld cols=%ld ld=%ld box=%dx%d) failed: %d", rows, cols, ld, box_cols, box_rows, (int)r); return -1; }
   return 0;
 }

@@ -1,10 +1,11 @@
 """GPT-2 small (north-star config ``BASELINE.json:configs[4]``: DDP bf16, seq 1024, large gradient
 buckets fused with the optimizer step; not part of the reference).  124,439,808 parameters with the
-LM head tied to the token embedding.  Linear layers run the tcgen05 GEMM; attention uses the
-library SDPA kernel (attention is not among the north-star's hand-written ops)."""
+LM head tied to the token embedding.  Linear layers run the tcgen05 GEMM; attention is the tcgen05 flash-attention kernel
+of csrc/ops/attention_tc.cu for bf16 / head dim 64 / T % 128 == 0 (the library SDPA call otherwise, and in the stock arm)."""
 from __future__ import annotations
 
 import math
+import os
 from dataclasses import dataclass
 
 import torch
@@ -12,6 +13,11 @@ import torch.nn.functional as F
 from torch import nn
 
 from .. import ops
+
+
+def cuda_ops():
+    from ..ops import cuda
+    return cuda
 
 
 @dataclass
@@ -64,9 +70,14 @@ class Block(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B, T, C = x.shape
-        q, k, v = _SplitHeads.apply(self.attn_qkv(self.ln_1(x).view(B * T, C)), B, T, self.n_head)
-        y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
-        y = y.transpose(1, 2).reshape(B * T, C)
+        qkv = self.attn_qkv(self.ln_1(x).view(B * T, C))
+        if ops.layers.use_kernels(qkv) and os.environ.get("DCP_ATTENTION", "1") == "1" and cuda_ops().causal_attention_supported(qkv, T, self.n_head):
+            # flash attention on tcgen05, reading q / k / v in place and returning the heads merged (csrc/ops/attention_tc.cu)
+            y = cuda_ops().causal_attention(qkv, B, T, self.n_head)
+        else:
+            q, k, v = _SplitHeads.apply(qkv, B, T, self.n_head)
+            y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+            y = y.transpose(1, 2).reshape(B * T, C)
         x = x + self.attn_proj(y).view(B, T, C)
         h = self.act(self.mlp_fc(self.ln_2(x).view(B * T, C)))
         return x + self.mlp_proj(h).view(B, T, C)

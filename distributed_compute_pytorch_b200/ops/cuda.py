@@ -62,6 +62,8 @@ def lib():
             "dcp_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
             "dcp_gelu_fwd": [vp, vp, l, i, vp], "dcp_gelu_bwd": [vp, vp, vp, l, i, vp],
             "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
+            "dcp_attn_fwd": [vp, vp, vp, i, i, i, vp],
+            "dcp_attn_bwd": [vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
             "dcp_conv_flat_pool_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, f, ull, ull, vp, i, i, vp],
             "dcp_conv_wgrad_flat_tc": [vp, vp, vp, l, i, i, i, vp],
             "dcp_convnet_conv1_fwd": [vp, vp, vp, vp, i, vp],
@@ -607,6 +609,43 @@ class _GELU(Function):
 
 def gelu(x):
     return _GELU.apply(x)
+
+
+class _CausalAttention(Function):
+    """Causal self-attention (head dim 64) straight on the fused projection: ``qkv`` [B*T, 3*H*64] bf16 -> [B*T, H*64] bf16.
+    Flash attention on tcgen05 / TMEM (csrc/ops/attention_tc.cu): q / k / v are read in place through one TMA tensor map, the
+    output comes back with the heads already merged, and backward returns d(qkv) in the projection's own layout - so the
+    split-heads / merge-heads copies of the module-level formulation disappear together with the library SDPA call."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, T, H):
+        qkv = qkv if qkv.is_contiguous() else qkv.contiguous()
+        out = torch.empty(B * T, H * 64, dtype=torch.bfloat16, device=qkv.device)
+        lse = torch.empty(B * H, T, dtype=torch.float32, device=qkv.device)
+        _chk(lib().dcp_attn_fwd(qkv.data_ptr(), out.data_ptr(), lse.data_ptr(), B, T, H, _stream()))
+        ctx.save_for_backward(qkv, out, lse)
+        ctx.dims = (B, T, H)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, out, lse = ctx.saved_tensors
+        B, T, H = ctx.dims
+        dout = dout if dout.is_contiguous() else dout.contiguous()
+        dqkv = torch.empty_like(qkv)
+        delta = torch.empty(B * H * T, dtype=torch.float32, device=qkv.device)
+        acc = torch.empty(B * T * H * 64, dtype=torch.float32, device=qkv.device)
+        _chk(lib().dcp_attn_bwd(qkv.data_ptr(), out.data_ptr(), dout.data_ptr(), lse.data_ptr(), dqkv.data_ptr(), delta.data_ptr(), acc.data_ptr(),
+                                B, T, H, _stream()))
+        return dqkv, None, None, None
+
+
+def causal_attention_supported(qkv: torch.Tensor, T: int, H: int) -> bool:
+    return qkv.is_cuda and qkv.dtype == torch.bfloat16 and T % 128 == 0 and qkv.shape[-1] == 3 * H * 64
+
+
+def causal_attention(qkv: torch.Tensor, B: int, T: int, H: int) -> torch.Tensor:
+    return _CausalAttention.apply(qkv, B, T, H)
 
 
 # -------------------------------------------------------------------------------------- optimizer --
