@@ -17,6 +17,7 @@
 //                          lives in REGISTERS (32 floats per thread): each PV_j is added from TMEM and rescaled there, so
 //                          TMEM never has to be rewritten.  Online softmax in the log2 domain.
 // The row-wise log-sum-exp (log2 domain) is saved for the backward pass.
+#include <type_traits>
 #include <cudaTypedefs.h>
 
 #include "ops/tc_common.cuh"
@@ -47,14 +48,42 @@ struct AttnFwdParams {
 __device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t u) { return r * 128u + ((u ^ (r & 7u)) << 4); }
 
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+// bulk-group side of the copy engine: tile store through a tensor map, fp32 reduce-add of a contiguous block
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src_smem, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(m), "r"(smem_u32(src_smem)), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_reduce_add_f32(float* dst, const void* src_smem, uint32_t bytes) {
+  asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f32 [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src_smem)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait0() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float ex2(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// packed fp32 pairs (FFMA2 / FMUL2 / FADD2) and the three-input maximum (FMNMX3): half the issue slots of the scalar forms
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  float2 d;
+  asm("fma.rn.ftz.f32x2 %0, %1, %2, %3;" : "=l"(reinterpret_cast<uint64_t&>(d)) : "l"(reinterpret_cast<const uint64_t&>(a)), "l"(reinterpret_cast<const uint64_t&>(b)), "l"(reinterpret_cast<const uint64_t&>(c)));
+  return d;
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  float2 d;
+  asm("mul.rn.ftz.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<uint64_t&>(d)) : "l"(reinterpret_cast<const uint64_t&>(a)), "l"(reinterpret_cast<const uint64_t&>(b)));
+  return d;
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  float2 d;
+  asm("add.rn.ftz.f32x2 %0, %1, %2;" : "=l"(reinterpret_cast<uint64_t&>(d)) : "l"(reinterpret_cast<const uint64_t&>(a)), "l"(reinterpret_cast<const uint64_t&>(b)));
+  return d;
+}
+__device__ __forceinline__ float fmax3(float a, float b, float c) { float d; asm("max.ftz.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c)); return d; }
+__device__ __forceinline__ float2 u2f2(uint32_t a, uint32_t b) { return make_float2(__uint_as_float(a), __uint_as_float(b)); }
 __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
 __global__ void __launch_bounds__(kAttnThreads, 2)
-k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
+k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_out, const AttnFwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
   uint8_t* q_smem = smem;                                   // 16 KB
@@ -62,8 +91,10 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
   uint8_t* p_smem = kv_smem + kRing * kTileBytes;           // 32 KB: P as two 64-column K-major chunks
   AttnBars* bars = reinterpret_cast<AttnBars*>(p_smem + 2 * kTileBytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const int qi = (int)gridDim.x - 1 - (int)blockIdx.x;      // heavy (late) query blocks first
-  const int bh = blockIdx.y, b = bh / p.H, h = bh % p.H;
+  // grid (batch*head, query blocks): blocks are handed out x-fastest, so ALL the heavy (late) query blocks run first and the
+  // one-tile blocks fill the tail - longest-first scheduling of unequal work
+  const int qi = (int)gridDim.y - 1 - (int)blockIdx.y;
+  const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
   const int row0 = b * p.T + qi * kBQ;                      // first row of this query block in the [B*T, 3C] matrix
   const int nkv = qi + 1;
 
@@ -150,13 +181,16 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
     const int half = warp >> 2, lg = warp & 3;
     const int row = lg * 32 + lane;                          // row inside the block = TMEM lane
     const uint32_t lane_addr = (uint32_t)(lg * 32) << 16;
-    float o[32];
+    float2 o[16];
 #pragma unroll
-    for (int i = 0; i < 32; ++i) o[i] = 0.f;
+    for (int i = 0; i < 16; ++i) o[i] = make_float2(0.f, 0.f);
     float m = -INFINITY, l = 0.f;
-    for (int j = 0; j < nkv; ++j) {
+    const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
+    uint8_t* chunk = p_smem + half * kTileBytes;
+    // one key block; kDiag: the block on the diagonal, the only one that needs the causal mask
+    auto tile = [&](auto dtag, int j) {
+      constexpr bool kDiag = decltype(dtag)::value;
       const uint32_t tS = tS0 + (j & 1) * 128 + lane_addr + half * 64;
-      const bool diag = j == qi;
       mbar_wait(&bars->s_full[j & 1], (j >> 1) & 1);
       tc_fence_after();
       // pass 1: maximum of this thread's 64 columns (S_j is read again below: TMEM reads are cheap, 64 live registers are not
@@ -168,12 +202,17 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
         tmem_ld32(tS + c * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (!diag || half * 64 + c * 32 + i <= row) mx = fmaxf(mx, __uint_as_float(r[i]));
+        for (int i = 0; i < 32; i += 2) {
+          float a = __uint_as_float(r[i]), b2 = __uint_as_float(r[i + 1]);
+          if (kDiag) { const int col = half * 64 + c * 32 + i; if (col > row) a = -INFINITY; if (col + 1 > row) b2 = -INFINITY; }
+          mx = fmax3(mx, a, b2);
+        }
       }
       bars->xmax[j & 1][half][row] = mx;
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const float m_new = fmaxf(m, fmaxf(mx, bars->xmax[j & 1][half ^ 1][row]) * p.scale_log2);
+      const float alpha = ex2(m - m_new);                    // m = -inf on the first block: alpha = 0, o and l are 0 anyway
+      const float2 al2 = make_float2(alpha, alpha);
       // previous block's P V arrives: add it, then rescale everything to the new maximum
       if (j > 0) {
         mbar_wait(&bars->pv_full, (j - 1) & 1);
@@ -182,16 +221,13 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
         tmem_ld32(tS0 + ((j - 1) & 1) * 128 + lane_addr + half * 32, r);
         tmem_ld_wait();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] += __uint_as_float(r[i]);
+        for (int i = 0; i < 16; ++i) o[i] = fmul2(fadd2(o[i], u2f2(r[2 * i], r[2 * i + 1])), al2);
       }
-      const float alpha = ex2(m - m_new);                    // m = -inf on the first block: alpha = 0, o and l are 0 anyway
       m = m_new;
       l *= alpha;
-#pragma unroll
-      for (int i = 0; i < 32; ++i) o[i] *= alpha;
       // P = exp2(S * scale - m), bf16, into chunk `half` of the swizzled K-major tile (the previous P V has finished reading it)
-      float sum = 0.f;
-      uint8_t* chunk = p_smem + half * kTileBytes;
+      const float2 nm2 = make_float2(-m, -m);
+      float2 sum = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t r[32];
@@ -202,22 +238,23 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
           uint32_t pk[4];
 #pragma unroll
           for (int i = 0; i < 8; i += 2) {
-            const int cc = c * 32 + u * 8 + i;
-            float p0 = ex2(__uint_as_float(r[u * 8 + i]) * p.scale_log2 - m), p1 = ex2(__uint_as_float(r[u * 8 + i + 1]) * p.scale_log2 - m);
-            if (diag) { if (half * 64 + cc > row) p0 = 0.f; if (half * 64 + cc + 1 > row) p1 = 0.f; }
-            // sum what the MMA will see (bf16-rounded), so that the normalisation matches the numerator
-            const __nv_bfloat162 q2 = __floats2bfloat162_rn(p0, p1);
-            sum += __low2float(q2) + __high2float(q2);
-            pk[i >> 1] = *reinterpret_cast<const uint32_t*>(&q2);
+            const int cc = half * 64 + c * 32 + u * 8 + i;
+            const float2 x = ffma2(u2f2(r[u * 8 + i], r[u * 8 + i + 1]), sc2, nm2);
+            float2 e = make_float2(ex2(x.x), ex2(x.y));
+            if (kDiag) { if (cc > row) e.x = 0.f; if (cc + 1 > row) e.y = 0.f; }
+            sum = fadd2(sum, e);
+            pk[i >> 1] = pack_bf16(e.x, e.y);
           }
           *reinterpret_cast<uint4*>(chunk + swz(row, c * 4 + u)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
         }
       }
-      l += sum;
+      l += sum.x + sum.y;
       tc_fence_before();
       fence_async_smem();                                    // generic-proxy stores -> visible to the tensor core's async proxy
       mbar_arrive(&bars->p_ready);
-    }
+    };
+    for (int j = 0; j < qi; ++j) tile(std::false_type{}, j);
+    tile(std::true_type{}, qi);
     // last block's P V
     mbar_wait(&bars->pv_full, (nkv - 1) & 1);
     tc_fence_after();
@@ -226,7 +263,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
       tmem_ld32(tS0 + ((nkv - 1) & 1) * 128 + lane_addr + half * 32, r);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 32; ++i) o[i] += __uint_as_float(r[i]);
+      for (int i = 0; i < 16; ++i) o[i] = fadd2(o[i], u2f2(r[2 * i], r[2 * i + 1]));
     }
     if (half == 1) bars->xsum[row] = l;
     asm volatile("bar.sync 1, 256;" ::: "memory");
@@ -236,13 +273,17 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
     asm volatile("bar.sync 1, 256;" ::: "memory");
     l = bars->xsum[row];
     const float inv = 1.f / l;
-    __nv_bfloat16* dst = p.out + (size_t)(row0 + row) * p.C + h * kD + half * 32;
+    // the output tile goes out through the copy engine (staged in the P tile, which the last P V has finished reading): a
+    // thread's 64 bytes per row would otherwise be 32 separate transactions per store instruction
 #pragma unroll
-    for (int i = 0; i < 32; i += 8) {
-      uint4 v = make_uint4(pack_bf16(o[i] * inv, o[i + 1] * inv), pack_bf16(o[i + 2] * inv, o[i + 3] * inv), pack_bf16(o[i + 4] * inv, o[i + 5] * inv),
-                           pack_bf16(o[i + 6] * inv, o[i + 7] * inv));
-      *reinterpret_cast<uint4*>(dst + i) = v;
+    for (int i = 0; i < 16; i += 4) {
+      uint4 v = make_uint4(pack_bf16(o[i].x * inv, o[i].y * inv), pack_bf16(o[i + 1].x * inv, o[i + 1].y * inv), pack_bf16(o[i + 2].x * inv, o[i + 2].y * inv),
+                           pack_bf16(o[i + 3].x * inv, o[i + 3].y * inv));
+      *reinterpret_cast<uint4*>(p_smem + swz(row, half * 4 + (i >> 2))) = v;
     }
+    fence_async_smem();
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    if (threadIdx.x == 0) { tma_store_2d(&map_out, p_smem, h * kD, row0); bulk_commit(); bulk_wait_read0(); }
     if (half == 0) p.lse[(size_t)bh * p.T + qi * kBQ + row] = m + log2f(l);
   }
   tc_fence_before();
@@ -251,58 +292,66 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const AttnFwdParams p) {
 }
 
 // =====================================================================================================
-// Backward.  One CTA per (128-row key/value block j, batch*head); query blocks i = j .. T/128 - 1 stream through it.
+// Backward.  Work item = (128-row key/value block j, batch*head); query blocks i = j .. T/128 - 1 stream through it:
 //   S  = Q_i K_j^T            dP = dO_i V_j^T                         (two 128x128x64 MMAs into TMEM)
 //   P  = exp2(S * scale - lse_i)          dS = P o (dP - delta_i) * softmax_scale      (threads: row = query, written as bf16 into
 //                                                                                         two swizzled [query][key] tiles)
 //   dV += P^T dO_i            dK += dS^T Q_i            dQ_i = dS K_j  (three 128x64x128 MMAs; P / dS are read both MN-major - the
 //                                                                        transposed products - and K-major from the same tiles)
-// dV / dK accumulate in TMEM over the whole loop and are written once (bf16, straight into the dqkv matrix next to dq, i.e. in
-// the layout the qkv projection's backward GEMMs read); dQ_i is added to an fp32 accumulator with vector reductions
-// (red.global.add.v4.f32: several key blocks contribute to one query block) and converted by k_attn_dq_convert.
-//   warp 4 TMA: K_j, V_j once; (Q_i, dO_i) through two stages        warp 5 MMA issuer        warps 0-3: thread = query row
+// dV / dK accumulate in TMEM over the item's loop and are written once (bf16, straight into the dqkv matrix next to dq, i.e. in
+// the layout the qkv projection's backward GEMMs read); dQ_i is added to an fp32 accumulator by the bulk-copy engine (several
+// key blocks contribute to one query block) and converted by k_attn_dq_convert.
+//
+// PERSISTENT: one CTA per SM walks a list of items (heaviest first, the direction alternating from round to round so that
+// every CTA gets a similar number of query blocks).  All three roles treat the query-block iterations of consecutive items
+// as ONE stream (counter g): the producer fetches the next item's K / V (double-buffered) and Q / dO while the current item
+// is still running, the MMA warp issues the next item's first S / dP ahead of the current item's last products, and the
+// threads write the finished item's dK / dV while those run - so no per-item prologue or epilogue is exposed.
+//   warp 8 TMA        warp 9 MMA issuer        warps 0-7: two threads per query row
 // =====================================================================================================
 struct __align__(16) AttnBwdBars {
-  uint64_t kv_full, qdo_full[2], qdo_empty[2], sdp_full, pds_ready, pds_free, dq_full, dq_free;
+  uint64_t kv_full[2], kv_empty[2], qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full;
   uint32_t tmem_base;
 };
 
 struct AttnBwdParams {
-  int T, H, C;
+  int T, H, C, BH;
   float scale_log2, scale;
   const float* lse;            // [B*H, T] log2 domain
   const float* delta;          // [B*H, T] rowsum(dO o O)
-  float* dq_acc;               // [B*T, C] fp32, zeroed by the caller
+  float* dq_acc;               // fp32, zeroed by the caller: one 128 x 64 tile per (batch*head, query block), [16-byte unit][row]
   __nv_bfloat16* dqkv;         // [B*T, 3C]: dk / dv written here (columns C + h*64, 2C + h*64)
+  long long* trace;            // debugging: clock64 stamps of CTA trace_x's first iterations (dcp_attn_set_trace), else nullptr
+  int trace_x, trace_y;
 };
+#define ATTN_STAMP(g, k) do { if (p.trace != nullptr && (g) < 32 && blockIdx.x == p.trace_x && lane == 0 && (warp == 0 || warp == 9)) p.trace[(g) * 8 + (k)] = clock64(); } while (0)
 
-__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
-  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
-}
+// the r-th item of CTA c out of G: rounds alternate direction (c, 2G-1-c, 2G+c, ...); items are ordered heaviest first
+__device__ __forceinline__ int bwd_item(int r, int c, int G) { return r * G + ((r & 1) ? G - 1 - c : c); }
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
-k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_do, const AttnBwdParams p) {
+k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_do, const __grid_constant__ CUtensorMap map_dqkv,
+           const AttnBwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = align_smem_1024(smem_raw);
-  uint8_t* k_smem = smem;                                   // 16 KB
-  uint8_t* v_smem = smem + kTileBytes;                      // 16 KB
-  uint8_t* qdo_smem = smem + 2 * kTileBytes;                // 2 stages x (Q 16 KB + dO 16 KB)
+  uint8_t* kv_smem = smem;                                  // 2 buffers x (K 16 KB + V 16 KB)
+  uint8_t* qdo_smem = smem + 4 * kTileBytes;                // 2 stages x (Q 16 KB + dO 16 KB)
   uint8_t* p_smem = qdo_smem + 4 * kTileBytes;              // 32 KB: P  [query][key], two 64-key chunks
   uint8_t* ds_smem = p_smem + 2 * kTileBytes;               // 32 KB: dS [query][key]
-  AttnBwdBars* bars = reinterpret_cast<AttnBwdBars*>(ds_smem + 2 * kTileBytes);
+  uint8_t* dq_smem = ds_smem + 2 * kTileBytes;              // 32 KB: dQ_i staging for the bulk reduce-add (fp32, [16-byte unit][row])
+  AttnBwdBars* bars = reinterpret_cast<AttnBwdBars*>(dq_smem + 2 * kTileBytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  const int kj = blockIdx.x;                                // key/value block: 0 (most query blocks) first
-  const int bh = blockIdx.y, b = bh / p.H, h = bh % p.H;
-  const int nq = p.T / kBQ, nit = nq - kj;
+  const int nq = p.T / kBQ, nitems = nq * p.BH, G = gridDim.x, cta = blockIdx.x;
 
   griddep_launch();
   if (warp == 8 && lane == 0) { tma_prefetch_desc(&map_qkv); tma_prefetch_desc(&map_do); }
   if (warp == 9) {
     if (lane == 0) {
-      mbar_init(&bars->kv_full, 1);
-      for (int i = 0; i < 2; ++i) { mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1); }
-      mbar_init(&bars->sdp_full, 1); mbar_init(&bars->pds_ready, 256); mbar_init(&bars->pds_free, 1);
-      mbar_init(&bars->dq_full, 1); mbar_init(&bars->dq_free, 256);
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 1);
+        mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1);
+      }
+      mbar_init(&bars->sdp_full, 1); mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1);
       mbar_fence_init();
     }
     __syncwarp();
@@ -316,34 +365,44 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   const uint32_t tS = tmem, tDP = tmem + 128, tDV = tmem + 256, tDK = tmem + 320, tDQ = tmem + 384;
 
   if (warp == 8) {
-    if (lane == 0) {
-      mbar_expect_tx(&bars->kv_full, 2 * kTileBytes);
-      tma_load_2d(k_smem, &map_qkv, &bars->kv_full, p.C + h * kD, b * p.T + kj * kBK);
-      tma_load_2d(v_smem, &map_qkv, &bars->kv_full, 2 * p.C + h * kD, b * p.T + kj * kBK);
-    }
-    __syncwarp();
-    for (int it = 0; it < nit; ++it) {
-      const int st = it & 1, ph = (it >> 1) & 1;
-      mbar_wait(&bars->qdo_empty[st], ph ^ 1);
+    // ---- TMA producer: K_j / V_j of item n into buffer n & 1, then its (Q_i, dO_i) pairs through the two stages
+    int g = 0;
+    for (int n = 0, w = bwd_item(0, cta, G); w < nitems; ++n, w = bwd_item(n, cta, G)) {
+      const int kj = w / p.BH, bh = w % p.BH, b = bh / p.H, h = bh % p.H, nit = nq - kj;
+      mbar_wait(&bars->kv_empty[n & 1], ((n >> 1) & 1) ^ 1);
       if (lane == 0) {
-        const int r0 = b * p.T + (kj + it) * kBQ;
-        mbar_expect_tx(&bars->qdo_full[st], 2 * kTileBytes);
-        tma_load_2d(qdo_smem + st * 2 * kTileBytes, &map_qkv, &bars->qdo_full[st], h * kD, r0);
-        tma_load_2d(qdo_smem + st * 2 * kTileBytes + kTileBytes, &map_do, &bars->qdo_full[st], h * kD, r0);
+        uint8_t* kb = kv_smem + (n & 1) * 2 * kTileBytes;
+        mbar_expect_tx(&bars->kv_full[n & 1], 2 * kTileBytes);
+        tma_load_2d(kb, &map_qkv, &bars->kv_full[n & 1], p.C + h * kD, b * p.T + kj * kBK);
+        tma_load_2d(kb + kTileBytes, &map_qkv, &bars->kv_full[n & 1], 2 * p.C + h * kD, b * p.T + kj * kBK);
       }
       __syncwarp();
+      for (int it = 0; it < nit; ++it, ++g) {
+        const int st = g & 1;
+        mbar_wait(&bars->qdo_empty[st], ((g >> 1) & 1) ^ 1);
+        if (lane == 0) {
+          const int r0 = b * p.T + (kj + it) * kBQ;
+          mbar_expect_tx(&bars->qdo_full[st], 2 * kTileBytes);
+          tma_load_2d(qdo_smem + st * 2 * kTileBytes, &map_qkv, &bars->qdo_full[st], h * kD, r0);
+          tma_load_2d(qdo_smem + st * 2 * kTileBytes + kTileBytes, &map_do, &bars->qdo_full[st], h * kD, r0);
+        }
+        __syncwarp();
+      }
     }
   } else if (warp == 9) {
+    // ---- MMA issuer
     const uint32_t idesc_s = make_idesc(false, false, false, kBQ, kBK);      // S / dP: both operands K-major, 128 x 128
     const uint32_t idesc_t = make_idesc(false, true, true, kBK, kD);         // dV / dK: A = P^T / dS^T (MN-major), B = dO / Q (MN-major)
     const uint32_t idesc_q = make_idesc(false, false, true, kBQ, kD);        // dQ: A = dS (K-major), B = K (MN-major)
-    const uint32_t ka = smem_u32(k_smem), va = smem_u32(v_smem), pa = smem_u32(p_smem), dsa = smem_u32(ds_smem);
-    auto issue_sdp = [&](int it) {
-      const int st = it & 1;
-      mbar_wait(&bars->qdo_full[st], (it >> 1) & 1);
+    const uint32_t pa = smem_u32(p_smem), dsa = smem_u32(ds_smem);
+    // S / dP of stream iteration g, which belongs to the item whose K / V sit in buffer `kvb`
+    auto issue_sdp = [&](int g, int kvb) {
+      const int st = g & 1;
+      mbar_wait(&bars->qdo_full[st], (g >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
         const uint32_t qa = smem_u32(qdo_smem + st * 2 * kTileBytes), doa = qa + kTileBytes;
+        const uint32_t ka = smem_u32(kv_smem + kvb * 2 * kTileBytes), va = ka + kTileBytes;
 #pragma unroll
         for (int k = 0; k < kD / 16; ++k)
           umma<false>(tS, make_smem_desc(qa + k * 32, 0, 1024), make_smem_desc(ka + k * 32, 0, 1024), idesc_s, k > 0);
@@ -354,48 +413,118 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       }
       __syncwarp();
     };
-    mbar_wait(&bars->kv_full, 0);
-    issue_sdp(0);
-    for (int it = 0; it < nit; ++it) {
-      const int st = it & 1;
-      mbar_wait(&bars->pds_ready, it & 1);                 // P / dS of this iteration are in shared memory; S / dP have been consumed
-      if (it + 1 < nit) issue_sdp(it + 1);                 // the next scores are computed while the three products below run
-      if (it > 0) mbar_wait(&bars->dq_free, (it - 1) & 1); // the threads have taken dQ of the previous iteration
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t qa = smem_u32(qdo_smem + st * 2 * kTileBytes), doa = qa + kTileBytes;
+    int g = 0;
+    if (bwd_item(0, cta, G) < nitems) {
+      mbar_wait(&bars->kv_full[0], 0);
+      issue_sdp(0, 0);
+    }
+    for (int n = 0, w = bwd_item(0, cta, G); w < nitems; ++n, w = bwd_item(n, cta, G)) {
+      const int nit = nq - w / p.BH;
+      const bool more = bwd_item(n + 1, cta, G) < nitems;
+      const uint32_t ka = smem_u32(kv_smem + (n & 1) * 2 * kTileBytes);
+      for (int it = 0; it < nit; ++it, ++g) {
+        const int st = g & 1;
+        mbar_wait(&bars->pds_ready, g & 1);                // P / dS of g are in shared memory; S / dP, dQ(g-1) and - at an item
+        ATTN_STAMP(g, 4);                                  // boundary - the finished item's dK / dV have been read
+        // the next scores (of this item or of the next one) are computed ahead of the three products below
+        if (it + 1 < nit) issue_sdp(g + 1, n & 1);
+        else if (more) { mbar_wait(&bars->kv_full[(n + 1) & 1], ((n + 1) >> 1) & 1); issue_sdp(g + 1, (n + 1) & 1); }
+        ATTN_STAMP(g, 5);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t qa = smem_u32(qdo_smem + st * 2 * kTileBytes), doa = qa + kTileBytes;
 #pragma unroll
-        for (int k = 0; k < kBQ / 16; ++k) {
-          // K index = query row: 16 rows = 2048 B per step in every operand here; LBO = next 64-key chunk of P / dS
-          const uint64_t pT = make_smem_desc(pa + k * 2048, kTileBytes, 1024), dsT = make_smem_desc(dsa + k * 2048, kTileBytes, 1024);
-          umma<false>(tDV, pT, make_smem_desc(doa + k * 2048, kTileBytes, 1024), idesc_t, (it > 0) || (k > 0));
-          umma<false>(tDK, dsT, make_smem_desc(qa + k * 2048, kTileBytes, 1024), idesc_t, (it > 0) || (k > 0));
+          for (int k = 0; k < kBQ / 16; ++k) {
+            // K index = query row: 16 rows = 2048 B per step in every operand here; LBO = next 64-key chunk of P / dS
+            const uint64_t pT = make_smem_desc(pa + k * 2048, kTileBytes, 1024), dsT = make_smem_desc(dsa + k * 2048, kTileBytes, 1024);
+            umma<false>(tDV, pT, make_smem_desc(doa + k * 2048, kTileBytes, 1024), idesc_t, (it > 0) || (k > 0));
+            umma<false>(tDK, dsT, make_smem_desc(qa + k * 2048, kTileBytes, 1024), idesc_t, (it > 0) || (k > 0));
+          }
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k)               // K index = key: dS chunk (k / 4), 32 B per step; K_j rows 16 k ..
+            umma<false>(tDQ, make_smem_desc(dsa + (k >> 2) * kTileBytes + (k & 3) * 32, 0, 1024), make_smem_desc(ka + k * 2048, kTileBytes, 1024), idesc_q, k > 0);
+          umma_commit(&bars->qdo_empty[st]);
+          if (it == nit - 1) umma_commit(&bars->kv_empty[n & 1]);
+          umma_commit(&bars->dq_full);
         }
-#pragma unroll
-        for (int k = 0; k < kBK / 16; ++k)                 // K index = key: dS chunk (k / 4), 32 B per step; K_j rows 16 k ..
-          umma<false>(tDQ, make_smem_desc(dsa + (k >> 2) * kTileBytes + (k & 3) * 32, 0, 1024), make_smem_desc(ka + k * 2048, kTileBytes, 1024), idesc_q, k > 0);
-        umma_commit(&bars->qdo_empty[st]);
-        umma_commit(&bars->pds_free);
-        umma_commit(&bars->dq_full);
+        __syncwarp();
+        ATTN_STAMP(g, 6);
       }
-      __syncwarp();
     }
   } else {
     // two threads per query row: `half` selects the 64 key columns of S / dP (= chunk `half` of the P / dS tiles), the 32 dQ
-    // columns, and at the end which of dK / dV this thread writes
+    // columns, and at the end of an item which of dK / dV this thread writes
     const int half = warp >> 2, lg = warp & 3;
     const int row = lg * 32 + lane;
     const uint32_t lane_addr = (uint32_t)(lg * 32) << 16;
-    for (int it = 0; it < nit; ++it) {
-      const int qi = kj + it;
-      const bool diag = it == 0;
-      const size_t grow = (size_t)bh * p.T + qi * kBQ + row;
-      const float lse = p.lse[grow], delta = p.delta[grow];
-      mbar_wait(&bars->sdp_full, it & 1);
-      if (it > 0) mbar_wait(&bars->pds_free, (it - 1) & 1);  // the previous iteration's products no longer read the P / dS tiles
+    // dQ of stream iteration gq (query-block tile `qtile` of the accumulator) -> fp32 accumulator.  Several key blocks add into
+    // one query block, so this is a reduction in global memory - done by the bulk-copy engine (one 32 KB cp.reduce.async.bulk
+    // add per tile out of a staging buffer) rather than by per-lane red instructions, which cost the load/store pipe ~1.3
+    // cycles per lane and instruction.  The accumulator tile of (head, query block) is contiguous, stored as [16-byte unit
+    // 0..15][row 0..127]: conflict-free to stage from "thread = row", and k_attn_dq_convert undoes it.
+    auto take_dq = [&](int gq, size_t qtile) {
+      mbar_wait(&bars->dq_full, gq & 1);                    // all five products of iteration gq are done: dQ is complete and the
+      tc_fence_after();                                     // P / dS tiles are no longer read
+      ATTN_STAMP(gq, 7);
+      uint32_t r[32];
+      tmem_ld32(tDQ + lane_addr + half * 32, r);
+      tmem_ld_wait();
+      if (threadIdx.x == 0) bulk_wait_read0();              // the previous tile has left the staging buffer
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        *reinterpret_cast<uint4*>(dq_smem + (((half * 8 + u) * kBQ + row) << 4)) = make_uint4(r[4 * u], r[4 * u + 1], r[4 * u + 2], r[4 * u + 3]);
+      fence_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) {
+        bulk_reduce_add_f32(p.dq_acc + qtile * (kBQ * kD), dq_smem, kBQ * kD * 4);
+        bulk_commit();
+      }
+    };
+    // dK (half 0) / dV (half 1) of a finished item: thread = key row.  Staged (swizzled, 16 KB each) in the P tile - free once
+    // the item's last products are done, and rewritten only after take_dq's wait on the bulk group below - and stored by the
+    // copy engine: a thread's 128 bytes per row would be 32 separate transactions per store instruction.
+    auto write_dkv = [&](int w, int gq) {
+      const int kj = w / p.BH, bh = w % p.BH, b = bh / p.H, h = bh % p.H;
+      mbar_wait(&bars->dq_full, gq & 1);
       tc_fence_after();
-      uint8_t* pc = p_smem + half * kTileBytes;
-      uint8_t* dc = ds_smem + half * kTileBytes;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t r[32];
+        tmem_ld32((half ? tDV : tDK) + lane_addr + c * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 32; i += 8)
+          *reinterpret_cast<uint4*>(p_smem + half * kTileBytes + swz(row, c * 4 + (i >> 3))) =
+              make_uint4(pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])),
+                         pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5])), pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7])));
+      }
+      fence_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) {
+        tma_store_2d(&map_dqkv, p_smem, p.C + h * kD, b * p.T + kj * kBK);
+        tma_store_2d(&map_dqkv, p_smem + kTileBytes, 2 * p.C + h * kD, b * p.T + kj * kBK);
+        bulk_commit();
+      }
+    };
+    uint8_t* pc = p_smem + half * kTileBytes;
+    uint8_t* dc = ds_smem + half * kTileBytes;
+    const float2 sc2 = make_float2(p.scale_log2, p.scale_log2), ss2 = make_float2(p.scale, p.scale);
+    int g = 0, w_prev = -1;
+    size_t qtile_prev = 0;
+    // stream iteration g = query block `it` of item w; kDiag: the block on the diagonal (it == 0), the only one that needs the mask
+    auto tile = [&](auto dtag, int w, int it) {
+      constexpr bool kDiag = decltype(dtag)::value;
+      const int kj = w / p.BH, bh = w % p.BH;
+      const size_t grow = (size_t)bh * p.T + (kj + it) * kBQ + row;
+      const float lse = p.lse[grow], delta = p.delta[grow];
+      const float2 nl2 = make_float2(-lse, -lse), nd2 = make_float2(-delta * p.scale, -delta * p.scale);
+      // P / dS of this iteration are computed into registers while the tensor core still runs the previous iteration's
+      // dV / dK / dQ products (the MMA warp issues S / dP of this iteration ahead of them)
+      uint32_t pk[32], dk[32];
+      mbar_wait(&bars->sdp_full, g & 1);
+      tc_fence_after();
+      ATTN_STAMP(g, 0);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         uint32_t rs[32], rp[32];
@@ -403,52 +532,43 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
         tmem_ld32(tDP + lane_addr + half * 64 + c * 32, rp);
         tmem_ld_wait();
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          uint32_t pk[4], dk[4];
-#pragma unroll
-          for (int i = 0; i < 8; i += 2) {
-            const int e = u * 8 + i, col = half * 64 + c * 32 + e;
-            float p0 = ex2(__uint_as_float(rs[e]) * p.scale_log2 - lse), p1 = ex2(__uint_as_float(rs[e + 1]) * p.scale_log2 - lse);
-            if (diag) { if (col > row) p0 = 0.f; if (col + 1 > row) p1 = 0.f; }
-            const float d0 = p0 * (__uint_as_float(rp[e]) - delta) * p.scale, d1 = p1 * (__uint_as_float(rp[e + 1]) - delta) * p.scale;
-            pk[i >> 1] = pack_bf16(p0, p1);
-            dk[i >> 1] = pack_bf16(d0, d1);
-          }
-          *reinterpret_cast<uint4*>(pc + swz(row, c * 4 + u)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-          *reinterpret_cast<uint4*>(dc + swz(row, c * 4 + u)) = make_uint4(dk[0], dk[1], dk[2], dk[3]);
+        for (int e = 0; e < 32; e += 2) {
+          const int col = half * 64 + c * 32 + e;
+          const float2 x = ffma2(u2f2(rs[e], rs[e + 1]), sc2, nl2);
+          float2 pr = make_float2(ex2(x.x), ex2(x.y));
+          if (kDiag) { if (col > row) pr.x = 0.f; if (col + 1 > row) pr.y = 0.f; }
+          const float2 d = fmul2(pr, ffma2(u2f2(rp[e], rp[e + 1]), ss2, nd2));     // P o (dP - delta) * scale
+          pk[c * 16 + (e >> 1)] = pack_bf16(pr.x, pr.y);
+          dk[c * 16 + (e >> 1)] = pack_bf16(d.x, d.y);
         }
       }
       tc_fence_before();
-      fence_async_smem();
-      mbar_arrive(&bars->pds_ready);
-      // dQ_i of this key block -> fp32 accumulator (32 of the 64 columns per thread)
-      mbar_wait(&bars->dq_full, it & 1);
-      tc_fence_after();
-      float* dq = p.dq_acc + ((size_t)b * p.T + qi * kBQ + row) * p.C + h * kD + half * 32;
-      {
-        uint32_t r[32];
-        tmem_ld32(tDQ + lane_addr + half * 32, r);
-        tmem_ld_wait();
+      ATTN_STAMP(g, 1);
+      if (kDiag && w_prev >= 0) write_dkv(w_prev, g - 1);   // item boundary: once the previous item's last products are done
+      if (g > 0) take_dq(g - 1, qtile_prev);                // (waits until the copy engine has read the tiles staged just above)
+      ATTN_STAMP(g, 2);
 #pragma unroll
-        for (int i = 0; i < 32; i += 4)
-          red_add_v4(dq + i, __uint_as_float(r[i]), __uint_as_float(r[i + 1]), __uint_as_float(r[i + 2]), __uint_as_float(r[i + 3]));
+      for (int u = 0; u < 8; ++u) {
+        *reinterpret_cast<uint4*>(pc + swz(row, u)) = make_uint4(pk[u * 4], pk[u * 4 + 1], pk[u * 4 + 2], pk[u * 4 + 3]);
+        *reinterpret_cast<uint4*>(dc + swz(row, u)) = make_uint4(dk[u * 4], dk[u * 4 + 1], dk[u * 4 + 2], dk[u * 4 + 3]);
       }
       tc_fence_before();
-      mbar_arrive(&bars->dq_free);
+      fence_async_smem();
+      mbar_arrive(&bars->pds_ready);                        // also: S / dP, the previous dQ and a finished item's dK / dV have been read
+      ATTN_STAMP(g, 3);
+      qtile_prev = (size_t)bh * nq + kj + it;
+      ++g;
+    };
+    for (int n = 0, w = bwd_item(0, cta, G); w < nitems; ++n, w = bwd_item(n, cta, G)) {
+      const int nit = nq - w / p.BH;
+      tile(std::true_type{}, w, 0);
+      w_prev = w;
+      for (int it = 1; it < nit; ++it) tile(std::false_type{}, w, it);
     }
-    // dK (half 0) / dV (half 1) of this key block: thread = key row
-    mbar_wait(&bars->pds_free, (nit - 1) & 1);
-    tc_fence_after();
-    __nv_bfloat16* dst = p.dqkv + ((size_t)b * p.T + kj * kBK + row) * (3 * p.C) + h * kD + (half + 1) * p.C;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      uint32_t r[32];
-      tmem_ld32((half ? tDV : tDK) + lane_addr + c * 32, r);
-      tmem_ld_wait();
-#pragma unroll
-      for (int i = 0; i < 32; i += 8)
-        *reinterpret_cast<uint4*>(dst + c * 32 + i) = make_uint4(pack_bf16(__uint_as_float(r[i]), __uint_as_float(r[i + 1])), pack_bf16(__uint_as_float(r[i + 2]), __uint_as_float(r[i + 3])),
-                                                                  pack_bf16(__uint_as_float(r[i + 4]), __uint_as_float(r[i + 5])), pack_bf16(__uint_as_float(r[i + 6]), __uint_as_float(r[i + 7])));
+    if (g > 0) {
+      write_dkv(w_prev, g - 1);
+      take_dq(g - 1, qtile_prev);
+      if (threadIdx.x == 0) bulk_wait0();                   // the last tile's reduction has been performed
     }
   }
   tc_fence_before();
@@ -456,38 +576,48 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   if (warp == 9) tmem_dealloc<512>(tmem);
 }
 
-// delta[bh, t] = sum_d dO[t, h, d] * O[t, h, d]: one thread per (row, head), 64 products
+// delta[bh, t] = sum_d dO[t, h, d] * O[t, h, d]: eight lanes per (row, head), 16 bytes of O and dO each (consecutive lanes read
+// consecutive memory), three shuffles.  The same threads zero the dQ accumulator (as many floats as O has elements).
 __global__ void __launch_bounds__(256) k_attn_delta(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ dout, float* __restrict__ delta,
-                                                    int BT, int T, int H) {
+                                                    float* __restrict__ dq_acc, long nchunk, int T, int H) {
   griddep_launch();
   griddep_wait();
-  const long idx = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (idx >= (long)BT * H) return;
-  const int h = (int)(idx % H); const long r = idx / H;
-  const uint4* po = reinterpret_cast<const uint4*>(o + r * (long)H * kD + h * kD);
-  const uint4* pd = reinterpret_cast<const uint4*>(dout + r * (long)H * kD + h * kD);
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;      // 16-byte chunk of the [B*T, H*64] matrices; nchunk is a multiple of 8
   float acc = 0.f;
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const uint4 a = po[i], d = pd[i];
+  if (i < nchunk) {
+    const uint4 a = reinterpret_cast<const uint4*>(o)[i], d = reinterpret_cast<const uint4*>(dout)[i];
     const __nv_bfloat162* a2 = reinterpret_cast<const __nv_bfloat162*>(&a);
     const __nv_bfloat162* d2 = reinterpret_cast<const __nv_bfloat162*>(&d);
 #pragma unroll
     for (int k = 0; k < 4; ++k) acc += __low2float(a2[k]) * __low2float(d2[k]) + __high2float(a2[k]) * __high2float(d2[k]);
+    reinterpret_cast<float4*>(dq_acc)[2 * i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4*>(dq_acc)[2 * i + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  const long b = r / T, t = r % T;
-  delta[(b * H + h) * T + t] = acc;
+  acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+  if (i < nchunk && (threadIdx.x & 7) == 0) {
+    const long rh = i >> 3, r = rh / H; const int h = (int)(rh % H);
+    delta[((r / T) * H + h) * T + r % T] = acc;
+  }
 }
 
-// dq (fp32 accumulator [B*T, C]) -> bf16 into columns [0, C) of dqkv [B*T, 3C]
-__global__ void __launch_bounds__(256) k_attn_dq_convert(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, long rows, int C) {
+// dq accumulator tiles (fp32, one [16-byte unit][row] tile of 128 x 64 per (batch*head, query block)) -> bf16 into columns
+// [0, C) of dqkv [B*T, 3C].  One CTA per tile; thread = (row, 32-column half).
+__global__ void __launch_bounds__(256) k_attn_dq_convert(const float* __restrict__ acc, __nv_bfloat16* __restrict__ dqkv, int T, int H) {
   griddep_launch();
   griddep_wait();
-  const long n8 = rows * C / 8;
-  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long)gridDim.x * blockDim.x) {
-    const long r = (i * 8) / C; const int c = (int)((i * 8) % C);
-    const float4 a = *reinterpret_cast<const float4*>(acc + i * 8), b = *reinterpret_cast<const float4*>(acc + i * 8 + 4);
-    *reinterpret_cast<uint4*>(dqkv + r * 3L * C + c) = make_uint4(pack_bf16(a.x, a.y), pack_bf16(a.z, a.w), pack_bf16(b.x, b.y), pack_bf16(b.z, b.w));
+  const int nq = T / kBQ, tile = blockIdx.x, bh = tile / nq, qi = tile % nq, b = bh / H, h = bh % H;
+  const int row = threadIdx.x & (kBQ - 1), half = threadIdx.x >> 7;
+  const uint4* src = reinterpret_cast<const uint4*>(acc + (size_t)tile * (kBQ * kD));
+  __nv_bfloat16* dst = dqkv + ((size_t)b * T + qi * kBQ + row) * (3 * H * kD) + h * kD + half * 32;
+  uint4 v[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) v[u] = src[(half * 8 + u) * kBQ + row];
+#pragma unroll
+  for (int u = 0; u < 8; u += 2) {
+    const float4 x = *reinterpret_cast<const float4*>(&v[u]), y = *reinterpret_cast<const float4*>(&v[u + 1]);
+    *reinterpret_cast<uint4*>(dst + u * 4) = make_uint4(pack_bf16(x.x, x.y), pack_bf16(x.z, x.w), pack_bf16(y.x, y.y), pack_bf16(y.z, y.w));
   }
 }
 
@@ -501,40 +631,50 @@ extern "C" {
 int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cudaStream_t s) {
   if (T % kBQ != 0 || B < 1 || H < 1) { dcp_set_error("attention: T=%d must be a multiple of %d", T, kBQ); return -1; }
   const int C = H * kD;
-  CUtensorMap map;
+  CUtensorMap map, map_out;
   if (encode_bf16_2d(&map, qkv, (long)B * T, 3L * C, 3L * C, kD, kBQ)) return -1;
+  if (encode_bf16_2d(&map_out, out, (long)B * T, C, C, kD, kBQ)) return -1;
   AttnFwdParams p{};
   p.T = T; p.H = H; p.C = C; p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
   const size_t smem = (size_t)kTileBytes * (1 + kRing + 2) + sizeof(AttnBars) + 1024;
   static bool attr = false;
   if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_fwd, dim3(T / kBQ, B * H), dim3(kAttnThreads), smem, s, map, p));
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_fwd, dim3(B * H, T / kBQ), dim3(kAttnThreads), smem, s, map, map_out, p));
   return 0;
 }
 
+static long long* g_attn_trace = nullptr;
+static int g_attn_trace_x = 0, g_attn_trace_y = 0;
+// Debugging aid: device buffer (>= 256 long long) that CTA (bx, by) of the backward kernel fills with clock64 stamps; nullptr = off.
+void dcp_attn_set_trace(void* buf, int bx, int by) { g_attn_trace = static_cast<long long*>(buf); g_attn_trace_x = bx; g_attn_trace_y = by; }
+
 // Backward of dcp_attn_fwd.  dout / out: bf16 [B*T, H*64]; lse from the forward; dqkv: bf16 [B*T, 3*H*64] receives dq | dk | dv
 // in the layout of qkv (what the projection's backward GEMMs consume - no split / merge copies).  Scratch from the caller:
-// delta (B*H*T floats) and dq_acc (B*T*H*64 floats; zeroed here, stream-ordered).
+// delta (B*H*T floats) and dq_acc (B*T*H*64 floats; zeroed here by the delta kernel).
 int dcp_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta, float* dq_acc, int B, int T, int H,
                  cudaStream_t s) {
   if (T % kBQ != 0 || B < 1 || H < 1) { dcp_set_error("attention: T=%d must be a multiple of %d", T, kBQ); return -1; }
   const int C = H * kD;
   const long BT = (long)B * T;
-  CUtensorMap mq, md;
+  CUtensorMap mq, md, mg;
   if (encode_bf16_2d(&mq, qkv, BT, 3L * C, 3L * C, kD, kBQ)) return -1;
   if (encode_bf16_2d(&md, dout, BT, C, C, kD, kBQ)) return -1;
-  DCP_CUDA_CHECK(cudaMemsetAsync(dq_acc, 0, sizeof(float) * BT * C, s));
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_delta, dim3((unsigned)((BT * H + 255) / 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(out),
-                                static_cast<const __nv_bfloat16*>(dout), delta, (int)BT, T, H));
+  if (encode_bf16_2d(&mg, dqkv, BT, 3L * C, 3L * C, kD, kBQ)) return -1;
+  const long nchunk = BT * C / 8;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_delta, dim3((unsigned)((nchunk + 255) / 256)), dim3(256), 0, s, static_cast<const __nv_bfloat16*>(out),
+                                static_cast<const __nv_bfloat16*>(dout), delta, dq_acc, nchunk, T, H));
   AttnBwdParams p{};
-  p.T = T; p.H = H; p.C = C; p.scale = 0.125f; p.scale_log2 = 0.125f * 1.4426950408889634f;
-  p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dqkv = static_cast<__nv_bfloat16*>(dqkv);
-  const size_t smem = (size_t)kTileBytes * 10 + sizeof(AttnBwdBars) + 1024;
+  p.T = T; p.H = H; p.C = C; p.BH = B * H; p.scale = 0.125f; p.scale_log2 = 0.125f * 1.4426950408889634f;
+  p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dqkv = static_cast<__nv_bfloat16*>(dqkv); p.trace = g_attn_trace; p.trace_x = g_attn_trace_x; p.trace_y = g_attn_trace_y;
+  const size_t smem = (size_t)kTileBytes * 14 + sizeof(AttnBwdBars) + 1024;
   static bool attr = false;
   if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_bwd, dim3(T / kBK, B * H), dim3(kAttnThreads), smem, s, mq, md, p));
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_dq_convert, dim3(148 * 4), dim3(256), 0, s, static_cast<const float*>(dq_acc), static_cast<__nv_bfloat16*>(dqkv), BT, C));
+  static int sms = 0;
+  if (sms == 0) { int dev = 0; DCP_CUDA_CHECK(cudaGetDevice(&dev)); DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)); }
+  const int items = B * H * (T / kBK);
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_bwd, dim3(items < sms ? items : sms), dim3(kAttnThreads), smem, s, mq, md, mg, p));
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_dq_convert, dim3((unsigned)(B * H * (T / kBQ))), dim3(256), 0, s, static_cast<const float*>(dq_acc), static_cast<__nv_bfloat16*>(dqkv), T, H));
   return 0;
 }
 
