@@ -38,7 +38,7 @@ def main():
     ap.add_argument("--reps", type=int, default=30)
     ap.add_argument("--once", action="store_true")
     ap.add_argument("--out", default="")
-    ap.add_argument("--trace-cta", default="0,0")
+    ap.add_argument("--trace-cta", default="0,0", help="bx,which: CTA index; which = 0 backward, 1 forward")
     ap.add_argument("--trace", action="store_true", help="clock64 stamps of backward CTA (0, 0): per query block, cycles since the first stamp")
     a = ap.parse_args()
     B, T, H, D = a.B, a.T, a.H, 64
@@ -61,6 +61,8 @@ def main():
         lib.dcp_attn_set_trace(None, 0, 0)
         st = buf.cpu().tolist()
         t0 = min(v for v in st if v)
+        if a.trace_cta.endswith(",1"):
+            print("forward stamps per key block: thr s_full, pass1 done, o updated, P stored; mma p_ready, S(j+1) issued, PV issued")
         names = ["thr: S/dP ready", "thr: P/dS in regs", "thr: dQ(it-1) taken", "thr: P/dS stored", "mma: P/dS ready", "mma: S/dP(it+1) issued", "mma: dV/dK/dQ issued", "thr: dQ complete"]
         for it in range(32):
             print(it, {n: st[it * 8 + k] - t0 for k, n in enumerate(names) if st[it * 8 + k]})

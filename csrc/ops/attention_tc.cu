@@ -42,7 +42,10 @@ struct AttnFwdParams {
   float scale_log2;            // softmax scale * log2(e)
   __nv_bfloat16* out;          // [B*T, C]
   float* lse;                  // [B*H, T] log2-domain log-sum-exp
+  long long* trace;            // debugging: clock64 stamps of CTA (trace_x, 0) (dcp_attn_set_trace), else nullptr
+  int trace_x;
 };
+#define ATTN_FSTAMP(j, k) do { if (p.trace != nullptr && (j) < 32 && blockIdx.x == p.trace_x && blockIdx.y == 0 && lane == 0 && (warp == 0 || warp == 9)) p.trace[(j) * 8 + (k)] = clock64(); } while (0)
 
 // 16-byte unit `u` (0..7) of row r inside a 128-row x 128-byte swizzled chunk
 __device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t u) { return r * 128u + ((u ^ (r & 7u)) << 4); }
@@ -158,7 +161,9 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
     for (int j = 0; j < nkv; ++j) {
       // p_ready(j): the softmax has consumed S_j, written P_j, and read P_{j-1} V_{j-1} out of the other buffer
       mbar_wait(&bars->p_ready, j & 1);
+      ATTN_FSTAMP(j, 4);
       if (j + 1 < nkv) issue_s(j + 1);         // into the other buffer, which is free now
+      ATTN_FSTAMP(j, 5);
       const int t = 2 * j + 1, st = t % kRing, ph = (t / kRing) & 1;
       mbar_wait(&bars->kv_full[st], ph);
       tc_fence_after();
@@ -175,6 +180,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
         umma_commit(&bars->pv_full);
       }
       __syncwarp();
+      ATTN_FSTAMP(j, 6);
     }
   } else {
     // ---- softmax warps: two threads per query row; `half` selects the 64 key columns (and the 32 output columns) of this thread
@@ -193,6 +199,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       const uint32_t tS = tS0 + (j & 1) * 128 + lane_addr + half * 64;
       mbar_wait(&bars->s_full[j & 1], (j >> 1) & 1);
       tc_fence_after();
+      ATTN_FSTAMP(j, 0);
       // pass 1: maximum of this thread's 64 columns (S_j is read again below: TMEM reads are cheap, 64 live registers are not
       // when two CTAs share an SM)
       float mx = -INFINITY;
@@ -209,6 +216,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
         }
       }
       bars->xmax[j & 1][half][row] = mx;
+      ATTN_FSTAMP(j, 1);
       asm volatile("bar.sync 1, 256;" ::: "memory");
       const float m_new = fmaxf(m, fmaxf(mx, bars->xmax[j & 1][half ^ 1][row]) * p.scale_log2);
       const float alpha = ex2(m - m_new);                    // m = -inf on the first block: alpha = 0, o and l are 0 anyway
@@ -225,6 +233,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       }
       m = m_new;
       l *= alpha;
+      ATTN_FSTAMP(j, 2);
       // P = exp2(S * scale - m), bf16, into chunk `half` of the swizzled K-major tile (the previous P V has finished reading it)
       const float2 nm2 = make_float2(-m, -m);
       float2 sum = make_float2(0.f, 0.f);
@@ -252,6 +261,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       tc_fence_before();
       fence_async_smem();                                    // generic-proxy stores -> visible to the tensor core's async proxy
       mbar_arrive(&bars->p_ready);
+      ATTN_FSTAMP(j, 3);
     };
     for (int j = 0; j < qi; ++j) tile(std::false_type{}, j);
     tile(std::true_type{}, qi);
@@ -625,6 +635,15 @@ __global__ void __launch_bounds__(256) k_attn_dq_convert(const float* __restrict
 
 extern "C" {
 
+static long long *g_attn_trace = nullptr, *g_attn_ftrace = nullptr;
+static int g_attn_trace_x = 0, g_attn_trace_y = 0;
+// Debugging aid: device buffer (>= 256 long long) that one CTA fills with clock64 stamps, eight per key / query block (see
+// ATTN_STAMP / ATTN_FSTAMP): CTA bx of the backward kernel, or - which = 1 - CTA (bx, 0) of the forward kernel.  nullptr = off.
+void dcp_attn_set_trace(void* buf, int bx, int which) {
+  (which ? g_attn_ftrace : g_attn_trace) = static_cast<long long*>(buf);
+  g_attn_trace_x = bx; g_attn_trace_y = 0;
+}
+
 // Causal self-attention forward for head dimension 64.  qkv: bf16 [B*T, 3*H*64] (the fused projection: q | k | v, heads inside
 // each third); out: bf16 [B*T, H*64]; lse: fp32 [B*H, T], log2-domain log-sum-exp of the scaled scores (consumed by
 // dcp_attn_bwd).  T must be a multiple of 128.  softmax scale = 1/sqrt(64).
@@ -636,7 +655,7 @@ int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cu
   if (encode_bf16_2d(&map_out, out, (long)B * T, C, C, kD, kBQ)) return -1;
   AttnFwdParams p{};
   p.T = T; p.H = H; p.C = C; p.scale_log2 = 0.125f * 1.4426950408889634f;
-  p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse;
+  p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse; p.trace = g_attn_ftrace; p.trace_x = g_attn_trace_x;
   const size_t smem = (size_t)kTileBytes * (1 + kRing + 2) + sizeof(AttnBars) + 1024;
   static bool attr = false;
   if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
@@ -644,10 +663,6 @@ int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cu
   return 0;
 }
 
-static long long* g_attn_trace = nullptr;
-static int g_attn_trace_x = 0, g_attn_trace_y = 0;
-// Debugging aid: device buffer (>= 256 long long) that CTA (bx, by) of the backward kernel fills with clock64 stamps; nullptr = off.
-void dcp_attn_set_trace(void* buf, int bx, int by) { g_attn_trace = static_cast<long long*>(buf); g_attn_trace_x = bx; g_attn_trace_y = by; }
 
 // Backward of dcp_attn_fwd.  dout / out: bf16 [B*T, H*64]; lse from the forward; dqkv: bf16 [B*T, 3*H*64] receives dq | dk | dv
 // in the layout of qkv (what the projection's backward GEMMs consume - no split / merge copies).  Scratch from the caller:

@@ -24,14 +24,17 @@ typedef struct ConvP { int N, H, W, C, K, R, S, stride, pad, Ho, Wo; } ConvP;
 size_t dcp_coll_oneshot_max_bytes(void* h);
 size_t dcp_coll_bounce_max_bytes(void* h);
 // algo: 1 one-shot, 2 two-shot P2P, 3 NVLS.  In-place on `buf` (n elements).  If `buf` lies inside the
-// symmetric heap the peers read it directly; otherwise it is bounced through the staging area.
+// symmetric heap the peers read it directly; otherwise it is bounced through the channel's staging area, in as many
+// chunks as its size needs.
 int dcp_all_reduce(void* h, void* buf, size_t n, int dtype, int op, int algo, int chan, int max_ctas, cudaStream_t stream);
 int dcp_broadcast(void* h, void* buf, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
 // out: [W][nbytes] contiguous.  root < 0: all_gather; root >= 0: gather to root (out may be null elsewhere).
+// A shard larger than the bounce capacity goes through in chunks (shard p's chunk lands at out + p * nbytes + done).
 int dcp_all_gather(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
-// in: [W][nbytes] contiguous on root.
+// in: [W][nbytes] contiguous on root.  Chunked like dcp_all_gather when a shard exceeds the bounce capacity.
 int dcp_scatter(void* h, const void* in, void* out, size_t nbytes, int root, int chan, int max_ctas, cudaStream_t stream);
 // root < 0: reduce_scatter (in: W*n_out elements, out: n_out).  root >= 0: reduce (in: n_out elements, out on root).
+// A non-symmetric input larger than the bounce capacity is reduced in chunks of the output range.
 int dcp_reduce_scatter(void* h, const void* in, void* out, size_t n_out, int dtype, int op, int root, int chan, int max_ctas, cudaStream_t stream);
 int dcp_send(void* h, const void* in, size_t nbytes, int dst, cudaStream_t stream);
 int dcp_recv(void* h, void* out, size_t nbytes, int src, cudaStream_t stream);
@@ -94,6 +97,19 @@ int64_t dcp_store_check(void* h, const char* key);
 int64_t dcp_store_delete(void* h, const char* key);
 int64_t dcp_store_num_keys(void* h);
 
+/* ---- csrc/ops/attention_tc.cu ---- */
+// Debugging aid: device buffer (>= 256 long long) that one CTA fills with clock64 stamps, eight per key / query block (see
+// ATTN_STAMP / ATTN_FSTAMP): CTA bx of the backward kernel, or - which = 1 - CTA (bx, 0) of the forward kernel.  nullptr = off.
+void dcp_attn_set_trace(void* buf, int bx, int which);
+// Causal self-attention forward for head dimension 64.  qkv: bf16 [B*T, 3*H*64] (the fused projection: q | k | v, heads inside
+// each third); out: bf16 [B*T, H*64]; lse: fp32 [B*H, T], log2-domain log-sum-exp of the scaled scores (consumed by
+// dcp_attn_bwd).  T must be a multiple of 128.  softmax scale = 1/sqrt(64).
+int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cudaStream_t s);
+// Backward of dcp_attn_fwd.  dout / out: bf16 [B*T, H*64]; lse from the forward; dqkv: bf16 [B*T, 3*H*64] receives dq | dk | dv
+// in the layout of qkv (what the projection's backward GEMMs consume - no split / merge copies).  Scratch from the caller:
+// delta (B*H*T floats) and dq_acc (B*T*H*64 floats; zeroed here by the delta kernel).
+int dcp_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta, float* dq_acc, int B, int T, int H, cudaStream_t s);
+
 /* ---- csrc/ops/batchnorm.cu ---- */
 // scratch: >= 4*C doubles.  Phase 1 of forward: zero + accumulate (sum, sumsq).
 int dcp_bn_stats(const void* x, void* scratch, long M, int C, int dtype, cudaStream_t s);
@@ -105,9 +121,13 @@ int dcp_bn_bwd_reduce(const void* x, const void* y, const void* dy, const float*
 int dcp_bn_bwd_apply(const void* x, const void* y, const void* dy, void* dx, const float* mean, const float* rstd, const float* gamma, const void* scratch, float* dgamma, float* dbeta, long M, int C, double count, int relu, int dtype, cudaStream_t s);
 
 /* ---- csrc/ops/conv_flat_tc.cu ---- */
-// in: [P, Cin] fp32 flat pixels (pitch W, HW pixels per image); wmat: [Cout][taps*Cin] fp32 (tap-major columns);
-// off[t]: flat row shift of tap t.  mode 0: out = (h < Hv && w < Wv) ? relu(acc + bias) : 0;  mode 1: out = mask > 0 ? acc : 0.
 int dcp_conv_flat_tc(const float* in, const float* wmat, float* out, const float* bias, const float* mask, long P, int Cin, int Cout, int taps, const int* off, int W, int HW, int Hv, int Wv, int mode, int num_ctas, cudaStream_t s);
+// Convolution + bias + ReLU + 2x2 max-pool + channel dropout in ONE kernel (K3-K6 of the reference model, ref:main.py:34-37): the
+// conv output never reaches memory.  pooled: [N][Cout][Hv/2][Wv/2] fp32 (the NCHW-flattened order fc1 consumes, ref:main.py:38-39),
+// arg: one byte per pooled element = position of the maximum in its window (for the backward pass).  Dropout drops whole channels
+// of an image with probability drop_p (scaled by 1/(1-p)), Philox stream `stream` + step counter, regenerated - not stored - in
+// backward.  Needs Hv % 4 == 0, Wv even, 4 * W <= 128 flat pixels, Cout == 64.
+int dcp_conv_flat_pool_tc(const float* in, const float* wmat, float* pooled, void* arg, const float* bias, long P, int Cin, int Cout, int taps, const int* off, int W, int HW, int Hv, int Wv, float drop_p, unsigned long long seed, unsigned long long stream, const void* step, int training, int num_ctas, cudaStream_t s);
 
 /* ---- csrc/ops/conv_linear_simt.cu ---- */
 int dcp_conv2d_fwd_simt(const void* x, const void* w, const void* bias, void* y, ConvP p, int relu, int dtype, cudaStream_t s);
@@ -131,6 +151,22 @@ int dcp_cast_from_f32(const float* in, void* out, long n, int dtype, cudaStream_
 // Exactly num_ctas partials are written (CTAs without pixels write zeros).
 int dcp_conv_wgrad_flat_tc(const float* x, const float* dy, float* scratch, long P, int Cout, int W, int num_ctas, cudaStream_t s);
 
+/* ---- csrc/ops/convnet_dp.cu ---- */
+int dcp_dp_nvls_mode(int set);
+// Payload path of the fused data-parallel tail: 1 = multimem.st through NVSwitch, 0 = one store per peer (default).
+int dcp_dp_set_nvls(int on);
+// Finish a split-K reduction (scratch: [nsplit][n] floats, n % 4 == 0) and push the n sums into floats
+// [elem_off, elem_off + n) of this rank's slot in every rank's payload block; the last CTA signals (chan, blk).
+// Nothing is written locally: dcp_dp_tail produces the averaged gradients.  ticket: one zeroed u32 in device memory
+// owned by the caller.  step: device int64 counter that holds the same value on every rank when the kernel runs.
+int dcp_splitk_reduce_push(void* h, const float* scratch, int nsplit, long n, void* payload, unsigned slot_elems, unsigned elem_off, int chan, int blk, const void* step, void* ticket, int pull, cudaStream_t s);
+// Consumer of the pushed gradients: for the `ntensors` rows of the optimizer table (param, grad, state1, state2, numel; every
+// grad a view into the bucket that starts at `bucket`, in bucket order = slot order) wait for the `nsig` producers
+// (signal words blks[i] on `chan`) of every rank, average the W slots, store the averaged gradient and apply the update.
+// row_sig[i] (i < ntensors <= 16) names the producer (index into blks) whose signal guards row i's gradients.
+// kind: 0 Adadelta, 1 SGD, 2 Adam; hp: the optimizer's device hyper-parameter block (dcp_optim_advance'd by the caller).
+int dcp_dp_tail(void* h, const void* table, int ntensors, long long max_numel, const float* hp, int kind, const void* bucket, void* payload, unsigned slot_elems, int chan, const int* blks, int nsig, const int* row_sig, const void* step, int pull, cudaStream_t s);
+
 /* ---- csrc/ops/convnet_fused.cu ---- */
 int dcp_convnet_conv1_fwd(const float* x, const float* w, const float* b, float* a1, int N, cudaStream_t s);
 int dcp_convnet_pool_fwd(const float* a2, float* pooled, void* arg, int N, float p, unsigned long long seed, unsigned long long stream, const void* step, int training, cudaStream_t s);
@@ -138,10 +174,30 @@ int dcp_convnet_pool_bwd(const float* dpooled, const float* pooled, const void* 
 // dw1 / db1 are overwritten.  The partial-sum table is one per device: two of these launches running at the same time
 // (different streams) would race on it.
 int dcp_convnet_conv1_wgrad(const float* dz1, const float* x, float* dw1, float* db1, int N, cudaStream_t s);
+int dcp_convnet_conv1_wgrad_allreduce(void* h, const float* dz1, const float* x, float* dw1, float* db1, int N, void* payload, int chan, int blk, cudaStream_t s);
+// Push-only variant for the fused data-parallel tail (ops/dp_push.cuh, convnet_dp.cu): the 320 sums go into this rank's slot
+// (floats [elem_off, elem_off + 320) in bucket order: dw1 then db1) of every rank's payload block, followed by one signal per
+// rank on (chan, blk); dw1 / db1 are NOT written - dcp_dp_tail produces the averaged gradients.  ws: caller-owned scratch of
+// 4 + 148 * 320 floats (ticket word + per-CTA partial sums), zero before the first call; one per concurrent user.
+int dcp_convnet_conv1_wgrad_push(void* h, const float* dz1, const float* x, int N, void* payload, unsigned slot_elems, unsigned elem_off, int chan, int blk, const void* step, void* ws, cudaStream_t s);
+// conv1's weight-gradient, its data-parallel average and its optimizer update in ONE kernel (struct C1LL above).  ll_block: a
+// region of the symmetric heap holding 2 * world * 320 * 8 bytes, at the same offset on every rank, zeroed before first use and
+// used by nothing else; rows: two rows of the optimizer's device pointer table - conv1.weight, conv1.bias - whose grad pointers
+// receive the averaged gradient; hp / kind as for dcp_optim_step (dcp_optim_advance'd by the caller); step: device int64
+// counter holding the same (non-zero, increasing) value on every rank when the kernel runs; ws: 4 + 148 * 320 floats of
+// caller-owned scratch, zero before the first call.
+int dcp_convnet_conv1_wgrad_ll(void* h, const float* dz1, const float* x, int N, void* ll_block, const void* rows, const float* hp, int kind, const void* step, void* ws, cudaStream_t s);
 // Fused head (see above).  N <= 128.  logits_out (log-probabilities [N,10]) may be null; dbias1 ([128], may be null)
 // receives the column sums of dh1, i.e. the bias gradient of the Linear layer in front.  All gradient outputs are
 // fully overwritten.  Training mode only (batch statistics); p2 = dropout probability of the second dropout.
 int dcp_convnet_head(const float* h1, const void* target, const float* gamma, const float* beta, float* run_mean, float* run_var, void* nbt, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
+// The same kernel inside a data-parallel job: `bn_block` is a 1032-byte block of symmetric heap `h` laid out
+// [running_mean 128 f32][running_var 128 f32][num_batches_tracked i64], allocated at the same offset on every rank.  Rank 0
+// computes the new running statistics from its batch and writes them into EVERY rank's block (peer stores over NVLink from
+// inside the kernel); the other ranks do not touch theirs.  That is what DistributedDataParallel's per-forward buffer
+// broadcast from rank 0 amounts to - without a collective launch, a side stream or a join in front of the head.
+// A rank may read the block after any later cross-rank synchronisation of the step (the gradient exchange is one).
+int dcp_convnet_head_dp(void* h, const float* h1, const void* target, const float* gamma, const float* beta, void* bn_block, const float* w2, const float* b2, float* loss, float* logits_out, float* dh1, float* dgamma, float* dbeta, float* dw2, float* db2, float* dbias1, int N, float eps, float momentum, float p2, unsigned long long seed, unsigned long long stream_id, const void* step, int training, cudaStream_t s);
 
 /* ---- csrc/ops/elementwise.cu ---- */
 // dy: channels-last [N, Ho, Wo, K]; up: [N, Hup, Wup, K] (K * sizeof(element) must be a multiple of 16)
@@ -158,6 +214,9 @@ int dcp_gap_bwd(const void* dy, void* dx, int N, int HW, int C, int dtype, cudaS
 int dcp_correct_count(const void* x, const void* target, void* count, int M, int C, int dtype, cudaStream_t s);
 
 /* ---- csrc/ops/gemm_bf16_persistent.cu ---- */
+// Hand the GEMM a scratch buffer (device memory, 16-byte aligned) for the tail split of two-wave problems; nullptr / 0 disables it.
+// GEMMs that use it must not overlap on different streams.
+int dcp_gemm_set_workspace(void* ws, size_t bytes);
 // bf16 operands; see gemm_tc.cu::dcp_tc_gemm_ex for the meaning of the major flags.  ksplit > 1: `out` is a
 // [ksplit][M * ldc] fp32 scratch that receives partial tiles (finish with dcp_splitk_reduce, which also adds the bias).
 // K must be a multiple of 64; MN-major operands need their row count (M resp. N) to be a multiple of 8 (TMA stride rule).
@@ -242,6 +301,17 @@ const struct DcpDevCtx* dcp_symm_ctx(void* h);
 int dcp_symm_error_flag(void* h);
 void dcp_symm_clear_error(void* h);
 void dcp_symm_destroy(void* h);
+// Create `world` heaps of heap_bytes each on `device`, every one seeing the others as its peers (plain device pointers: same
+// process, same GPU), no multicast.  Returns the group; dcp_emu_rank(group, r) is an ordinary heap handle for every other
+// entry point of this library - except that collectives issued on it are deferred until dcp_emu_flush().
+void* dcp_emu_create(int world, int device, size_t heap_bytes, double timeout_s, size_t p2p_slot_bytes, size_t staging_bytes);
+void* dcp_emu_rank(void* group, int r);
+int dcp_emu_pending(void* group);
+// Launch everything the ranks have queued: slot i of every rank becomes ONE cooperative kernel of (grid, world) CTAs on
+// `stream`.  The ranks must have queued the same collectives in the same order (same kernel, same grid) - as they would have
+// to on N GPUs; point-to-point slots may be empty on ranks that take no part.  Returns -1 (and drops the queue) on a mismatch.
+int dcp_emu_flush(void* group, cudaStream_t stream);
+void dcp_emu_destroy(void* group);
 
 /* ---- hand-maintained additions ---- */
 
