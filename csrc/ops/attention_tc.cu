@@ -17,6 +17,7 @@
 //                          lives in REGISTERS (32 floats per thread): each PV_j is added from TMEM and rescaled there, so
 //                          TMEM never has to be rewritten.  Online softmax in the log2 domain.
 // The row-wise log-sum-exp (log2 domain) is saved for the backward pass.
+#include <cstdlib>
 #include <type_traits>
 #include <cudaTypedefs.h>
 
@@ -31,21 +32,21 @@ constexpr int kTileBytes = kBQ * kD * 2;            // 16 KB: one 128 x 64 bf16 
 constexpr int kRing = 3;                            // K / V tiles in flight
 
 struct __align__(16) AttnBars {
-  uint64_t q_full, kv_full[kRing], kv_empty[kRing], s_full[2], p_ready, pv_full;
+  uint64_t q_full, q_empty, kv_full[kRing], kv_empty[kRing], s_full[2], o_taken, p_ready, pv_full;
   uint32_t tmem_base;
   float xmax[2][2][kBQ];       // [block parity][column half][row]: row maxima of the two column halves
   float xsum[kBQ];             // second half's row sum, for the final normalisation
 };
 
 struct AttnFwdParams {
-  int T, H, C;                 // sequence length, heads, model width (H * 64)
+  int T, H, C, BH;             // sequence length, heads, model width (H * 64), batch * heads
   float scale_log2;            // softmax scale * log2(e)
   __nv_bfloat16* out;          // [B*T, C]
   float* lse;                  // [B*H, T] log2-domain log-sum-exp
   long long* trace;            // debugging: clock64 stamps of CTA (trace_x, 0) (dcp_attn_set_trace), else nullptr
   int trace_x;
 };
-#define ATTN_FSTAMP(j, k) do { if (p.trace != nullptr && (j) < 32 && blockIdx.x == p.trace_x && blockIdx.y == 0 && lane == 0 && (warp == 0 || warp == 9)) p.trace[(j) * 8 + (k)] = clock64(); } while (0)
+#define ATTN_FSTAMP(j, k) do { if (p.trace != nullptr && (j) < 32 && blockIdx.x == p.trace_x && lane == 0 && (warp == 0 || warp == 9)) p.trace[(j) * 8 + (k)] = clock64(); } while (0)
 
 // 16-byte unit `u` (0..7) of row r inside a 128-row x 128-byte swizzled chunk
 __device__ __forceinline__ uint32_t swz(uint32_t r, uint32_t u) { return r * 128u + ((u ^ (r & 7u)) << 4); }
@@ -85,6 +86,13 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
   return *reinterpret_cast<uint32_t*>(&v);
 }
 
+// the r-th item of CTA c out of G: rounds alternate direction (c, 2G-1-c, 2G+c, ...); items are ordered heaviest first, so
+// every CTA collects a similar number of tiles
+__device__ __forceinline__ int attn_item(int r, int c, int G) { return r * G + ((r & 1) ? G - 1 - c : c); }
+
+// PERSISTENT: two CTAs per SM, each walking its list of (query block, batch*head) items; the key blocks of consecutive items
+// form ONE stream (counter g) for all three roles, so the producer fetches the next item's Q / K_0 while the last block's
+// softmax runs and the MMA warp issues its first S ahead of the current item's last P V.
 __global__ void __launch_bounds__(kAttnThreads, 2)
 k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ CUtensorMap map_out, const AttnFwdParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -94,21 +102,18 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   uint8_t* p_smem = kv_smem + kRing * kTileBytes;           // 32 KB: P as two 64-column K-major chunks
   AttnBars* bars = reinterpret_cast<AttnBars*>(p_smem + 2 * kTileBytes);
   const int warp = warp_idx_uniform(), lane = threadIdx.x & 31;
-  // grid (batch*head, query blocks): blocks are handed out x-fastest, so ALL the heavy (late) query blocks run first and the
-  // one-tile blocks fill the tail - longest-first scheduling of unequal work
-  const int qi = (int)gridDim.y - 1 - (int)blockIdx.y;
-  const int bh = blockIdx.x, b = bh / p.H, h = bh % p.H;
-  const int row0 = b * p.T + qi * kBQ;                      // first row of this query block in the [B*T, 3C] matrix
-  const int nkv = qi + 1;
+  const int nq = p.T / kBQ, nitems = nq * p.BH, G = gridDim.x, cta = blockIdx.x;
+  // item w: query block nq - 1 - w / BH (late = heavy query blocks first), batch*head w % BH
 
+  ATTN_FSTAMP(30, 0);
   griddep_launch();
-  if (warp == 8 && lane == 0) tma_prefetch_desc(&map_qkv);
+  if (warp == 8 && lane == 0) { tma_prefetch_desc(&map_qkv); tma_prefetch_desc(&map_out); }
   if (warp == 9) {
     if (lane == 0) {
-      mbar_init(&bars->q_full, 1);
+      mbar_init(&bars->q_full, 1); mbar_init(&bars->q_empty, 1);
       for (int i = 0; i < kRing; ++i) { mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 1); }
       for (int i = 0; i < 2; ++i) mbar_init(&bars->s_full[i], 1);
-      mbar_init(&bars->p_ready, 256); mbar_init(&bars->pv_full, 1);
+      mbar_init(&bars->o_taken, 256); mbar_init(&bars->p_ready, 256); mbar_init(&bars->pv_full, 1);
       mbar_fence_init();
     }
     __syncwarp();
@@ -119,138 +124,173 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *((volatile uint32_t*)&bars->tmem_base);
-  const uint32_t tS0 = tmem;                                // S_j (128 columns) and later P_j V_j (64 columns) in buffer j & 1
+  ATTN_FSTAMP(30, 1);
+  const uint32_t tS0 = tmem;                                // S_g (128 columns) and later P_g V_g (64 columns) in buffer g & 1
 
   if (warp == 8) {
     // ---- TMA producer
-    if (lane == 0) {
-      mbar_expect_tx(&bars->q_full, kTileBytes);
-      tma_load_2d(q_smem, &map_qkv, &bars->q_full, h * kD, row0);
-    }
-    __syncwarp();
-    for (int t = 0; t < 2 * nkv; ++t) {                     // tile t: K_j for t = 2 j, V_j for t = 2 j + 1
-      const int st = t % kRing, ph = (t / kRing) & 1;
-      mbar_wait(&bars->kv_empty[st], ph ^ 1);
+    int t = 0;                                              // K / V tile stream: K of block g is tile 2 g, V is tile 2 g + 1
+    for (int n = 0, w = attn_item(0, cta, G); w < nitems; ++n, w = attn_item(n, cta, G)) {
+      const int qi = nq - 1 - w / p.BH, bh = w % p.BH, b = bh / p.H, h = bh % p.H;
+      mbar_wait(&bars->q_empty, (n & 1) ^ 1);               // the previous item's last S has been computed
       if (lane == 0) {
-        mbar_expect_tx(&bars->kv_full[st], kTileBytes);
-        tma_load_2d(kv_smem + st * kTileBytes, &map_qkv, &bars->kv_full[st], ((t & 1) + 1) * p.C + h * kD, b * p.T + (t >> 1) * kBK);
+        mbar_expect_tx(&bars->q_full, kTileBytes);
+        tma_load_2d(q_smem, &map_qkv, &bars->q_full, h * kD, b * p.T + qi * kBQ);
       }
       __syncwarp();
+      for (int tt = 0; tt < 2 * (qi + 1); ++tt, ++t) {
+        const int st = t % kRing, ph = (t / kRing) & 1;
+        mbar_wait(&bars->kv_empty[st], ph ^ 1);
+        if (lane == 0) {
+          mbar_expect_tx(&bars->kv_full[st], kTileBytes);
+          tma_load_2d(kv_smem + st * kTileBytes, &map_qkv, &bars->kv_full[st], ((tt & 1) + 1) * p.C + h * kD, b * p.T + (tt >> 1) * kBK);
+        }
+        __syncwarp();
+      }
     }
   } else if (warp == 9) {
     // ---- MMA issuer
     const uint32_t idesc_s = make_idesc(false, false, false, kBQ, kBK);          // S: A = Q (K-major), B = K (K-major)
     const uint32_t idesc_pv = make_idesc(false, false, true, kBQ, kD);           // PV: A = P (K-major), B = V (MN-major)
     const uint32_t qa = smem_u32(q_smem), pa = smem_u32(p_smem);
-    auto issue_s = [&](int j) {
-      const int t = 2 * j, st = t % kRing, ph = (t / kRing) & 1;
+    // S of stream block g; `last`: the item's last key block - Q may be replaced once this product is done
+    auto issue_s = [&](int g, bool last) {
+      const int t = 2 * g, st = t % kRing, ph = (t / kRing) & 1;
       mbar_wait(&bars->kv_full[st], ph);
       tc_fence_after();
       if (elect_one()) {
         const uint32_t ka = smem_u32(kv_smem + st * kTileBytes);
 #pragma unroll
         for (int k = 0; k < kD / 16; ++k)
-          umma<false>(tS0 + (j & 1) * 128, make_smem_desc(qa + k * 32, 0, 1024), make_smem_desc(ka + k * 32, 0, 1024), idesc_s, k > 0);
-        umma_commit(&bars->kv_empty[st]);      // K_j consumed
-        umma_commit(&bars->s_full[j & 1]);
+          umma<false>(tS0 + (g & 1) * 128, make_smem_desc(qa + k * 32, 0, 1024), make_smem_desc(ka + k * 32, 0, 1024), idesc_s, k > 0);
+        umma_commit(&bars->kv_empty[st]);      // K consumed
+        umma_commit(&bars->s_full[g & 1]);
+        if (last) umma_commit(&bars->q_empty);
       }
       __syncwarp();
     };
-    mbar_wait(&bars->q_full, 0);
-    issue_s(0);
-    for (int j = 0; j < nkv; ++j) {
-      // p_ready(j): the softmax has consumed S_j, written P_j, and read P_{j-1} V_{j-1} out of the other buffer
-      mbar_wait(&bars->p_ready, j & 1);
-      ATTN_FSTAMP(j, 4);
-      if (j + 1 < nkv) issue_s(j + 1);         // into the other buffer, which is free now
-      ATTN_FSTAMP(j, 5);
-      const int t = 2 * j + 1, st = t % kRing, ph = (t / kRing) & 1;
-      mbar_wait(&bars->kv_full[st], ph);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t va = smem_u32(kv_smem + st * kTileBytes);
+    int g = 0;
+    if (attn_item(0, cta, G) < nitems) {
+      mbar_wait(&bars->q_full, 0);
+      issue_s(0, nq - 1 - attn_item(0, cta, G) / p.BH == 0);
+    }
+    for (int n = 0, w = attn_item(0, cta, G); w < nitems; ++n, w = attn_item(n, cta, G)) {
+      const int nkv = nq - w / p.BH;
+      const int w_next = attn_item(n + 1, cta, G);
+      for (int j = 0; j < nkv; ++j, ++g) {
+        // o_taken(g): the softmax threads have read P_{g-1} V_{g-1} out of the other buffer (early in block g, before its
+        // exponentials): the next S (of this item or of the next one) goes there now and is ready when they finish block g
+        mbar_wait(&bars->o_taken, g & 1);
+        tc_fence_after();
+        ATTN_FSTAMP(g, 4);
+        if (j + 1 < nkv) issue_s(g + 1, j + 2 == nkv);
+        else if (w_next < nitems) { mbar_wait(&bars->q_full, (n + 1) & 1); issue_s(g + 1, nq - 1 - w_next / p.BH == 0); }
+        ATTN_FSTAMP(g, 5);
+        // p_ready(g): S_g has been consumed and P_g written
+        mbar_wait(&bars->p_ready, g & 1);
+        const int t = 2 * g + 1, st = t % kRing, ph = (t / kRing) & 1;
+        mbar_wait(&bars->kv_full[st], ph);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t va = smem_u32(kv_smem + st * kTileBytes);
 #pragma unroll
-        for (int k = 0; k < kBK / 16; ++k) {
-          // A: P chunk (k / 4) of 64 kv columns, 32 bytes per K step inside it; B: V rows 16 k .. 16 k + 15 (MN-major: 2048 B per step)
-          const uint64_t da = make_smem_desc(pa + (k >> 2) * kTileBytes + (k & 3) * 32, 0, 1024);
-          const uint64_t db = make_smem_desc(va + k * 2048, kBK * 128, 1024);
-          umma<false>(tS0 + (j & 1) * 128, da, db, idesc_pv, k > 0);
+          for (int k = 0; k < kBK / 16; ++k) {
+            // A: P chunk (k / 4) of 64 kv columns, 32 bytes per K step inside it; B: V rows 16 k .. 16 k + 15 (MN-major: 2048 B per step)
+            const uint64_t da = make_smem_desc(pa + (k >> 2) * kTileBytes + (k & 3) * 32, 0, 1024);
+            const uint64_t db = make_smem_desc(va + k * 2048, kBK * 128, 1024);
+            umma<false>(tS0 + (g & 1) * 128, da, db, idesc_pv, k > 0);
+          }
+          umma_commit(&bars->kv_empty[st]);      // V consumed
+          umma_commit(&bars->pv_full);
         }
-        umma_commit(&bars->kv_empty[st]);      // V_j consumed
-        umma_commit(&bars->pv_full);
+        __syncwarp();
+        ATTN_FSTAMP(g, 6);
       }
-      __syncwarp();
-      ATTN_FSTAMP(j, 6);
     }
   } else {
     // ---- softmax warps: two threads per query row; `half` selects the 64 key columns (and the 32 output columns) of this thread
     const int half = warp >> 2, lg = warp & 3;
     const int row = lg * 32 + lane;                          // row inside the block = TMEM lane
     const uint32_t lane_addr = (uint32_t)(lg * 32) << 16;
-    float2 o[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) o[i] = make_float2(0.f, 0.f);
-    float m = -INFINITY, l = 0.f;
     const float2 sc2 = make_float2(p.scale_log2, p.scale_log2);
     uint8_t* chunk = p_smem + half * kTileBytes;
-    // one key block; kDiag: the block on the diagonal, the only one that needs the causal mask
-    auto tile = [&](auto dtag, int j) {
+    float2 o[16];
+    float m, l;
+    int g = 0;
+    // one key block (stream index g, block j of its item); kDiag: the block on the diagonal, the only one that needs the causal mask
+    auto tile = [&](auto dtag, int j, bool first_of_later_item) {
       constexpr bool kDiag = decltype(dtag)::value;
-      const uint32_t tS = tS0 + (j & 1) * 128 + lane_addr + half * 64;
-      mbar_wait(&bars->s_full[j & 1], (j >> 1) & 1);
+      const uint32_t tS = tS0 + (g & 1) * 128 + lane_addr + half * 64;
+      mbar_wait(&bars->s_full[g & 1], (g >> 1) & 1);
       tc_fence_after();
-      ATTN_FSTAMP(j, 0);
-      // pass 1: maximum of this thread's 64 columns (S_j is read again below: TMEM reads are cheap, 64 live registers are not
+      ATTN_FSTAMP(g, 0);
+      // pass 1: maximum of this thread's 64 columns (S is read again below: TMEM reads are cheap, 64 live registers are not
       // when two CTAs share an SM)
+      // On the diagonal block the 32-column chunk hc = 2 half + c of warp group lg (rows 32 lg ..) is entirely below the
+      // diagonal for hc < lg, entirely above it for hc > lg (skipped: nothing to read, P = 0) and cut by it for hc == lg
+      // (column i of the chunk is visible to lane >= i) - all warp-uniform, so the mask costs one chunk in four.
       float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
+        const int hc = half * 2 + c;
+        if (kDiag && hc > lg) continue;
         uint32_t r[32];
         tmem_ld32(tS + c * 32, r);
         tmem_ld_wait();
+        if (kDiag && hc == lg) {
 #pragma unroll
-        for (int i = 0; i < 32; i += 2) {
-          float a = __uint_as_float(r[i]), b2 = __uint_as_float(r[i + 1]);
-          if (kDiag) { const int col = half * 64 + c * 32 + i; if (col > row) a = -INFINITY; if (col + 1 > row) b2 = -INFINITY; }
-          mx = fmax3(mx, a, b2);
+          for (int i = 0; i < 32; i += 2)
+            mx = fmax3(mx, i > lane ? -INFINITY : __uint_as_float(r[i]), i + 1 > lane ? -INFINITY : __uint_as_float(r[i + 1]));
+        } else {
+#pragma unroll
+          for (int i = 0; i < 32; i += 2) mx = fmax3(mx, __uint_as_float(r[i]), __uint_as_float(r[i + 1]));
         }
       }
-      bars->xmax[j & 1][half][row] = mx;
-      ATTN_FSTAMP(j, 1);
+      bars->xmax[g & 1][half][row] = mx;
+      ATTN_FSTAMP(g, 1);
+      if (first_of_later_item && threadIdx.x == 0) bulk_wait_read0();   // the previous item's output tile has left the P buffer
       asm volatile("bar.sync 1, 256;" ::: "memory");
-      const float m_new = fmaxf(m, fmaxf(mx, bars->xmax[j & 1][half ^ 1][row]) * p.scale_log2);
+      const float m_new = fmaxf(m, fmaxf(mx, bars->xmax[g & 1][half ^ 1][row]) * p.scale_log2);
       const float alpha = ex2(m - m_new);                    // m = -inf on the first block: alpha = 0, o and l are 0 anyway
       const float2 al2 = make_float2(alpha, alpha);
       // previous block's P V arrives: add it, then rescale everything to the new maximum
       if (j > 0) {
-        mbar_wait(&bars->pv_full, (j - 1) & 1);
+        mbar_wait(&bars->pv_full, (g - 1) & 1);
         tc_fence_after();
         uint32_t r[32];
-        tmem_ld32(tS0 + ((j - 1) & 1) * 128 + lane_addr + half * 32, r);
+        tmem_ld32(tS0 + ((g - 1) & 1) * 128 + lane_addr + half * 32, r);
         tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 16; ++i) o[i] = fmul2(fadd2(o[i], u2f2(r[2 * i], r[2 * i + 1])), al2);
       }
+      tc_fence_before();
+      mbar_arrive(&bars->o_taken);
       m = m_new;
       l *= alpha;
-      ATTN_FSTAMP(j, 2);
+      ATTN_FSTAMP(g, 2);
       // P = exp2(S * scale - m), bf16, into chunk `half` of the swizzled K-major tile (the previous P V has finished reading it)
       const float2 nm2 = make_float2(-m, -m);
       float2 sum = make_float2(0.f, 0.f);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
+        const int hc = half * 2 + c;
+        if (kDiag && hc > lg) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) *reinterpret_cast<uint4*>(chunk + swz(row, c * 4 + u)) = make_uint4(0u, 0u, 0u, 0u);
+          continue;
+        }
         uint32_t r[32];
         tmem_ld32(tS + c * 32, r);
         tmem_ld_wait();
+        const bool cut = kDiag && hc == lg;
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           uint32_t pk[4];
 #pragma unroll
           for (int i = 0; i < 8; i += 2) {
-            const int cc = half * 64 + c * 32 + u * 8 + i;
             const float2 x = ffma2(u2f2(r[u * 8 + i], r[u * 8 + i + 1]), sc2, nm2);
             float2 e = make_float2(ex2(x.x), ex2(x.y));
-            if (kDiag) { if (cc > row) e.x = 0.f; if (cc + 1 > row) e.y = 0.f; }
+            if (kDiag) { if (cut && u * 8 + i > lane) e.x = 0.f; if (cut && u * 8 + i + 1 > lane) e.y = 0.f; }
             sum = fadd2(sum, e);
             pk[i >> 1] = pack_bf16(e.x, e.y);
           }
@@ -261,44 +301,53 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       tc_fence_before();
       fence_async_smem();                                    // generic-proxy stores -> visible to the tensor core's async proxy
       mbar_arrive(&bars->p_ready);
-      ATTN_FSTAMP(j, 3);
+      ATTN_FSTAMP(g, 3);
+      ++g;
     };
-    for (int j = 0; j < qi; ++j) tile(std::false_type{}, j);
-    tile(std::true_type{}, qi);
-    // last block's P V
-    mbar_wait(&bars->pv_full, (nkv - 1) & 1);
-    tc_fence_after();
-    {
-      uint32_t r[32];
-      tmem_ld32(tS0 + ((nkv - 1) & 1) * 128 + lane_addr + half * 32, r);
-      tmem_ld_wait();
+    for (int n = 0, w = attn_item(0, cta, G); w < nitems; ++n, w = attn_item(n, cta, G)) {
+      const int qi = nq - 1 - w / p.BH, bh = w % p.BH, b = bh / p.H, h = bh % p.H;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) o[i] = fadd2(o[i], u2f2(r[2 * i], r[2 * i + 1]));
-    }
-    if (half == 1) bars->xsum[row] = l;
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    if (half == 0) l += bars->xsum[row];
-    else l += 0.f;
-    if (half == 0) bars->xsum[row] = l;
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    l = bars->xsum[row];
-    const float inv = 1.f / l;
-    // the output tile goes out through the copy engine (staged in the P tile, which the last P V has finished reading): a
-    // thread's 64 bytes per row would otherwise be 32 separate transactions per store instruction
+      for (int i = 0; i < 16; ++i) o[i] = make_float2(0.f, 0.f);
+      m = -INFINITY; l = 0.f;
+      for (int j = 0; j < qi; ++j) tile(std::false_type{}, j, n > 0 && j == 0);
+      tile(std::true_type{}, qi, n > 0 && qi == 0);
+      // last block's P V
+      mbar_wait(&bars->pv_full, (g - 1) & 1);
+      tc_fence_after();
+      {
+        uint32_t r[32];
+        tmem_ld32(tS0 + ((g - 1) & 1) * 128 + lane_addr + half * 32, r);
+        tmem_ld_wait();
 #pragma unroll
-    for (int i = 0; i < 16; i += 4) {
-      uint4 v = make_uint4(pack_bf16(o[i].x * inv, o[i].y * inv), pack_bf16(o[i + 1].x * inv, o[i + 1].y * inv), pack_bf16(o[i + 2].x * inv, o[i + 2].y * inv),
-                           pack_bf16(o[i + 3].x * inv, o[i + 3].y * inv));
-      *reinterpret_cast<uint4*>(p_smem + swz(row, half * 4 + (i >> 2))) = v;
+        for (int i = 0; i < 16; ++i) o[i] = fadd2(o[i], u2f2(r[2 * i], r[2 * i + 1]));
+      }
+      tc_fence_before();
+      if (half == 1) bars->xsum[row] = l;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (half == 0) { l += bars->xsum[row]; bars->xsum[row] = l; }      // only this thread touches xsum[row] between the barriers
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      l = bars->xsum[row];
+      const float inv = 1.f / l;
+      // the output tile goes out through the copy engine (staged in the P tile, which the last P V has finished reading): a
+      // thread's 64 bytes per row would otherwise be 32 separate transactions per store instruction
+#pragma unroll
+      for (int i = 0; i < 16; i += 4) {
+        uint4 v = make_uint4(pack_bf16(o[i].x * inv, o[i].y * inv), pack_bf16(o[i + 1].x * inv, o[i + 1].y * inv), pack_bf16(o[i + 2].x * inv, o[i + 2].y * inv),
+                             pack_bf16(o[i + 3].x * inv, o[i + 3].y * inv));
+        *reinterpret_cast<uint4*>(p_smem + swz(row, half * 4 + (i >> 2))) = v;
+      }
+      fence_async_smem();
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) { tma_store_2d(&map_out, p_smem, h * kD, b * p.T + qi * kBQ); bulk_commit(); }
+      if (half == 0) p.lse[(size_t)bh * p.T + qi * kBQ + row] = m + log2f(l);
     }
-    fence_async_smem();
-    asm volatile("bar.sync 1, 256;" ::: "memory");
-    if (threadIdx.x == 0) { tma_store_2d(&map_out, p_smem, h * kD, row0); bulk_commit(); bulk_wait_read0(); }
-    if (half == 0) p.lse[(size_t)bh * p.T + qi * kBQ + row] = m + log2f(l);
+    if (threadIdx.x == 0) bulk_wait_read0();
+    ATTN_FSTAMP(30, 2);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 9) tmem_dealloc<256>(tmem);
+  ATTN_FSTAMP(30, 3);
 }
 
 // =====================================================================================================
@@ -320,7 +369,7 @@ k_attn_fwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
 //   warp 8 TMA        warp 9 MMA issuer        warps 0-7: two threads per query row
 // =====================================================================================================
 struct __align__(16) AttnBwdBars {
-  uint64_t kv_full[2], kv_empty[2], qdo_full[2], qdo_empty[2], sdp_full, pds_ready, dq_full;
+  uint64_t kv_full[2], kv_empty[2], qdo_full[2], qdo_empty[2], sdp_full, sdp_taken, pds_ready, dq_full;
   uint32_t tmem_base;
 };
 
@@ -361,7 +410,7 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
         mbar_init(&bars->kv_full[i], 1); mbar_init(&bars->kv_empty[i], 1);
         mbar_init(&bars->qdo_full[i], 1); mbar_init(&bars->qdo_empty[i], 1);
       }
-      mbar_init(&bars->sdp_full, 1); mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1);
+      mbar_init(&bars->sdp_full, 1); mbar_init(&bars->sdp_taken, 256); mbar_init(&bars->pds_ready, 256); mbar_init(&bars->dq_full, 1);
       mbar_fence_init();
     }
     __syncwarp();
@@ -434,13 +483,16 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       const uint32_t ka = smem_u32(kv_smem + (n & 1) * 2 * kTileBytes);
       for (int it = 0; it < nit; ++it, ++g) {
         const int st = g & 1;
-        mbar_wait(&bars->pds_ready, g & 1);                // P / dS of g are in shared memory; S / dP, dQ(g-1) and - at an item
-        ATTN_STAMP(g, 4);                                  // boundary - the finished item's dK / dV have been read
-        // the next scores (of this item or of the next one) are computed ahead of the three products below
+        // sdp_taken(g): S / dP of g are in the threads' registers: the next scores (of this item or of the next one) are
+        // issued now, behind the previous iteration's products, and are ready when the threads have stored P / dS of g
+        mbar_wait(&bars->sdp_taken, g & 1);
+        tc_fence_after();
+        ATTN_STAMP(g, 4);
         if (it + 1 < nit) issue_sdp(g + 1, n & 1);
         else if (more) { mbar_wait(&bars->kv_full[(n + 1) & 1], ((n + 1) >> 1) & 1); issue_sdp(g + 1, (n + 1) & 1); }
         ATTN_STAMP(g, 5);
-        tc_fence_after();
+        mbar_wait(&bars->pds_ready, g & 1);                // P / dS of g are in shared memory; dQ(g-1) and - at an item boundary -
+        tc_fence_after();                                  // the finished item's dK / dV have been read
         if (elect_one()) {
           const uint32_t qa = smem_u32(qdo_smem + st * 2 * kTileBytes), doa = qa + kTileBytes;
 #pragma unroll
@@ -537,22 +589,31 @@ k_attn_bwd(const __grid_constant__ CUtensorMap map_qkv, const __grid_constant__ 
       ATTN_STAMP(g, 0);
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
+        // diagonal block: chunk hc = 2 half + c is above the diagonal for hc > lg (P = dS = 0, nothing to read) and cut by it
+        // for hc == lg (column e visible to lane >= e) - warp-uniform, as in the forward kernel
+        const int hc = half * 2 + c;
+        if (kDiag && hc > lg) {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) { pk[c * 16 + e] = 0u; dk[c * 16 + e] = 0u; }
+          continue;
+        }
+        const bool cut = kDiag && hc == lg;
         uint32_t rs[32], rp[32];
         tmem_ld32(tS + lane_addr + half * 64 + c * 32, rs);
         tmem_ld32(tDP + lane_addr + half * 64 + c * 32, rp);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; e += 2) {
-          const int col = half * 64 + c * 32 + e;
           const float2 x = ffma2(u2f2(rs[e], rs[e + 1]), sc2, nl2);
           float2 pr = make_float2(ex2(x.x), ex2(x.y));
-          if (kDiag) { if (col > row) pr.x = 0.f; if (col + 1 > row) pr.y = 0.f; }
+          if (kDiag) { if (cut && e > lane) pr.x = 0.f; if (cut && e + 1 > lane) pr.y = 0.f; }
           const float2 d = fmul2(pr, ffma2(u2f2(rp[e], rp[e + 1]), ss2, nd2));     // P o (dP - delta) * scale
           pk[c * 16 + (e >> 1)] = pack_bf16(pr.x, pr.y);
           dk[c * 16 + (e >> 1)] = pack_bf16(d.x, d.y);
         }
       }
       tc_fence_before();
+      mbar_arrive(&bars->sdp_taken);
       ATTN_STAMP(g, 1);
       if (kDiag && w_prev >= 0) write_dkv(w_prev, g - 1);   // item boundary: once the previous item's last products are done
       if (g > 0) take_dq(g - 1, qtile_prev);                // (waits until the copy engine has read the tiles staged just above)
@@ -654,12 +715,18 @@ int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cu
   if (encode_bf16_2d(&map, qkv, (long)B * T, 3L * C, 3L * C, kD, kBQ)) return -1;
   if (encode_bf16_2d(&map_out, out, (long)B * T, C, C, kD, kBQ)) return -1;
   AttnFwdParams p{};
-  p.T = T; p.H = H; p.C = C; p.scale_log2 = 0.125f * 1.4426950408889634f;
+  p.T = T; p.H = H; p.C = C; p.BH = B * H; p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse; p.trace = g_attn_ftrace; p.trace_x = g_attn_trace_x;
   const size_t smem = (size_t)kTileBytes * (1 + kRing + 2) + sizeof(AttnBars) + 1024;
   static bool attr = false;
   if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_fwd, dim3(B * H, T / kBQ), dim3(kAttnThreads), smem, s, map, map_out, p));
+  static int sms = 0;
+  if (sms == 0) { int dev = 0; DCP_CUDA_CHECK(cudaGetDevice(&dev)); DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)); }
+  const int items = B * H * (T / kBQ);
+  static int per_sm = -1;           // DCP_ATTN_FWD_CTAS_PER_SM: 0 = one CTA per item (no persistence); default two persistent CTAs per SM
+  if (per_sm < 0) { const char* e = getenv("DCP_ATTN_FWD_CTAS_PER_SM"); per_sm = e ? atoi(e) : 2; }
+  const int grid = (per_sm <= 0 || items < per_sm * sms) ? items : per_sm * sms;
+  DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_fwd, dim3(grid), dim3(kAttnThreads), smem, s, map, map_out, p));
   return 0;
 }
 
