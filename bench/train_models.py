@@ -76,7 +76,8 @@ def run_ours(opt, rank, world):
     model.train()
     ddp = dcp.DistributedDataParallel(model, device_ids=[rank], bucket_cap_mb=(256 if opt.model == "gpt2" else None))
     if opt.model == "gpt2":
-        optim = FusedShardedOptimizer(ddp, kind="adamw", lr=3e-4, weight_decay=0.1)   # reduce_scatter -> AdamW -> all_gather per bucket
+        optim = FusedShardedOptimizer(ddp, kind="adamw", lr=3e-4, weight_decay=0.1,
+                                      shadow_dtype=(torch.bfloat16 if opt.bf16 and os.environ.get("DCP_BF16_SHADOW", "1") == "1" else None))   # reduce_scatter -> AdamW -> all_gather per bucket
     else:
         optim = ops.SGD(ddp.parameters(), lr=0.1, momentum=0.9, weight_decay=1e-4)
     batches, B, units = data(opt, dev, rank)

@@ -74,9 +74,12 @@ template <> struct Vec16<__nv_bfloat16> {
 };
 constexpr int kMaxVPL = 4;   // 16-byte vectors per lane (template parameter VPL = ceil(C / vector / 32)): C <= 1024 (bf16) / 512 (f32)
 
+// res / sum_out (both or neither): the row normalised is x + res, and that sum is also written out - the residual add of a
+// pre-LN transformer block fused into the LayerNorm that follows it.
 template <typename T, int kVPL>
 __global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__ x, T* __restrict__ y, const float* __restrict__ g, const float* __restrict__ b,
-                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out, int C, int rows, float eps) {
+                                                           float* __restrict__ mean_out, float* __restrict__ rstd_out, int C, int rows, float eps,
+                                                           const T* __restrict__ res = nullptr, T* __restrict__ sum_out = nullptr) {
   constexpr int VN = Vec16<T>::N;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nvec = C / VN;
   const float invC = 1.f / (float)C;
@@ -89,6 +92,15 @@ __global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__
       const int vi = lane + 32 * k;
       if (vi < nvec) {
         Vec16<T>::load(xr + vi * VN, v[k]);
+        if (res != nullptr) {
+          float rr[VN];
+          Vec16<T>::load(res + (long)r * C + vi * VN, rr);
+#pragma unroll
+          for (int i = 0; i < VN; ++i) v[k][i] += rr[i];
+          Vec16<T>::store(sum_out + (long)r * C + vi * VN, v[k]);
+#pragma unroll
+          for (int i = 0; i < VN; ++i) v[k][i] = to_f(from_f<T>(v[k][i]));   // normalise what later kernels will read (the rounded sum)
+        }
 #pragma unroll
         for (int i = 0; i < VN; ++i) s += v[k][i];
       }
@@ -119,7 +131,9 @@ __global__ void __launch_bounds__(kT) k_layernorm_fwd_warp(const T* __restrict__
 template <typename T, int kVPL>
 __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ g,
                                                            const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
-                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int rows) {
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int rows,
+                                                           const T* __restrict__ dres = nullptr) {
+  // dres: gradient arriving at the normalised tensor from its other consumer (the residual path); added into dx here
   constexpr int VN = Vec16<T>::N;
   extern __shared__ float acc[];                     // [2][C], zeroed, then += the 8 warps' partial sums
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nvec = C / VN;
@@ -161,6 +175,12 @@ __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__
         float out[VN];
 #pragma unroll
         for (int i = 0; i < VN; ++i) out[i] = rs * (d[k][i] * gam[k][i] - s1 - xh[k][i] * s2);
+        if (dres != nullptr) {
+          float rr[VN];
+          Vec16<T>::load(dres + o + vi * VN, rr);
+#pragma unroll
+          for (int i = 0; i < VN; ++i) out[i] += rr[i];
+        }
         Vec16<T>::store(dx + o + vi * VN, out);
       }
     }
@@ -174,6 +194,45 @@ __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__
     }
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) { atomicAdd(&dgamma[c], acc[c]); atomicAdd(&dbeta[c], acc[C + c]); }
+}
+
+// four consecutive elements of a row as floats
+__device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+__device__ __forceinline__ float4 ld4(const __nv_bfloat16* p) {
+  const uint2 v = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&v.x), b = *reinterpret_cast<const __nv_bfloat162*>(&v.y);
+  return make_float4(__low2float(a), __high2float(a), __low2float(b), __high2float(b));
+}
+__device__ __forceinline__ void st4(float* p, float4 v) { *reinterpret_cast<float4*>(p) = v; }
+__device__ __forceinline__ void st4(__nv_bfloat16* p, float4 v) {
+  const __nv_bfloat162 a = __floats2bfloat162_rn(v.x, v.y), b = __floats2bfloat162_rn(v.z, v.w);
+  *reinterpret_cast<uint2*>(p) = make_uint2(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b));
+}
+template <typename T> __global__ void __launch_bounds__(256) k_embed_fwd(const long* __restrict__ idx, const float* __restrict__ wte, const float* __restrict__ wpe,
+                                                                         T* __restrict__ out, long n, int Tlen, int C) {
+  const int c4 = C / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / c4; const int c = (int)(i % c4) * 4;
+    const float4 a = ld4(wte + idx[r] * C + c), b = ld4(wpe + (r % Tlen) * C + c);
+    st4(out + r * C + c, make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w));
+  }
+}
+template <typename T> __global__ void __launch_bounds__(256) k_embed_bwd_wte(const long* __restrict__ idx, const T* __restrict__ dy, float* __restrict__ dwte, long n, int C) {
+  const int c4 = C / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x) {
+    const long r = i / c4; const int c = (int)(i % c4) * 4;
+    const float4 v = ld4(dy + r * C + c);
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dwte + idx[r] * C + c), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+  }
+}
+template <typename T> __global__ void __launch_bounds__(128) k_embed_bwd_wpe(const T* __restrict__ dy, float* __restrict__ dwpe, long npos, int B, int Tlen, int C) {
+  const int c4 = C / 4;
+  for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < npos; i += (long)gridDim.x * blockDim.x) {
+    const long t = i / c4; const int c = (int)(i % c4) * 4;
+    float4 a = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int b = 0; b < B; ++b) { const float4 v = ld4(dy + ((long)b * Tlen + t) * C + c); a.x += v.x; a.y += v.y; a.z += v.z; a.w += v.w; }
+    st4(dwpe + t * C + c, a);
+  }
 }
 
 __device__ __forceinline__ float gelu_tanh(float x) {
@@ -227,6 +286,57 @@ int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const f
   int rpc = (rows + ctas - 1) / ctas;
   ctas = (rows + rpc - 1) / rpc;
   DISPATCH_ACT(dtype, (k_layernorm_bwd<T><<<ctas, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows, rpc)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+// y = LayerNorm(x + res), sum_out = x + res (the residual stream after the add): one pass instead of an add kernel plus a
+// LayerNorm.  Row length as in the warp-per-row path of dcp_layernorm_fwd (C a multiple of the 16-byte vector, <= 1024 bf16 /
+// 512 fp32 elements), 16-byte aligned pointers; returns -1 otherwise (the caller falls back to add + layer norm).
+int dcp_add_layernorm_fwd(const void* x, const void* res, void* sum_out, void* y, const float* gamma, const float* beta, float* mean, float* rstd,
+                          int rows, int C, float eps, int dtype, cudaStream_t s) {
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (!(C % vn == 0 && C / vn <= 32 * kMaxVPL) || ((uintptr_t)x | (uintptr_t)res | (uintptr_t)sum_out | (uintptr_t)y) % 16 != 0) {
+    dcp_set_error("add_layernorm: unsupported row length %d or unaligned pointers", C); return -1;
+  }
+  const int ctas = min((rows + kT / 32 - 1) / (kT / 32), 148 * 8);
+  const int vpl = (C / vn + 31) / 32;
+#define LN_FWD(V) DISPATCH_ACT(dtype, (k_layernorm_fwd_warp<T, V><<<ctas, kT, 0, s>>>((const T*)x, (T*)y, gamma, beta, mean, rstd, C, rows, eps, (const T*)res, (T*)sum_out)))
+  if (vpl == 1) { LN_FWD(1); } else if (vpl == 2) { LN_FWD(2); } else if (vpl == 3) { LN_FWD(3); } else { LN_FWD(4); }
+#undef LN_FWD
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+// Backward of dcp_add_layernorm_fwd: dx = LayerNorm-backward(dy) + dsum, where dsum is the gradient that reached the sum from
+// the residual path (the same dx is the gradient of both x and res).  x = the saved sum.  dgamma / dbeta: fp32 [C], zeroed here.
+int dcp_add_layernorm_bwd(const void* x, const void* dy, const void* dsum, const float* gamma, const float* mean, const float* rstd, void* dx,
+                          float* dgamma, float* dbeta, int rows, int C, int dtype, cudaStream_t s) {
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (!(C % vn == 0 && C / vn <= 32 * kMaxVPL) || ((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dsum | (uintptr_t)dx) % 16 != 0) {
+    dcp_set_error("add_layernorm backward: unsupported row length %d or unaligned pointers", C); return -1;
+  }
+  DCP_CUDA_CHECK(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, s));
+  DCP_CUDA_CHECK(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, s));
+  const int ctasw = min((rows + kT / 32 - 1) / (kT / 32), 148 * 2);
+  const int vpl = (C / vn + 31) / 32;
+#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows, (const T*)dsum)))
+  if (vpl == 1) { LN_BWD(1); } else if (vpl == 2) { LN_BWD(2); } else if (vpl == 3) { LN_BWD(3); } else { LN_BWD(4); }
+#undef LN_BWD
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+
+// Token + position embedding of a transformer: out[r, :] = T(wte[idx[r], :] + wpe[r % Tlen, :]) for r < rows = B * Tlen.
+// fp32 tables, f32 / bf16 output, C a multiple of 4.  (One gather kernel instead of two gathers, an add and a cast.)
+int dcp_embed_fwd(const long* idx, const float* wte, const float* wpe, void* out, long rows, int Tlen, int C, int dtype, cudaStream_t s) {
+  if (C % 4) { dcp_set_error("embed: C=%d must be a multiple of 4", C); return -1; }
+  const long n = rows * (C / 4);
+  DISPATCH_ACT(dtype, (k_embed_fwd<T><<<grid_1d(n, 256), 256, 0, s>>>(idx, wte, wpe, (T*)out, n, Tlen, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+// Backward: dwte[idx[r], :] += dy[r, :] (vector reductions; dwte fp32 [V, C] zeroed by the caller - rows that are no token stay
+// zero) and dwpe[t, :] = sum_b dy[b * Tlen + t, :] for t < Tlen (plain stores; the caller zeroes the rows beyond Tlen).
+int dcp_embed_bwd(const long* idx, const void* dy, float* dwte, float* dwpe, long rows, int Tlen, int C, int dtype, cudaStream_t s) {
+  if (C % 4) { dcp_set_error("embed: C=%d must be a multiple of 4", C); return -1; }
+  const long n = rows * (C / 4), npos = (long)Tlen * (C / 4);
+  DISPATCH_ACT(dtype, (k_embed_bwd_wte<T><<<grid_1d(n, 256), 256, 0, s>>>(idx, (const T*)dy, dwte, n, C)));
+  DISPATCH_ACT(dtype, (k_embed_bwd_wpe<T><<<grid_1d(npos, 128), 128, 0, s>>>((const T*)dy, dwpe, npos, (int)(rows / Tlen), Tlen, C)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 int dcp_gelu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s) {

@@ -68,9 +68,8 @@ class Block(nn.Module):
         self.mlp_proj = ops.Linear(4 * cfg.n_embd, cfg.n_embd)
         self.n_head = cfg.n_head
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
-        B, T, C = x.shape
-        qkv = self.attn_qkv(self.ln_1(x).view(B * T, C))
+    def _attention(self, h: torch.Tensor, B: int, T: int, C: int) -> torch.Tensor:
+        qkv = self.attn_qkv(h.view(B * T, C))
         if ops.layers.use_kernels(qkv) and os.environ.get("DCP_ATTENTION", "1") == "1" and cuda_ops().causal_attention_supported(qkv, T, self.n_head):
             # flash attention on tcgen05, reading q / k / v in place and returning the heads merged (csrc/ops/attention_tc.cu)
             y = cuda_ops().causal_attention(qkv, B, T, self.n_head)
@@ -78,9 +77,27 @@ class Block(nn.Module):
             q, k, v = _SplitHeads.apply(qkv, B, T, self.n_head)
             y = F.scaled_dot_product_attention(q, k, v, is_causal=True)
             y = y.transpose(1, 2).reshape(B * T, C)
-        x = x + self.attn_proj(y).view(B, T, C)
+        return self.attn_proj(y).view(B, T, C)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B, T, C = x.shape
+        x = x + self._attention(self.ln_1(x), B, T, C)
         h = self.act(self.mlp_fc(self.ln_2(x).view(B * T, C)))
         return x + self.mlp_proj(h).view(B, T, C)
+
+    def forward_fused(self, x: torch.Tensor, pending):
+        """Same block with every residual add folded into the LayerNorm that follows it (ops.cuda.add_layer_norm): takes the
+        residual stream ``x`` and the previous block's MLP output ``pending`` that has not been added yet (None for the first
+        block), returns the stream after the attention add and this block's own MLP output, again un-added."""
+        K = cuda_ops()
+        B, T, C = x.shape
+        if pending is None:
+            h = self.ln_1(x)
+        else:
+            x, h = K.add_layer_norm(x, pending, self.ln_1.weight, self.ln_1.bias, self.ln_1.eps)
+        a = self._attention(h, B, T, C)
+        x, h = K.add_layer_norm(x, a, self.ln_2.weight, self.ln_2.bias, self.ln_2.eps)
+        return x, self.mlp_proj(self.act(self.mlp_fc(h.view(B * T, C)))).view(B, T, C)
 
 
 class GPT2(nn.Module):
@@ -106,13 +123,24 @@ class GPT2(nn.Module):
 
     def forward(self, idx: torch.Tensor, targets: torch.Tensor = None):
         B, T = idx.shape
-        pos = torch.arange(T, device=idx.device)
-        x = self.wte(idx) + self.wpe(pos)
-        if self.compute_dtype is not None:
-            x = x.to(self.compute_dtype)
-        for blk in self.h:
-            x = blk(x)
-        x = self.ln_f(x)
+        kern = ops.layers.use_kernels(idx) and os.environ.get("DCP_GPT2_FUSED", "1") == "1"
+        if kern and self.wte.weight.dtype == torch.float32:
+            # one gather kernel: wte[idx] + wpe[pos], written in the compute dtype (csrc/ops/transformer.cu)
+            x = cuda_ops().embed(idx, self.wte.weight, self.wpe.weight, self.compute_dtype or torch.float32)
+        else:
+            pos = torch.arange(T, device=idx.device)
+            x = self.wte(idx) + self.wpe(pos)
+            if self.compute_dtype is not None:
+                x = x.to(self.compute_dtype)
+        if kern and cuda_ops().add_layer_norm_supported(x):
+            pending = None
+            for blk in self.h:
+                x, pending = blk.forward_fused(x, pending)
+            _, x = cuda_ops().add_layer_norm(x, pending, self.ln_f.weight, self.ln_f.bias, self.ln_f.eps)
+        else:
+            for blk in self.h:
+                x = blk(x)
+            x = self.ln_f(x)
         if ops.layers.use_kernels(x):
             from ..ops import cuda
             logits = cuda.linear(x.view(B * T, -1), self.wte.weight, None, False)

@@ -62,6 +62,9 @@ def lib():
             "dcp_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
             "dcp_gelu_fwd": [vp, vp, l, i, vp], "dcp_gelu_bwd": [vp, vp, vp, l, i, vp],
             "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
+            "dcp_add_layernorm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, C.c_float, i, vp],
+            "dcp_add_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
+            "dcp_embed_fwd": [vp, vp, vp, vp, l, i, i, i, vp], "dcp_embed_bwd": [vp, vp, vp, vp, l, i, i, i, vp],
             "dcp_attn_fwd": [vp, vp, vp, i, i, i, vp],
             "dcp_attn_bwd": [vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
             "dcp_conv_flat_pool_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, f, ull, ull, vp, i, i, vp],
@@ -481,6 +484,29 @@ class _Conv2d(Function):
         return dx, dw, db, None, None, None
 
 
+# Low-precision shadows of fp32 master weights: (data_ptr, dtype) -> tensor of that dtype which its owner keeps current (the
+# fused sharded optimizer re-casts a whole bucket with ONE launch after each update, parallel/zero.py).  Linear layers use the
+# shadow instead of casting their weight on every forward.
+_SHADOWS = {}
+
+
+def register_shadow(master: torch.Tensor, shadow: torch.Tensor) -> None:
+    _SHADOWS[(master.data_ptr(), shadow.dtype)] = (shadow, tuple(master.shape))
+
+
+def drop_shadows(masters) -> None:
+    for m in masters:
+        for k in [k for k in _SHADOWS if k[0] == m.data_ptr()]:
+            del _SHADOWS[k]
+
+
+def _lowp(w32: torch.Tensor, dtype) -> torch.Tensor:
+    ent = _SHADOWS.get((w32.data_ptr(), dtype))
+    if ent is not None and ent[1] == tuple(w32.shape):
+        return ent[0]
+    return _cast(w32, dtype)
+
+
 def _cast(t32: torch.Tensor, dtype) -> torch.Tensor:
     out = torch.empty_like(t32, dtype=dtype)
     _chk(lib().dcp_cast_from_f32(t32.data_ptr(), out.data_ptr(), t32.numel(), _DT[dtype], _stream()))
@@ -503,8 +529,8 @@ class _Linear(Function):
         w = w if w.is_contiguous() else w.contiguous()
         ctx.w_dtype = w.dtype
         if w.dtype != x2.dtype:     # fp32 master weights, bf16 compute
-            w = _cast(w, x2.dtype) if w.dtype == torch.float32 else w.to(x2.dtype)
-            b = None if b is None else (_cast(b, x2.dtype) if b.dtype == torch.float32 else b.to(x2.dtype))
+            w = _lowp(w, x2.dtype) if w.dtype == torch.float32 else w.to(x2.dtype)
+            b = None if b is None else (_lowp(b, x2.dtype) if b.dtype == torch.float32 else b.to(x2.dtype))
         M, K = x2.shape
         N = w.shape[0]
         y = torch.empty((M, N), dtype=x.dtype, device=x.device)
@@ -587,6 +613,90 @@ class _LayerNorm(Function):
 
 def layer_norm(x, gamma, beta, eps: float = 1e-5):
     return _LayerNorm.apply(x, gamma, beta, eps)
+
+
+class _AddLayerNorm(Function):
+    """(x, res) -> (s, y) with s = x + res and y = LayerNorm(s): the residual add of a pre-LN transformer block fused into the
+    LayerNorm that follows it (one pass over the row instead of an add kernel plus a LayerNorm).  Backward folds the gradient
+    that reaches ``s`` from the residual path into the LayerNorm backward, so autograd's accumulation add disappears as well;
+    x and res receive the same gradient tensor."""
+
+    @staticmethod
+    def forward(ctx, x, res, gamma, beta, eps):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1]); x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        r2 = res.reshape(-1, shape[-1]); r2 = r2 if r2.is_contiguous() else r2.contiguous()
+        rows, Cc = x2.shape
+        ssum, y = torch.empty_like(x2), torch.empty_like(x2)
+        mean = torch.empty(rows, dtype=torch.float32, device=x.device)
+        rstd = torch.empty(rows, dtype=torch.float32, device=x.device)
+        _chk(lib().dcp_add_layernorm_fwd(x2.data_ptr(), r2.data_ptr(), ssum.data_ptr(), y.data_ptr(), gamma.data_ptr(), beta.data_ptr(), mean.data_ptr(),
+                                         rstd.data_ptr(), rows, Cc, float(eps), _dt(x2), _stream()))
+        ctx.save_for_backward(ssum, gamma, mean, rstd)
+        ctx.shape = shape
+        ctx.set_materialize_grads(False)
+        return ssum.view(shape), y.view(shape)
+
+    @staticmethod
+    def backward(ctx, dsum, dy):
+        ssum, gamma, mean, rstd = ctx.saved_tensors
+        rows, Cc = ssum.shape
+        if dy is None:                                   # only the sum was used
+            return dsum, dsum, None, None, None
+        dy = dy.reshape(rows, Cc); dy = dy if dy.is_contiguous() else dy.contiguous()
+        dx = torch.empty_like(ssum)
+        dg = torch.empty(Cc, dtype=torch.float32, device=ssum.device)
+        db = torch.empty(Cc, dtype=torch.float32, device=ssum.device)
+        if dsum is None:
+            _chk(lib().dcp_layernorm_bwd(ssum.data_ptr(), dy.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(), dg.data_ptr(),
+                                         db.data_ptr(), rows, Cc, _dt(ssum), _stream()))
+        else:
+            dsum = dsum.reshape(rows, Cc); dsum = dsum if dsum.is_contiguous() else dsum.contiguous()
+            _chk(lib().dcp_add_layernorm_bwd(ssum.data_ptr(), dy.data_ptr(), dsum.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                             dx.data_ptr(), dg.data_ptr(), db.data_ptr(), rows, Cc, _dt(ssum), _stream()))
+        dx = dx.view(ctx.shape)
+        return dx, dx, dg, db, None
+
+
+def add_layer_norm_supported(x: torch.Tensor) -> bool:
+    vn = 4 if x.dtype == torch.float32 else 8
+    return x.is_cuda and x.dtype in (torch.float32, torch.bfloat16) and x.shape[-1] % vn == 0 and x.shape[-1] // vn <= 128
+
+
+def add_layer_norm(x, res, gamma, beta, eps: float = 1e-5):
+    """Returns (x + res, LayerNorm(x + res))."""
+    return _AddLayerNorm.apply(x, res, gamma, beta, eps)
+
+
+class _Embed(Function):
+    """Token + position embedding: out[b, t, :] = dtype(wte[idx[b, t]] + wpe[t]) in one gather kernel; backward scatters into
+    the (dense, fp32) table gradients with vector reductions instead of the sort-based library path."""
+
+    @staticmethod
+    def forward(ctx, idx, wte, wpe, dtype):
+        B, T = idx.shape
+        Cc = wte.shape[1]
+        idx = idx if idx.is_contiguous() else idx.contiguous()
+        out = torch.empty(B, T, Cc, dtype=dtype, device=wte.device)
+        _chk(lib().dcp_embed_fwd(idx.data_ptr(), wte.data_ptr(), wpe.data_ptr(), out.data_ptr(), B * T, T, Cc, _DT[dtype], _stream()))
+        ctx.save_for_backward(idx)
+        ctx.shapes = (wte.shape, wpe.shape)
+        return out
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        B, T = idx.shape
+        ws, ps = ctx.shapes
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        dwte = torch.zeros(ws, dtype=torch.float32, device=dy.device)
+        dwpe = torch.zeros(ps, dtype=torch.float32, device=dy.device) if ps[0] > T else torch.empty(ps, dtype=torch.float32, device=dy.device)
+        _chk(lib().dcp_embed_bwd(idx.data_ptr(), dy.data_ptr(), dwte.data_ptr(), dwpe.data_ptr(), B * T, T, ws[1], _dt(dy), _stream()))
+        return None, dwte, dwpe, None
+
+
+def embed(idx, wte, wpe, dtype):
+    return _Embed.apply(idx, wte, wpe, dtype)
 
 
 class _GELU(Function):

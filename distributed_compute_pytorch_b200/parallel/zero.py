@@ -26,7 +26,7 @@ _KINDS = {"adadelta": 0, "sgd": 1, "adam": 2, "adamw": 2}
 class FusedShardedOptimizer:
     def __init__(self, ddp: DistributedDataParallel, kind: str = "adam", lr: float = 1e-3, rho: float = 0.9, eps: float = None,
                  momentum: float = 0.0, dampening: float = 0.0, nesterov: bool = False, betas=(0.9, 0.999), weight_decay: float = 0.0,
-                 use_nvls: bool = True, max_ctas: int = 0):
+                 use_nvls: bool = True, max_ctas: int = 0, shadow_dtype=None):
         if ddp._cuda_backend is None:
             raise RuntimeError("FusedShardedOptimizer needs the NVLink P2P backend (CUDA parameters, world_size >= 1)")
         self.ddp, self.be = ddp, ddp._cuda_backend
@@ -52,6 +52,10 @@ class FusedShardedOptimizer:
         self.hp = torch.zeros(8, dtype=torch.float32, device=dev)
         self._last_hyper = None
         self.param_bufs: List[torch.Tensor] = []
+        # shadow_dtype (e.g. torch.bfloat16): keep a low-precision copy of every flat parameter buffer, refreshed by ONE cast launch
+        # per bucket right behind the update; the Linear layers multiply with it instead of casting their weight every forward
+        self.shadow_dtype = shadow_dtype
+        self.shadow_bufs: List[torch.Tensor] = []
         self.states = []
         nstate = 1 if self.kind == 1 else 2
         for b in ddp._buckets:
@@ -69,12 +73,30 @@ class FusedShardedOptimizer:
                 dst = dst.view(p.shape) if p.is_contiguous() else dst.as_strided(p.shape, p.stride())
                 dst.copy_(p.detach())
                 p.data = dst
+            if shadow_dtype is not None:
+                sbuf = torch.empty(npad, dtype=shadow_dtype, device=dev)
+                for p, v in zip(b.params, b.views):
+                    if p.is_contiguous():
+                        off = (v.data_ptr() - base) // b.flat.element_size()
+                        K.register_shadow(p.data, sbuf[off: off + p.numel()].view(p.shape))
+                self.shadow_bufs.append(sbuf)
             gd = K._DT[b.flat.dtype]
             shard = int(cl.dcp_fused_shard_elems(n, self.be.world, gd))
             self.param_bufs.append(pbuf)
             self.states.append([torch.zeros(shard, dtype=torch.float32, device=dev) for _ in range(nstate)])
         ddp._bucket_override = self._on_bucket_ready
         self._sync_hyper()
+        self.refresh_shadows()
+
+    def refresh_shadows(self) -> None:
+        """Re-cast every flat parameter buffer into its low-precision shadow (after loading a checkpoint into the parameters)."""
+        for pbuf, sbuf in zip(self.param_bufs, self.shadow_bufs):
+            K._chk(self._lib.dcp_cast_from_f32(pbuf.data_ptr(), sbuf.data_ptr(), pbuf.numel(), K._DT[sbuf.dtype], K._stream()))
+
+    def close(self) -> None:
+        if self.shadow_bufs:
+            K.drop_shadows([p.data for b in self.ddp._buckets for p in b.params])
+            self.shadow_bufs = []
 
     def _sync_hyper(self) -> None:
         h = self._hyper()
@@ -96,6 +118,9 @@ class FusedShardedOptimizer:
             rc = be.lib.dcp_fused_rs_opt_ag(be.handle, bucket.flat.data_ptr(), self.param_bufs[i].data_ptr(), st[0].data_ptr(),
                                            st[1].data_ptr() if len(st) > 1 else None, bucket.flat.numel(), self.hp.data_ptr(), self.kind,
                                            K._DT[bucket.flat.dtype], int(self.use_nvls), CH_OPT, self.max_ctas, be.comm_stream.cuda_stream)
+            if rc == 0 and self.shadow_bufs:
+                sb = self.shadow_bufs[i]
+                rc = self._lib.dcp_cast_from_f32(self.param_bufs[i].data_ptr(), sb.data_ptr(), sb.numel(), K._DT[sb.dtype], be.comm_stream.cuda_stream)
         be._check(rc, "fused reduce_scatter/optimizer/all_gather")
         ev = torch.cuda.Event()
         ev.record(be.comm_stream)
