@@ -132,20 +132,22 @@ template <typename T, int kVPL>
 __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__ x, const T* __restrict__ dy, const float* __restrict__ g,
                                                            const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
                                                            float* __restrict__ dgamma, float* __restrict__ dbeta, int C, int rows,
-                                                           const T* __restrict__ dres = nullptr) {
+                                                           const T* __restrict__ dres = nullptr, float* __restrict__ dxsum = nullptr) {
+  // dxsum (fp32 [C], zeroed by the caller): column sums of the dx written here = the bias gradient of the Linear whose output was
+  // the `res` operand of the forward (its dy IS this dx), saving that layer a pass over dy
   // dres: gradient arriving at the normalised tensor from its other consumer (the residual path); added into dx here
   constexpr int VN = Vec16<T>::N;
   extern __shared__ float acc[];                     // [2][C], zeroed, then += the 8 warps' partial sums
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nvec = C / VN;
   const float invC = 1.f / (float)C;
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) acc[c] = 0.f;
-  float gam[kVPL][VN], dg[kVPL][VN], db[kVPL][VN];
+  for (int c = threadIdx.x; c < 3 * C; c += blockDim.x) acc[c] = 0.f;
+  float gam[kVPL][VN], dg[kVPL][VN], db[kVPL][VN], dsx[kVPL][VN];
 #pragma unroll
   for (int k = 0; k < kVPL; ++k)
 #pragma unroll
     for (int i = 0; i < VN; ++i) {
       const int c = (lane + 32 * k) * VN + i;
-      gam[k][i] = c < C ? g[c] : 0.f; dg[k][i] = 0.f; db[k][i] = 0.f;
+      gam[k][i] = c < C ? g[c] : 0.f; dg[k][i] = 0.f; db[k][i] = 0.f; dsx[k][i] = 0.f;
     }
   for (int r = blockIdx.x * (kT / 32) + warp; r < rows; r += gridDim.x * (kT / 32)) {
     const long o = (long)r * C;
@@ -181,6 +183,10 @@ __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__
 #pragma unroll
           for (int i = 0; i < VN; ++i) out[i] += rr[i];
         }
+        if (dxsum != nullptr) {
+#pragma unroll
+          for (int i = 0; i < VN; ++i) dsx[k][i] += out[i];
+        }
         Vec16<T>::store(dx + o + vi * VN, out);
       }
     }
@@ -190,10 +196,17 @@ __global__ void __launch_bounds__(kT) k_layernorm_bwd_warp(const T* __restrict__
   for (int k = 0; k < kVPL; ++k)
     if (lane + 32 * k < nvec) {
 #pragma unroll
-      for (int i = 0; i < VN; ++i) { const int c = (lane + 32 * k) * VN + i; atomicAdd(&acc[c], dg[k][i]); atomicAdd(&acc[C + c], db[k][i]); }
+      for (int i = 0; i < VN; ++i) {
+        const int c = (lane + 32 * k) * VN + i;
+        atomicAdd(&acc[c], dg[k][i]); atomicAdd(&acc[C + c], db[k][i]);
+        if (dxsum != nullptr) atomicAdd(&acc[2 * C + c], dsx[k][i]);
+      }
     }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) { atomicAdd(&dgamma[c], acc[c]); atomicAdd(&dbeta[c], acc[C + c]); }
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    atomicAdd(&dgamma[c], acc[c]); atomicAdd(&dbeta[c], acc[C + c]);
+    if (dxsum != nullptr) atomicAdd(&dxsum[c], acc[2 * C + c]);
+  }
 }
 
 // four consecutive elements of a row as floats
@@ -251,6 +264,48 @@ template <typename T> __global__ void k_gelu_bwd(const T* __restrict__ x, const 
   for (long i = (long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long)gridDim.x * blockDim.x)
     dx[i] = from_f<T>(to_f(dy[i]) * gelu_tanh_grad(to_f(x[i])));
 }
+// dx = dy * gelu'(x) AND colsum[c] += sum_r dx[r, c] (the bias gradient of the Linear that produced x): 16-byte accesses, a
+// thread owns one vector of columns over a strip of rows, the eight row lanes of a CTA fold through shared memory.
+template <typename T> __global__ void __launch_bounds__(256) k_gelu_bwd_colsum(const T* __restrict__ x, const T* __restrict__ dy, T* __restrict__ dx,
+                                                                               float* __restrict__ colsum, long rows, int C, long rows_per_cta) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float sacc[8][32 * VN + 1];
+  const int lx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+  const long vcol = (long)blockIdx.x * 32 + lx;
+  const bool live = vcol * VN < C;
+  float a[VN];
+#pragma unroll
+  for (int i = 0; i < VN; ++i) a[i] = 0.f;
+  const long r0 = (long)blockIdx.y * rows_per_cta, r1 = min(rows, r0 + rows_per_cta);
+  if (live) {
+    for (long r = r0 + ly; r < r1; r += 16) {
+      float xv[2][VN], dv[2][VN];
+      const bool two = r + 8 < r1;
+      Vec16<T>::load(x + r * C + vcol * VN, xv[0]); Vec16<T>::load(dy + r * C + vcol * VN, dv[0]);
+      if (two) { Vec16<T>::load(x + (r + 8) * C + vcol * VN, xv[1]); Vec16<T>::load(dy + (r + 8) * C + vcol * VN, dv[1]); }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !two) break;
+        float o[VN];
+#pragma unroll
+        for (int i = 0; i < VN; ++i) { o[i] = to_f(from_f<T>(dv[u][i] * gelu_tanh_grad(xv[u][i]))); a[i] += o[i]; }
+        Vec16<T>::store(dx + (r + 8 * u) * C + vcol * VN, o);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < VN; ++i) sacc[ly][lx * VN + i] = a[i];
+  __syncthreads();
+  for (int i = threadIdx.x; i < 32 * VN; i += 256) {
+    const long c = (long)blockIdx.x * 32 * VN + i;
+    if (c < C) {
+      float t = 0.f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += sacc[k][i];
+      atomicAdd(&colsum[c], t);
+    }
+  }
+}
 }  // namespace
 
 extern "C" {
@@ -277,7 +332,7 @@ int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const f
   if (C % vn == 0 && C / vn <= 32 * kMaxVPL && ((uintptr_t)x % 16 == 0) && ((uintptr_t)dy % 16 == 0) && ((uintptr_t)dx % 16 == 0)) {
     const int ctasw = min((rows + kT / 32 - 1) / (kT / 32), 148 * 2);
     const int vpl = (C / vn + 31) / 32;
-#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows)))
+#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 3 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows)))
     if (vpl == 1) { LN_BWD(1); } else if (vpl == 2) { LN_BWD(2); } else if (vpl == 3) { LN_BWD(3); } else { LN_BWD(4); }
 #undef LN_BWD
     DCP_CUDA_CHECK(cudaGetLastError()); return 0;
@@ -306,17 +361,19 @@ int dcp_add_layernorm_fwd(const void* x, const void* res, void* sum_out, void* y
 }
 // Backward of dcp_add_layernorm_fwd: dx = LayerNorm-backward(dy) + dsum, where dsum is the gradient that reached the sum from
 // the residual path (the same dx is the gradient of both x and res).  x = the saved sum.  dgamma / dbeta: fp32 [C], zeroed here.
+// dxsum: optional fp32 [C] that receives the column sums of dx (zeroed here) - the bias gradient of the Linear that produced res.
 int dcp_add_layernorm_bwd(const void* x, const void* dy, const void* dsum, const float* gamma, const float* mean, const float* rstd, void* dx,
-                          float* dgamma, float* dbeta, int rows, int C, int dtype, cudaStream_t s) {
+                          float* dgamma, float* dbeta, float* dxsum, int rows, int C, int dtype, cudaStream_t s) {
   const int vn = dtype == DCP_F32 ? 4 : 8;
   if (!(C % vn == 0 && C / vn <= 32 * kMaxVPL) || ((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dsum | (uintptr_t)dx) % 16 != 0) {
     dcp_set_error("add_layernorm backward: unsupported row length %d or unaligned pointers", C); return -1;
   }
   DCP_CUDA_CHECK(cudaMemsetAsync(dgamma, 0, sizeof(float) * C, s));
   DCP_CUDA_CHECK(cudaMemsetAsync(dbeta, 0, sizeof(float) * C, s));
+  if (dxsum != nullptr) DCP_CUDA_CHECK(cudaMemsetAsync(dxsum, 0, sizeof(float) * C, s));
   const int ctasw = min((rows + kT / 32 - 1) / (kT / 32), 148 * 2);
   const int vpl = (C / vn + 31) / 32;
-#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 2 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows, (const T*)dsum)))
+#define LN_BWD(V) DISPATCH_ACT(dtype, (k_layernorm_bwd_warp<T, V><<<ctasw, kT, sizeof(float) * 3 * C, s>>>((const T*)x, (const T*)dy, gamma, mean, rstd, (T*)dx, dgamma, dbeta, C, rows, (const T*)dsum, dxsum)))
   if (vpl == 1) { LN_BWD(1); } else if (vpl == 2) { LN_BWD(2); } else if (vpl == 3) { LN_BWD(3); } else { LN_BWD(4); }
 #undef LN_BWD
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
@@ -337,6 +394,20 @@ int dcp_embed_bwd(const long* idx, const void* dy, float* dwte, float* dwpe, lon
   const long n = rows * (C / 4), npos = (long)Tlen * (C / 4);
   DISPATCH_ACT(dtype, (k_embed_bwd_wte<T><<<grid_1d(n, 256), 256, 0, s>>>(idx, (const T*)dy, dwte, n, C)));
   DISPATCH_ACT(dtype, (k_embed_bwd_wpe<T><<<grid_1d(npos, 128), 128, 0, s>>>((const T*)dy, dwpe, npos, (int)(rows / Tlen), Tlen, C)));
+  DCP_CUDA_CHECK(cudaGetLastError()); return 0;
+}
+// GELU backward over a [rows, C] matrix that also produces the column sums of dx (fp32 [C], zeroed here): C a multiple of the
+// 16-byte vector, aligned pointers (-1 otherwise; the caller falls back to dcp_gelu_bwd).
+int dcp_gelu_bwd_colsum(const void* x, const void* dy, void* dx, float* colsum, long rows, int C, int dtype, cudaStream_t s) {
+  const int vn = dtype == DCP_F32 ? 4 : 8;
+  if (C % vn || ((uintptr_t)x | (uintptr_t)dy | (uintptr_t)dx) % 16 != 0) { dcp_set_error("gelu_bwd_colsum: C=%d / alignment unsupported", C); return -1; }
+  DCP_CUDA_CHECK(cudaMemsetAsync(colsum, 0, sizeof(float) * C, s));
+  const int gx = (C / vn + 31) / 32;
+  long gy = (148L * 4 + gx - 1) / gx; const long maxy = (rows + 15) / 16;
+  if (gy > maxy) gy = maxy; if (gy < 1) gy = 1;
+  const long rpc = ((rows + gy - 1) / gy + 15) / 16 * 16;          // strips start on multiples of 16 rows
+  gy = (rows + rpc - 1) / rpc;
+  DISPATCH_ACT(dtype, (k_gelu_bwd_colsum<T><<<dim3(gx, (unsigned)gy), 256, 0, s>>>((const T*)x, (const T*)dy, (T*)dx, colsum, rows, C, rpc)));
   DCP_CUDA_CHECK(cudaGetLastError()); return 0;
 }
 int dcp_gelu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s) {

@@ -63,7 +63,8 @@ def lib():
             "dcp_gelu_fwd": [vp, vp, l, i, vp], "dcp_gelu_bwd": [vp, vp, vp, l, i, vp],
             "dcp_conv_flat_tc": [vp, vp, vp, vp, vp, l, i, i, i, vp, i, i, i, i, i, i, vp],
             "dcp_add_layernorm_fwd": [vp, vp, vp, vp, vp, vp, vp, vp, i, i, C.c_float, i, vp],
-            "dcp_add_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
+            "dcp_add_layernorm_bwd": [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
+            "dcp_gelu_bwd_colsum": [vp, vp, vp, vp, l, i, i, vp],
             "dcp_embed_fwd": [vp, vp, vp, vp, l, i, i, i, vp], "dcp_embed_bwd": [vp, vp, vp, vp, l, i, i, i, vp],
             "dcp_attn_fwd": [vp, vp, vp, i, i, i, vp],
             "dcp_attn_bwd": [vp, vp, vp, vp, vp, vp, vp, i, i, i, vp],
@@ -484,6 +485,26 @@ class _Conv2d(Function):
         return dx, dw, db, None, None, None
 
 
+# Column sums that a backward kernel produced as a by-product of writing a gradient tensor: [(tensor, colsum)].  The Linear whose
+# output gradient IS that tensor takes its bias gradient from here instead of reading dy once more (GELU backward -> mlp_fc,
+# add+LayerNorm backward -> attn_proj / mlp_proj).  The entry keeps the tensor alive, so its address cannot be reused meanwhile.
+_COLSUMS = []
+
+
+def _offer_colsum(t: torch.Tensor, colsum: torch.Tensor) -> None:
+    _COLSUMS.append((t, colsum))
+    if len(_COLSUMS) > 4:
+        del _COLSUMS[0]
+
+
+def _take_colsum(dy: torch.Tensor, n: int):
+    for k, (t, cs) in enumerate(_COLSUMS):
+        if t.data_ptr() == dy.data_ptr() and t.numel() == dy.numel() and cs.numel() == n and t.dtype == dy.dtype:
+            del _COLSUMS[k]
+            return cs
+    return None
+
+
 # Low-precision shadows of fp32 master weights: (data_ptr, dtype) -> tensor of that dtype which its owner keeps current (the
 # fused sharded optimizer re-casts a whole bucket with ONE launch after each update, parallel/zero.py).  Linear layers use the
 # shadow instead of casting their weight on every forward.
@@ -565,11 +586,13 @@ class _Linear(Function):
             dx = dx.view(shape)
         if ctx.needs_input_grad[1]:
             dw32 = torch.empty((N, K), dtype=torch.float32, device=x2.device)
-            db32 = torch.empty(N, dtype=torch.float32, device=x2.device) if has_b else None
+            ready = _take_colsum(dy, N) if (has_b and not relu) else None      # bias gradient already summed by dy's producer
+            db32 = ready if ready is not None else (torch.empty(N, dtype=torch.float32, device=x2.device) if has_b else None)
             if USE_TC and tc.linear_supported(N, K, M, x2.dtype):
-                tc.linear_wgrad(dy, x2, dw32, db32)
+                tc.linear_wgrad(dy, x2, dw32, None if ready is not None else db32)
             else:
-                _chk(lib().dcp_linear_wgrad_simt(dy.data_ptr(), x2.data_ptr(), dw32.data_ptr(), _p(db32), M, N, K, _dt(x2), _stream()))
+                _chk(lib().dcp_linear_wgrad_simt(dy.data_ptr(), x2.data_ptr(), dw32.data_ptr(), None if ready is not None else _p(db32), M, N, K,
+                                                 _dt(x2), _stream()))
             dw = dw32 if ctx.w_dtype == torch.float32 else _cast(dw32, ctx.w_dtype)
             if has_b:
                 db = db32 if ctx.w_dtype == torch.float32 else _cast(db32, ctx.w_dtype)
@@ -647,13 +670,12 @@ class _AddLayerNorm(Function):
         dx = torch.empty_like(ssum)
         dg = torch.empty(Cc, dtype=torch.float32, device=ssum.device)
         db = torch.empty(Cc, dtype=torch.float32, device=ssum.device)
-        if dsum is None:
-            _chk(lib().dcp_layernorm_bwd(ssum.data_ptr(), dy.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx.data_ptr(), dg.data_ptr(),
-                                         db.data_ptr(), rows, Cc, _dt(ssum), _stream()))
-        else:
+        if dsum is not None:
             dsum = dsum.reshape(rows, Cc); dsum = dsum if dsum.is_contiguous() else dsum.contiguous()
-            _chk(lib().dcp_add_layernorm_bwd(ssum.data_ptr(), dy.data_ptr(), dsum.data_ptr(), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
-                                             dx.data_ptr(), dg.data_ptr(), db.data_ptr(), rows, Cc, _dt(ssum), _stream()))
+        cs = torch.empty(Cc, dtype=torch.float32, device=ssum.device)
+        _chk(lib().dcp_add_layernorm_bwd(ssum.data_ptr(), dy.data_ptr(), _p(dsum), gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                         dx.data_ptr(), dg.data_ptr(), db.data_ptr(), cs.data_ptr(), rows, Cc, _dt(ssum), _stream()))
+        _offer_colsum(dx, cs)        # dx is the output gradient of the Linear that produced `res`: its bias gradient is ready
         dx = dx.view(ctx.shape)
         return dx, dx, dg, db, None
 
@@ -713,7 +735,14 @@ class _GELU(Function):
         (x,) = ctx.saved_tensors
         dy = dy if dy.is_contiguous() else dy.contiguous()
         dx = torch.empty_like(x)
-        _chk(lib().dcp_gelu_bwd(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), _dt(x), _stream()))
+        Cc = x.shape[-1]
+        if x.dim() >= 2 and x.dtype in (torch.float32, torch.bfloat16) and Cc % (4 if x.dtype == torch.float32 else 8) == 0 and x.numel() >= (1 << 16):
+            # also sums dx over the rows: the bias gradient of the Linear that produced x
+            cs = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            _chk(lib().dcp_gelu_bwd_colsum(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), cs.data_ptr(), x.numel() // Cc, Cc, _dt(x), _stream()))
+            _offer_colsum(dx, cs)
+        else:
+            _chk(lib().dcp_gelu_bwd(x.data_ptr(), dy.data_ptr(), dx.data_ptr(), x.numel(), _dt(x), _stream()))
         return dx
 
 

@@ -139,3 +139,26 @@ def _shadow_worker(rank, world, port):
 
 def test_bf16_shadow_follows_the_fused_optimizer():
     dcp.spawn(_shadow_worker, args=(1, free_port()), nprocs=1, join=True)
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_gelu_backward_hands_the_bias_gradient_to_the_linear(dtype):
+    """GELU backward sums its dx over the rows; the Linear below takes that as its bias gradient (ops/cuda.py _COLSUMS)."""
+    from distributed_compute_pytorch_b200.ops import cuda as K
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    rows, Cin, Cout = 1000, 64, 256                      # 1000 rows: ragged against the 16-row strips of the kernel
+    lin = dcp.ops.Linear(Cin, Cout).to(dev)
+    act = dcp.ops.GELU()
+    x = torch.randn(rows, Cin, device=dev, dtype=dtype)
+    w = torch.randn(rows, Cout, device=dev)
+    K._COLSUMS.clear()
+    (act(lin(x)).float() * w).sum().backward()
+    assert not K._COLSUMS                                  # the offer was taken
+    ref = torch.nn.Linear(Cin, Cout).to(dev)
+    ref.load_state_dict(lin.state_dict())
+    (F.gelu(ref(x.float()), approximate="tanh") * w).sum().backward()
+    tol = 2e-3 if dtype == torch.float32 else 6e-2
+    den = ref.bias.grad.abs().max().item()
+    assert (lin.bias.grad - ref.bias.grad).abs().max().item() / den < tol
+    assert (lin.weight.grad - ref.weight.grad).abs().max().item() / ref.weight.grad.abs().max().item() < tol
