@@ -261,6 +261,23 @@ int dcp_counter_advance(void* counter, cudaStream_t s);
 int dcp_layernorm_fwd(const void* x, void* y, const float* gamma, const float* beta, float* mean, float* rstd, int rows, int C, float eps, int dtype, cudaStream_t s);
 // dgamma / dbeta: fp32 [C], zeroed here.
 int dcp_layernorm_bwd(const void* x, const void* dy, const float* gamma, const float* mean, const float* rstd, void* dx, float* dgamma, float* dbeta, int rows, int C, int dtype, cudaStream_t s);
+// y = LayerNorm(x + res), sum_out = x + res (the residual stream after the add): one pass instead of an add kernel plus a
+// LayerNorm.  Row length as in the warp-per-row path of dcp_layernorm_fwd (C a multiple of the 16-byte vector, <= 1024 bf16 /
+// 512 fp32 elements), 16-byte aligned pointers; returns -1 otherwise (the caller falls back to add + layer norm).
+int dcp_add_layernorm_fwd(const void* x, const void* res, void* sum_out, void* y, const float* gamma, const float* beta, float* mean, float* rstd, int rows, int C, float eps, int dtype, cudaStream_t s);
+// Backward of dcp_add_layernorm_fwd: dx = LayerNorm-backward(dy) + dsum, where dsum is the gradient that reached the sum from
+// the residual path (the same dx is the gradient of both x and res).  x = the saved sum.  dgamma / dbeta: fp32 [C], zeroed here.
+// dxsum: optional fp32 [C] that receives the column sums of dx (zeroed here) - the bias gradient of the Linear that produced res.
+int dcp_add_layernorm_bwd(const void* x, const void* dy, const void* dsum, const float* gamma, const float* mean, const float* rstd, void* dx, float* dgamma, float* dbeta, float* dxsum, int rows, int C, int dtype, cudaStream_t s);
+// Token + position embedding of a transformer: out[r, :] = T(wte[idx[r], :] + wpe[r % Tlen, :]) for r < rows = B * Tlen.
+// fp32 tables, f32 / bf16 output, C a multiple of 4.  (One gather kernel instead of two gathers, an add and a cast.)
+int dcp_embed_fwd(const long* idx, const float* wte, const float* wpe, void* out, long rows, int Tlen, int C, int dtype, cudaStream_t s);
+// Backward: dwte[idx[r], :] += dy[r, :] (vector reductions; dwte fp32 [V, C] zeroed by the caller - rows that are no token stay
+// zero) and dwpe[t, :] = sum_b dy[b * Tlen + t, :] for t < Tlen (plain stores; the caller zeroes the rows beyond Tlen).
+int dcp_embed_bwd(const long* idx, const void* dy, float* dwte, float* dwpe, long rows, int Tlen, int C, int dtype, cudaStream_t s);
+// GELU backward over a [rows, C] matrix that also produces the column sums of dx (fp32 [C], zeroed here): C a multiple of the
+// 16-byte vector, aligned pointers (-1 otherwise; the caller falls back to dcp_gelu_bwd).
+int dcp_gelu_bwd_colsum(const void* x, const void* dy, void* dx, float* colsum, long rows, int C, int dtype, cudaStream_t s);
 int dcp_gelu_fwd(const void* x, void* y, long n, int dtype, cudaStream_t s);
 int dcp_gelu_bwd(const void* x, const void* dy, void* dx, long n, int dtype, cudaStream_t s);
 
