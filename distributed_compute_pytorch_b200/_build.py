@@ -25,8 +25,17 @@ OBJ = ROOT / "build" / "obj"
 HOST_SOURCES = ["host/store.cpp", "host/mesh.cpp", "ddp/reducer.cpp"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "--use_fast_math", "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr",
+    "-Xcompiler", "-fPIC", "-Xptxas", "-v", "--expt-relaxed-constexpr",
 ]
+# --use_fast_math (approximate expf / logf / division / rsqrt, flush-to-zero) only where the result feeds bf16 / tf32 tensor-core
+# operands or a dropout mask.  The numerically sensitive kernels - losses, BatchNorm statistics, every optimizer update (stand-alone,
+# fused with the collective, and the data-parallel tail of the flagship step) - are compiled with IEEE arithmetic so that long runs
+# track torch.optim (tests/test_optimizer_drift_gpu.py).
+PRECISE_SOURCES = {"ops/loss.cu", "ops/batchnorm.cu", "ops/optim.cu", "ops/convnet_dp.cu", "coll/fused_opt.cu"}
+
+
+def _flags_for(src: str) -> list[str]:
+    return NVCC_FLAGS + ([] if src in PRECISE_SOURCES else ["--use_fast_math"])
 
 
 def _cuda_sources() -> list[str]:
@@ -91,7 +100,7 @@ def build_cuda(force: bool = False, verbose: bool = False) -> Path | None:
         obj = OBJ / (s.replace("/", "_") + ".o")
         objs.append(obj)
         if force or _newer(obj, [src] + hdrs):
-            cmd = [nvcc] + NVCC_FLAGS + os.environ.get("DCP_NVCC_EXTRA", "").split() + ["-I", str(ROOT / "include"), "-I", str(CSRC), "-c", str(src), "-o", str(obj)]
+            cmd = [nvcc] + _flags_for(s) + os.environ.get("DCP_NVCC_EXTRA", "").split() + ["-I", str(ROOT / "include"), "-I", str(CSRC), "-c", str(src), "-o", str(obj)]
             jobs.append((cmd, OBJ / (obj.name + ".log")))
     if jobs:
         with ThreadPoolExecutor(max_workers=min(8, len(jobs))) as ex:
