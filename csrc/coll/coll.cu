@@ -64,7 +64,7 @@ struct AllreduceOneshotBody {
       for (int p = 0; p < W; ++p) reinterpret_cast<T*>(c.peer[p] + my_slot)[i] = val;
     }
     uint32_t e = dcp_signal_all(c, chan);
-    dcp_wait_all(c, chan, e);
+    if (!dcp_wait_all(c, chan, e)) return;
     const char* base = c.peer[c.rank] + region_off + (size_t)half * W * slot_bytes;
     for (size_t v = tid; v < nvec; v += stride) {
       Acc acc[V];
@@ -122,7 +122,7 @@ struct AllreduceTwoshotBody {
         for (int i = 0; i < V; ++i) reinterpret_cast<T*>(mine)[v * V + i] = in[v * V + i];
       for (size_t i = nvec * V + tid; i < n; i += stride) reinterpret_cast<T*>(mine)[i] = in[i];
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     const Span s = rank_slice(nvec, W, c.rank);
     // vector v is always handled by the thread with v % stride == tid - in copy-in, reduce and copy-out and
     // on every rank - so the CTA that staged an element (and chose the parity half) is the one that reads it
@@ -174,7 +174,7 @@ struct AllreduceTwoshotBody {
         for (int p = 0; p < W; ++p) reinterpret_cast<T*>(c.peer[p] + off)[i] = r;
       }
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     if (out != nullptr) {
       const bool al = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
       if (al) for (size_t v = tid; v < nvec; v += stride) st16(out + v * V, ld16(mine + v * 16));
@@ -284,7 +284,7 @@ struct AllreduceStagedBody {
       const size_t lo = b * 16, hi = e * 16 < nbytes ? e * 16 : nbytes;
       if (hi > lo) copy_bytes(c.peer[p] + off + (size_t)c.rank * per * 16, in + lo, hi - lo, tid, stride, p != c.rank);
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     // 2 + 3. reduce own slice from the local slots, publish it
     {
       const size_t b = per * c.rank < nv ? per * c.rank : nv, e = b + per < nv ? b + per : nv;
@@ -314,7 +314,7 @@ struct AllreduceStagedBody {
         }
       }
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     // 4. copy out, slice by slice (chunk index relative to the slice start = the index its owner used)
     char* out = reinterpret_cast<char*>(a.out);
     for (int q = 0; q < W; ++q) {
@@ -341,7 +341,7 @@ struct BroadcastBody {
     int sym = a.sym;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
     if (!sym) off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * half_bytes;
-    else dcp_barrier(c, chan);  // peers may still be reading their copy of the tensor
+    else if (!dcp_barrier(c, chan)) return;  // peers may still be reading their copy of the tensor
     if (c.rank == root) {
       const char* src = sym ? c.peer[root] + off : data;
       if (c.nvls && c.world > 2 && (off % 16 == 0)) {      // two ranks: one plain peer store per vector runs at link rate, a multicast store does not
@@ -353,7 +353,7 @@ struct BroadcastBody {
         }
       }
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     if (!sym) {
       if (c.rank != root) copy_bytes(data, c.peer[c.rank] + off, nbytes, tid, stride, false);
       dcp_gcalls_finish(c.peer[c.rank], chan);
@@ -379,7 +379,7 @@ struct BroadcastRelayBody {
     const int root = a.root, chan = a.chan, sym = a.sym, W = c.world;
     const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
     if (!sym) off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * a.half_bytes;
-    else dcp_barrier(c, chan);                       // peers may still be reading their copy of the tensor
+    else if (!dcp_barrier(c, chan)) return;                       // peers may still be reading their copy of the tensor
     char* me = c.peer[c.rank];
     __syncthreads();                                 // the barrier's epoch update (thread 0) is visible to everyone below
     const uint32_t e0 = *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x));
@@ -403,8 +403,7 @@ struct BroadcastRelayBody {
         if ((int)threadIdx.x < W) st_release_sys(dcp_sig(c.peer[threadIdx.x], chan, blockIdx.x, root), e0 + 1 + k);
       }
       // relay this rank's slice (the root relays its own slice too: nobody else has it)
-      if (threadIdx.x == 0) wait_ge(c, dcp_sig(me, chan, blockIdx.x, root), e0 + 1 + k);
-      __syncthreads();
+      if (!__syncthreads_and(threadIdx.x != 0 || wait_ge(c, dcp_sig(me, chan, blockIdx.x, root), e0 + 1 + k))) return;   // the root never delivered
       {
         const Span sl = rank_slice(nvec, W, c.rank);
         const size_t len = sl.end - sl.begin, kb = sl.begin + len * k / kRelaySub, ke = sl.begin + len * (k + 1) / kRelaySub;
@@ -423,7 +422,7 @@ struct BroadcastRelayBody {
     // closing barrier on epoch e0 + kRelaySub + 1 (the epoch word still holds e0: bring it to e0 + kRelaySub first)
     __syncthreads();
     if (threadIdx.x == 0) *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x)) = e0 + kRelaySub;
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     if (!sym) {
       if (c.rank != root) copy_bytes(data, me + off, nbytes, tid, stride, false);
       dcp_gcalls_finish(me, chan);
@@ -449,7 +448,7 @@ struct AllgatherBody {
     int sym = a.sym;
   const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x, stride = (size_t)gridDim.x * blockDim.x;
     if (!sym) off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * half_bytes;
-    else dcp_barrier(c, chan);
+    else if (!dcp_barrier(c, chan)) return;
     const size_t my = off + (size_t)c.rank * slot_stride;
     if (c.nvls && c.world > 2 && root < 0 && (my % 16 == 0)) {   // two ranks: one plain peer store per vector is the faster path
       push_all_nvls(c, my, in, nbytes, tid, stride);        // one store per 16 bytes instead of W: egress drops W-fold
@@ -459,7 +458,7 @@ struct AllgatherBody {
         copy_bytes(c.peer[p] + my, in, nbytes, tid, stride, true);
       }
     }
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     if (!sym) {
       if (root < 0 || c.rank == root)
         for (int p = 0; p < c.world; ++p) copy_bytes(out + (size_t)p * out_stride, c.peer[c.rank] + off + (size_t)p * slot_stride, nbytes, tid, stride, false);
@@ -485,7 +484,7 @@ struct ScatterBody {
     off += (size_t)(dcp_gcalls(c.peer[c.rank], chan) & 1u) * half_bytes;
     if (c.rank == root)
       for (int p = 0; p < c.world; ++p) copy_bytes(c.peer[p] + off, in + (size_t)p * in_stride, nbytes, tid, stride, true);
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     copy_bytes(out, c.peer[c.rank] + off, nbytes, tid, stride, false);
     dcp_gcalls_finish(c.peer[c.rank], chan);
   }
@@ -555,7 +554,7 @@ struct ReduceScatterBody {
         const T* piece = root < 0 ? in + (size_t)p * pstride : in;
         copy_bytes(c.peer[p] + off + (size_t)c.rank * slot, reinterpret_cast<const char*>(piece), n_out * sizeof(T), tid, stride, p != c.rank);
       }
-      dcp_barrier(c, chan);
+      if (!dcp_barrier(c, chan)) return;
       if (owner) {
         const char* src[DCP_MAX_RANKS];
 #pragma unroll
@@ -576,7 +575,7 @@ struct ReduceScatterBody {
       return;
     }
     // ---- pull from the peers' symmetric tensors
-    dcp_barrier(c, chan);
+    if (!dcp_barrier(c, chan)) return;
     if (owner) {
       const size_t first = root < 0 ? (size_t)c.rank * n_out : 0;
       const size_t soff = off + first * sizeof(T);
@@ -628,7 +627,7 @@ struct ReduceScatterBody {
         out[i] = Tr::down(red_finish<T>(acc, scale, W, op));
       }
     }
-    dcp_barrier(c, chan);                 // the input is the caller's tensor: nobody may still read it after the call
+    if (!dcp_barrier(c, chan)) return;                 // the input is the caller's tensor: nobody may still read it after the call
   }
 };
 

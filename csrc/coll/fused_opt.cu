@@ -46,7 +46,7 @@ struct FusedRsOptAgBody {
   const size_t vb = min(per * c.rank, nvec), ve = min(vb + per, nvec);
   const OptHyper H = load_hyper<KIND>(hp);
   const float gs = hp[7], inv_w = 1.f / (float)W;
-  dcp_barrier(c, chan);
+  if (!dcp_barrier(c, chan)) return;
   uint4 raw[DCP_MAX_RANKS], nxt[DCP_MAX_RANKS];
   if (vb + tid < ve) fetch(c, goff, vb + tid, raw);
   for (size_t v = vb + tid; v < ve; v += stride) {
@@ -114,7 +114,7 @@ struct FusedRsOptAgBody {
 #pragma unroll
     for (int p = 0; p < DCP_MAX_RANKS; ++p) raw[p] = nxt[p];
   }
-  dcp_barrier(c, chan);
+  if (!dcp_barrier(c, chan)) return;
   }
 };
 }  // namespace

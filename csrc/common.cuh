@@ -155,20 +155,24 @@ __device__ __forceinline__ void dcp_gcalls_finish(char* heap, int chan) {
 // Release/acquire at system scope: writes issued by any thread of this CTA before the call are
 // visible to the peer CTAs after they return, and vice versa.  Epochs increase monotonically, so the
 // signal words never need resetting and the barrier is CUDA-graph replayable.
-__device__ __forceinline__ void dcp_barrier(const DcpDevCtx& c, int chan) {
+// Returns false (to every thread of the CTA) when a peer did not arrive within ctx.timeout_ns: the caller then skips its data
+// phase instead of reducing / copying whatever happens to be in the buffers (the error flag is already raised for the host).
+__device__ __forceinline__ bool dcp_barrier(const DcpDevCtx& c, int chan) {
   __syncthreads();
   char* me = c.peer[c.rank];
   uint32_t* ep = dcp_epoch(me, chan, blockIdx.x);
   const uint32_t e = *((volatile uint32_t*)ep) + 1;
+  int ok = 1;
   if (threadIdx.x < c.world) {
     const int peer = threadIdx.x;
     // the release store is cumulative over everything the CTA wrote before the __syncthreads() above: no separate fence
     // (st.release.sys already costs one system-scope drain; a second __threadfence_system() in front doubled it)
     st_release_sys(dcp_sig(c.peer[peer], chan, blockIdx.x, c.rank), e);
-    wait_ge(c, dcp_sig(me, chan, blockIdx.x, peer), e);
+    ok = wait_ge(c, dcp_sig(me, chan, blockIdx.x, peer), e) ? 1 : 0;
   }
-  __syncthreads();
+  ok = __syncthreads_and(ok);
   if (threadIdx.x == 0) *((volatile uint32_t*)ep) = e;
+  return ok != 0;
 }
 
 // Signal-only / wait-only halves (used when the payload was pushed before the signal).
@@ -179,9 +183,11 @@ __device__ __forceinline__ uint32_t dcp_signal_all(const DcpDevCtx& c, int chan)
   if (threadIdx.x < c.world) st_release_sys(dcp_sig(c.peer[threadIdx.x], chan, blockIdx.x, c.rank), e);
   return e;
 }
-__device__ __forceinline__ void dcp_wait_all(const DcpDevCtx& c, int chan, uint32_t e) {
+__device__ __forceinline__ bool dcp_wait_all(const DcpDevCtx& c, int chan, uint32_t e) {
   char* me = c.peer[c.rank];
-  if (threadIdx.x < c.world) wait_ge(c, dcp_sig(me, chan, blockIdx.x, threadIdx.x), e);
-  __syncthreads();
+  int ok = 1;
+  if (threadIdx.x < c.world) ok = wait_ge(c, dcp_sig(me, chan, blockIdx.x, threadIdx.x), e) ? 1 : 0;
+  ok = __syncthreads_and(ok);
   if (threadIdx.x == 0) *((volatile uint32_t*)dcp_epoch(me, chan, blockIdx.x)) = e;
+  return ok != 0;       // false: a peer never signalled - skip the data phase (see dcp_barrier)
 }

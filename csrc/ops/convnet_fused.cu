@@ -345,11 +345,12 @@ __global__ void __launch_bounds__(kC1Lanes * 32) k_conv1_wgrad(const float* __re
     for (int p = 0; p < W; ++p) reinterpret_cast<float*>(cx.peer[p] + half_off)[cx.rank * 320 + threadIdx.x] = v;
   }
   __syncthreads();
+  int arrived = 1;
   if (threadIdx.x < W) {
     st_release_sys(dcp_sig(cx.peer[threadIdx.x], ar.chan, ar.blk, cx.rank), s_epoch);
-    wait_ge(cx, dcp_sig(me, ar.chan, ar.blk, threadIdx.x), s_epoch);
+    arrived = wait_ge(cx, dcp_sig(me, ar.chan, ar.blk, threadIdx.x), s_epoch) ? 1 : 0;
   }
-  __syncthreads();
+  if (!__syncthreads_and(arrived)) return;      // a peer never delivered: leave the gradient un-reduced, the error flag is raised
   if (threadIdx.x < 320) {
     const float* slots = reinterpret_cast<const float*>(me + half_off);
     float sum = 0.f;
