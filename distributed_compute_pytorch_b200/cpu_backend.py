@@ -14,7 +14,7 @@ from typing import List, Optional
 import torch
 
 from ._native import host_lib
-from .types import ReduceOp
+from .types import ReduceOp, Work
 
 _SMALL_BYTES = 32 * 1024
 
@@ -86,23 +86,63 @@ class CpuBackend:
 
     # ---- point to point ---------------------------------------------------------------------------
     def send(self, tensor: torch.Tensor, dst: int, tag: int = 0) -> None:
+        self._drain()
         flat, _ = self._flat(tensor)
         self._send(flat, dst, tag)
 
     def recv(self, tensor: torch.Tensor, src: int, tag: int = 0) -> None:
+        self._drain()
         flat, back = self._flat(tensor)
         self._recv(flat, src, tag)
         if back:
             tensor.detach().copy_(flat.view(tensor.shape))
 
+    # Non-blocking point to point: one worker thread owns the sending direction of the sockets and one the receiving direction
+    # (the native calls release the GIL; the two directions of a socket are independent byte streams), so the usual exchange -
+    # every rank posts irecv, then isend, then waits - makes progress on both.  Operations of one kind complete in the order
+    # they were posted; blocking calls and collectives first wait for everything still in flight.
+    def _worker(self, kind: str):
+        from concurrent.futures import ThreadPoolExecutor
+        if getattr(self, "_workers", None) is None:
+            self._workers, self._pending = {}, []
+        if kind not in self._workers:
+            self._workers[kind] = ThreadPoolExecutor(max_workers=1, thread_name_prefix=f"dcp-{kind}")
+        return self._workers[kind]
+
+    def _drain(self) -> None:
+        pend = getattr(self, "_pending", None)
+        if pend:
+            self._pending = []
+            for f in pend:
+                f.result()
+
+    def isend(self, tensor: torch.Tensor, dst: int, tag: int = 0) -> Work:
+        flat, _ = self._flat(tensor)
+        fut = self._worker("tx").submit(self._send, flat, dst, tag)
+        self._pending.append(fut)
+        return Work(done=False, finalize=fut.result, poll=fut.done, keep=(tensor, flat))
+
+    def irecv(self, tensor: torch.Tensor, src: int, tag: int = 0) -> Work:
+        flat, back = self._flat(tensor)
+
+        def job():
+            self._recv(flat, src, tag)
+            if back:
+                tensor.detach().copy_(flat.view(tensor.shape))
+        fut = self._worker("rx").submit(job)
+        self._pending.append(fut)
+        return Work(done=False, finalize=fut.result, poll=fut.done, keep=(tensor, flat))
+
     # ---- collectives ------------------------------------------------------------------------------
     def barrier(self) -> None:
+        self._drain()
         if self.world == 1:
             return
         token = torch.zeros(1, dtype=torch.int32)
         self.all_reduce(token, ReduceOp.SUM)
 
     def broadcast(self, tensor: torch.Tensor, src: int) -> None:
+        self._drain()
         if self.world == 1:
             return
         flat, back = self._flat(tensor)
@@ -123,6 +163,7 @@ class CpuBackend:
             tensor.detach().copy_(flat.view(tensor.shape))
 
     def all_reduce(self, tensor: torch.Tensor, op: ReduceOp = ReduceOp.SUM) -> None:
+        self._drain()
         if self.world == 1:
             return
         flat, back = self._flat(tensor)
@@ -160,6 +201,7 @@ class CpuBackend:
             tensor.detach().copy_(flat.view(tensor.shape))
 
     def reduce(self, tensor: torch.Tensor, dst: int, op: ReduceOp = ReduceOp.SUM) -> None:
+        self._drain()
         if self.world == 1:
             return
         flat, back = self._flat(tensor)
@@ -180,6 +222,7 @@ class CpuBackend:
             self._send(flat, dst, tag=31)
 
     def all_gather(self, outputs: List[torch.Tensor], tensor: torch.Tensor) -> None:
+        self._drain()
         flat, _ = self._flat(tensor)
         W, r = self.world, self.rank
         outputs[r].detach().copy_(tensor.detach())
@@ -192,11 +235,13 @@ class CpuBackend:
                 out.copy_(buf.view(out.shape))
 
     def all_gather_into_tensor(self, output: torch.Tensor, tensor: torch.Tensor) -> None:
+        self._drain()
         out = output.detach()
         assert out.is_contiguous() and out.numel() == tensor.numel() * self.world
         self.all_gather(list(out.view(-1).chunk(self.world)), tensor.detach().reshape(-1))
 
     def gather(self, tensor: torch.Tensor, gather_list: Optional[List[torch.Tensor]], dst: int) -> None:
+        self._drain()
         flat, _ = self._flat(tensor)
         if self.rank == dst:
             for src in range(self.world):
@@ -212,6 +257,7 @@ class CpuBackend:
             self._send(flat, dst, tag=51)
 
     def scatter(self, tensor: torch.Tensor, scatter_list: Optional[List[torch.Tensor]], src: int) -> None:
+        self._drain()
         if self.rank == src:
             for dst in range(self.world):
                 if dst == src:
@@ -223,6 +269,7 @@ class CpuBackend:
             self.recv(tensor, src, tag=61)
 
     def reduce_scatter(self, output: torch.Tensor, input_list: List[torch.Tensor], op: ReduceOp = ReduceOp.SUM) -> None:
+        self._drain()
         W, r = self.world, self.rank
         acc: List[Optional[torch.Tensor]] = [None] * W
         acc[r] = input_list[r].detach().contiguous().view(-1).clone()
@@ -239,10 +286,14 @@ class CpuBackend:
         output.detach().copy_(res.view(output.shape))
 
     def reduce_scatter_tensor(self, output: torch.Tensor, input: torch.Tensor, op: ReduceOp = ReduceOp.SUM) -> None:
+        self._drain()
         inp = input.detach().contiguous().view(-1)
         self.reduce_scatter(output, list(inp.chunk(self.world)), op)
 
     def close(self) -> None:
+        for ex in (getattr(self, "_workers", None) or {}).values():
+            ex.shutdown(wait=True)
+        self._workers = None
         if self._mesh:
             self._lib.dcp_mesh_destroy(self._mesh)
             self._mesh = None

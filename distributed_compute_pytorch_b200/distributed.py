@@ -191,13 +191,22 @@ def recv(tensor: torch.Tensor, src: Optional[int] = None, group=None, tag: int =
 
 
 def isend(tensor, dst=None, group=None, tag=0, group_dst=None) -> Work:
-    send(tensor, dst, group, tag, group_dst)
-    return _done(True, _backend_for(tensor, _world(group)))
+    """Non-blocking send: returns at once; ``wait()`` on the handle completes it (CPU: joins the sender thread; CUDA: orders the
+    caller's stream behind the transfer).  The tensor must not be modified before that."""
+    pg = _world(group)
+    dst = dst if dst is not None else group_dst
+    if dst == pg.rank_:
+        raise ValueError("Invalid destination rank: destination rank should not be the same as the rank of the current process.")
+    return _backend_for(tensor, pg).isend(tensor, dst, tag)
 
 
 def irecv(tensor, src=None, group=None, tag=0, group_src=None) -> Work:
-    recv(tensor, src, group, tag, group_src)
-    return _done(True, _backend_for(tensor, _world(group)))
+    """Non-blocking receive: the tensor holds the data once ``wait()`` on the handle has returned."""
+    pg = _world(group)
+    src = src if src is not None else group_src
+    if src is None:
+        raise NotImplementedError("irecv from any source is not supported; pass src")
+    return _backend_for(tensor, pg).irecv(tensor, src, tag)
 
 
 # ---- collectives ----------------------------------------------------------------------------------

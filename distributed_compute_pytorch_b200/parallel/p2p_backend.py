@@ -380,18 +380,62 @@ class P2PBackend:
         self.reduce_scatter_tensor(output, torch.cat([t.detach().reshape(-1) for t in input_list]), op)
 
     def send(self, tensor: torch.Tensor, dst: int, tag: int = 0) -> None:
+        self._join_async()
         t, _ = self._contig(tensor)
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_send(self._h, t.data_ptr(), t.numel() * t.element_size(), dst, self._stream())
         self._check(rc, "send")
 
     def recv(self, tensor: torch.Tensor, src: int, tag: int = 0) -> None:
+        self._join_async()
         t, back = self._contig(tensor)
         with torch.cuda.device(self._torch_dev):
             rc = self.lib.dcp_recv(self._h, t.data_ptr(), t.numel() * t.element_size(), src, self._stream())
         self._check(rc, "recv")
         if back:
             tensor.detach().copy_(t)
+
+    # Non-blocking point to point: sends are queued on one side stream and receives on another (each ordered behind the
+    # caller's current stream), so a receive kernel that is still waiting for its peer never sits in front of this rank's own
+    # send - the exchange "irecv, isend, wait both" that every rank runs at once makes progress.  Operations of one kind stay
+    # ordered among themselves; the Work's wait() orders the caller's stream behind the transfer (no host block).
+    def _async_stream(self, kind: str):
+        st = getattr(self, "_p2p_streams", None)
+        if st is None:
+            st = self._p2p_streams = {}
+        if kind not in st:
+            st[kind] = torch.cuda.Stream(self._torch_dev)
+        return st[kind]
+
+    def _join_async(self) -> None:
+        """Blocking transfers and collectives run behind everything still queued on the two side streams."""
+        for s in (getattr(self, "_p2p_streams", None) or {}).values():
+            torch.cuda.current_stream(self._torch_dev).wait_stream(s)
+
+    def isend(self, tensor: torch.Tensor, dst: int, tag: int = 0) -> Work:
+        t, _ = self._contig(tensor)
+        s = self._async_stream("tx")
+        s.wait_stream(torch.cuda.current_stream(self._torch_dev))
+        with torch.cuda.device(self._torch_dev):
+            rc = self.lib.dcp_send(self._h, t.data_ptr(), t.numel() * t.element_size(), dst, s.cuda_stream)
+        self._check(rc, "isend")
+        t.record_stream(s)
+        ev = torch.cuda.Event(); ev.record(s)
+        return Work(event=ev, keep=(tensor, t))
+
+    def irecv(self, tensor: torch.Tensor, src: int, tag: int = 0) -> Work:
+        t, back = self._contig(tensor)
+        s = self._async_stream("rx")
+        s.wait_stream(torch.cuda.current_stream(self._torch_dev))
+        with torch.cuda.device(self._torch_dev):
+            rc = self.lib.dcp_recv(self._h, t.data_ptr(), t.numel() * t.element_size(), src, s.cuda_stream)
+        self._check(rc, "irecv")
+        if back:
+            with torch.cuda.stream(s):
+                tensor.detach().copy_(t)
+        t.record_stream(s)
+        ev = torch.cuda.Event(); ev.record(s)
+        return Work(event=ev, keep=(tensor, t))
 
     def barrier(self) -> None:
         """Device barrier across ranks + host sync (so it also orders host-side effects)."""

@@ -24,8 +24,11 @@ class Work:
     collective's stream (no host block), matching the behaviour users expect from NCCL work objects.
     """
 
-    def __init__(self, event=None, stream=None, finalize: Optional[Callable[[], None]] = None, done: bool = True):
+    def __init__(self, event=None, stream=None, finalize: Optional[Callable[[], None]] = None, done: bool = True,
+                 poll: Optional[Callable[[], bool]] = None, keep=None):
         self._event, self._stream, self._finalize, self._done = event, stream, finalize, done
+        self._poll = poll            # host-side operations in flight (CPU isend / irecv): True once finished
+        self._keep = keep            # tensors that must outlive the operation
 
     def wait(self, timeout=None) -> bool:
         if self._finalize is not None:
@@ -38,6 +41,8 @@ class Work:
         return True
 
     def is_completed(self) -> bool:
+        if self._poll is not None and self._finalize is not None:
+            return bool(self._poll())
         if self._event is not None:
             return bool(self._event.query())
         return self._done and self._finalize is None

@@ -88,6 +88,37 @@ def test_all_primitives(world):
     dcp.spawn(_worker, args=(world, free_port()), nprocs=world, join=True)
 
 
+def _exchange(rank, world, port):
+    """The exchange every rank runs at once - post irecv, post isend, wait both - needs receives and sends to progress
+    independently; with blocking stand-ins it deadlocks.  8 MB messages do not fit a socket buffer."""
+    dist = init(rank, world, port, "gloo")
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    for n in (5, 2_000_000):
+        inbox = torch.empty(n)
+        out = torch.full((n,), float(rank))
+        r = dist.irecv(inbox, src=prv)
+        s = dist.isend(out, dst=nxt)
+        assert r.wait() and s.wait()
+        assert r.is_completed() and s.is_completed()
+        assert torch.equal(inbox, torch.full((n,), float(prv)))
+    # several operations in flight, completed out of posting order, followed by a collective (which drains whatever is pending)
+    bufs = [torch.empty(1000) for _ in range(3)]
+    rs = [dist.irecv(b, src=prv, tag=k) for k, b in enumerate(bufs)]
+    ss = [dist.isend(torch.full((1000,), float(10 * rank + k)), dst=nxt, tag=k) for k in range(3)]
+    t = torch.ones(4); dist.all_reduce(t)
+    assert t[0].item() == world
+    for w in reversed(rs + ss):
+        w.wait()
+    for k, b in enumerate(bufs):
+        assert torch.equal(b, torch.full((1000,), float(10 * prv + k)))
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_isend_irecv_exchange_does_not_deadlock(world):
+    dcp.spawn(_exchange, args=(world, free_port()), nprocs=world, join=True)
+
+
 def _failing(rank, world, port):
     dist = init(rank, world, port, "gloo")
     if rank == 1:

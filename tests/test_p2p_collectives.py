@@ -111,6 +111,21 @@ def _worker(rank, world, port, symm_mode):
         else:
             dist.recv(buf, src=prv); dist.send(torch.full((n,), float(rank), device=dev), dst=nxt)
         assert torch.equal(buf, torch.full((n,), float(prv), device=dev))
+    # the same ring with EVERY rank posting irecv, then isend, then waiting (receives and sends run on separate side streams;
+    # with blocking stand-ins each rank's receive kernel would sit in front of its own send)
+    for n in (1000, 3 * (1 << 20) + 1):
+        buf = torch.empty(n, device=dev); out = torch.full((n,), float(rank), device=dev)
+        r = dist.irecv(buf, src=prv); s = dist.isend(out, dst=nxt)
+        r.wait(); s.wait()
+        assert torch.equal(buf, torch.full((n,), float(prv), device=dev))
+        torch.cuda.synchronize(); assert r.is_completed() and s.is_completed()
+    # ... and a blocking pair right behind the non-blocking ones (ordered after them)
+    buf = torch.empty(77, device=dev)
+    if rank % 2 == 0:
+        dist.send(torch.full((77,), float(rank), device=dev), dst=nxt); dist.recv(buf, src=prv)
+    else:
+        dist.recv(buf, src=prv); dist.send(torch.full((77,), float(rank), device=dev), dst=nxt)
+    assert torch.equal(buf, torch.full((77,), float(prv), device=dev))
     w = dist.all_reduce(torch.ones(3, device=dev), async_op=True); w.wait(); torch.cuda.synchronize(); assert w.is_completed()
     # stress: 200 back-to-back small all_reduces without host sync
     acc = torch.zeros(64, device=dev)
