@@ -414,7 +414,15 @@ int pick_bn(int N) { return N <= 32 ? 32 : (N <= 64 ? 64 : 128); }
 
 }  // namespace
 
+// -1: DCP_GEMM_NARROW decides; 0 / 1 / 2: the caller decides for the launches that follow (two such GEMMs issued on two streams
+// to run side by side want the wide tiles: 72 CTAs each, both resident at once) - see dcp_gemm_set_narrow
+static int g_gemm_narrow_override = -1;
+
 extern "C" {
+// Host-side launch choice for wide, shallow fp32 / tf32 problems: 64-column tiles (twice the CTAs) when 1, 128-column when 0,
+// the DCP_GEMM_NARROW default when -1.  Affects the launches issued after the call from this process.
+void dcp_gemm_set_narrow(int v) { g_gemm_narrow_override = v; }
+
 
 // C[M,N] (+)= op(A) . op(B)^T with fp32 accumulation on tcgen05.
 //   a_mn = 0: A is [M][K] row-major (lda);   a_mn = 1: A is [K][M] row-major (lda)
@@ -455,7 +463,8 @@ int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, in
   {
     // wide, shallow problems (fc1's weight / data gradient: 128 x 9216, K = 128) are pure streaming: with 128-column tiles only
     // 72 CTAs exist and half the SMs (and their share of the memory system) idle; 64-column tiles double the CTAs
-    static const int narrow = [] { const char* e = getenv("DCP_GEMM_NARROW"); return e ? atoi(e) : 1; }();
+    static const int narrow_env = [] { const char* e = getenv("DCP_GEMM_NARROW"); return e ? atoi(e) : 1; }();
+    const int narrow = g_gemm_narrow_override >= 0 ? g_gemm_narrow_override : narrow_env;
     const long tiles = (long)((M + kBM - 1) / kBM) * ((N + p.BN - 1) / p.BN) * (ksplit < 1 ? 1 : ksplit);
     if (narrow && p.BN == 128 && tiles < 100) p.BN = narrow >= 2 ? 32 : 64;
   }

@@ -101,6 +101,7 @@ class FusedConvNetTrainer:
         self.wg_parts = min(148, -(-P // 128))
         self.wg_scratch = torch.empty(self.wg_parts * 64 * 289, **f32)
         self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
+        self.fc1_overlap = os.environ.get("DCP_FC1_OVERLAP", "1") == "1"     # fc1 weight gradient on the side stream, next to the data gradient
         self.pool_fused = os.environ.get("DCP_POOL_FUSED", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
         self.off_bwd = (C.c_int * 9)(*[-((2 - r) * 26 + (2 - s)) for r in range(3) for s in range(3)])
@@ -207,11 +208,31 @@ class FusedConvNetTrainer:
         else:
             self._head_unfused(L, ck, s, p, g, bn, N, tr, step_ptr)
             ck(L.dcp_colsum(self.dh1.data_ptr(), g["fc1.bias"].data_ptr(), N, 128, 0, s()))
-        tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
         ar_late = "ar_late" in ab
-        ev0 = self._reduce_bucket(0) if ("b0" not in ab and not ar_late) else None
-        tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
-        if ar_late and "b0" not in ab:
+        ev_w = None
+        if self.fc1_overlap:
+            # fc1's weight gradient and data gradient both contract over K = 128 only: each is a short, latency-bound launch
+            # that leaves the GPU half idle, and neither needs the other - so the weight gradient runs on the side stream next to
+            # the data gradient (bucket 0's all-reduce and optimizer update wait for it, the convolution backward does not)
+            # (128-column tiles for this pair: 72 CTAs each, so both kernels are resident at once)
+            self.side.wait_stream(main)
+            tc._lib.dcp_gemm_set_narrow(0)
+            try:
+                with torch.cuda.stream(self.side):
+                    tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
+                    ev_w = torch.cuda.Event(); ev_w.record(self.side)
+                tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+            finally:
+                tc._lib.dcp_gemm_set_narrow(-1)
+            ev0 = None
+            if "b0" not in ab and self.be is not None:
+                # the side stream IS the communication stream: bucket 0's all-reduce queues behind the weight gradient there
+                ev0 = self._reduce_bucket(0)
+        else:
+            tc.gemm(self.dh1, self.pooled, g["fc1.weight"], None, 128, 9216, N, 128, 9216, 9216, 1, 1, False, 1)
+            ev0 = self._reduce_bucket(0) if ("b0" not in ab and not ar_late) else None
+            tc.gemm(self.dh1, p["fc1.weight"], self.dpooled, None, N, 9216, 128, 128, 9216, 9216, 0, 1, False, 1)
+        if ar_late and "b0" not in ab and not self.fc1_overlap:
             ev0 = self._reduce_bucket(0)
         # fc1.weight has been read for the last time: the optimizer update of everything in bucket 0 (97 % of the
         # parameters) runs on the side stream, behind that bucket's all-reduce, underneath the convolution backward
@@ -227,6 +248,8 @@ class FusedConvNetTrainer:
                 self.side.wait_stream(main)
             elif ev0 is not None:
                 main.wait_event(ev0); ev0 = None
+            if opt_stream is main and ev_w is not None:
+                main.wait_event(ev_w)
             if opt_stream is not None:
                 ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, opt_stream.cuda_stream))
             if opt_stream is self.side:
@@ -299,13 +322,15 @@ class FusedConvNetTrainer:
                 if "opt0end" in ab:
                     if ev0 is not None:
                         main.wait_event(ev0); ev0 = None
+                    if ev_w is not None:
+                        main.wait_event(ev_w)
                     _, (r0, n0, m0), _ = rows
                     ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r0, n0, m0, ent["hp"].data_ptr(), self.opt._kind, 0, s()))
                 # the one kernel that waits: all producers of all ranks -> average -> gradients + optimizer update of bucket 1
                 ck(L.dcp_dp_tail(self.be.handle, ent["table"].data_ptr() + 40 * r1, n1, m1, ent["hp"].data_ptr(), self.opt._kind,
                                  self.buckets[1].data_ptr(), self.dp_pay.data_ptr(), self.dp_slot, CH_TAIL, self.dp_blks, 2,
                                  self._row_sig(r1, n1), step_ptr, 0, s()))
-            for ev in (ev0, ev_opt0, ev_push):   # joins AFTER the last kernel: the side streams only have to finish with the step
+            for ev in (ev0, ev_opt0, ev_push, ev_w):   # joins AFTER the last kernel: the side streams only have to finish with the step
                 if ev is not None:
                     main.wait_event(ev)
             return
@@ -324,11 +349,11 @@ class FusedConvNetTrainer:
                     main.wait_event(ev)
             ent, _, (r1, n1, m1) = rows
             ck(L.dcp_optim_step(ent["table"].data_ptr() + 40 * r1, n1, m1, ent["hp"].data_ptr(), self.opt._kind, 0, s()))
-            for ev in (ev0, ev_opt0):
+            for ev in (ev0, ev_opt0, ev_w):
                 if ev is not None:
                     main.wait_event(ev)
         else:
-            for ev in (ev0, ev1a, ev1, ev_opt0):
+            for ev in (ev0, ev1a, ev1, ev_opt0, ev_w):
                 if ev is not None:
                     main.wait_event(ev)
             self.opt.step()

@@ -227,6 +227,9 @@ int dcp_gemm_bf16_persistent(const void* A, const void* B, void* out, const void
 int dcp_conv_bf16_persistent(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int stride, int Ho, int Wo, int Wb, int Hb, int Nb, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
 
 /* ---- csrc/ops/gemm_tc.cu ---- */
+// Host-side launch choice for wide, shallow fp32 / tf32 problems: 64-column tiles (twice the CTAs) when 1, 128-column when 0,
+// the DCP_GEMM_NARROW default when -1.  Affects the launches issued after the call from this process.
+void dcp_gemm_set_narrow(int v);
 int dcp_tc_gemm(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, cudaStream_t s);
 int dcp_tc_gemm_ex(const void* A, const void* B, void* out, const void* bias, int M, int N, int K, long lda, long ldb, long ldc, int a_mn, int b_mn, int dtype, int out_bf16, int bias_bf16, int relu, int ksplit, int x3, cudaStream_t s);
 int dcp_tc_conv(const void* x, const void* wmat, void* y, const void* bias, int N, int H, int W, int C, int Kout, int R, int S, int pad, int Ho, int Wo, int Wb, int Hb, int Nb, int dtype, int out_bf16, int bias_bf16, int relu, cudaStream_t s);
