@@ -101,6 +101,7 @@ class FusedConvNetTrainer:
         self.wg_parts = min(148, -(-P // 128))
         self.wg_scratch = torch.empty(self.wg_parts * 64 * 289, **f32)
         self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
+        self.early_side = os.environ.get("DCP_EARLY_SIDE", "1") == "1"       # filter flip + optimizer step counter on the side stream at the start of the step
         self.fc1_overlap = os.environ.get("DCP_FC1_OVERLAP", "1") == "1"     # fc1 weight gradient on the side stream, next to the data gradient
         self.pool_fused = os.environ.get("DCP_POOL_FUSED", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
@@ -175,6 +176,19 @@ class FusedConvNetTrainer:
             self.side.wait_stream(main)
             self.be.broadcast(self.bn_flat, 0, stream=self.side, chan=CH_DDP)
             ev_buf = torch.cuda.Event(); ev_buf.record(self.side)
+        # Two tiny launches that nothing in the forward pass needs - the data-gradient's copy of conv2's filter (taps flipped, channels
+        # swapped; conv2.weight may then be updated while the data-gradient is still running) and the optimizer's step counter - go
+        # to the side stream right away instead of sitting between the big kernels of the main stream; main picks them up with an
+        # event wait long after they finished.
+        ev_early = None
+        early = self.early_side and rows is not None and "opt0main" not in ab and "opt0end" not in ab and ev_buf is None
+        if early:
+            self.side.wait_stream(main)
+            with torch.cuda.stream(self.side):
+                ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
+                K._push_hyper(self.opt, self.opt.param_groups[0], rows[0])
+                ck(L.dcp_optim_advance(rows[0]["hp"].data_ptr(), s()))
+                ev_early = torch.cuda.Event(); ev_early.record(self.side)
         # ---- forward
         ck(L.dcp_convnet_conv1_fwd(self.x.data_ptr(), p["conv1.weight"].data_ptr(), p["conv1.bias"].data_ptr(), self.a1.data_ptr(), N, s()))
         if self.pool_fused:
@@ -188,7 +202,8 @@ class FusedConvNetTrainer:
             ck(L.dcp_convnet_pool_fwd(self.a2.data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(), N, net.dropout1.p, self.seed, 1, step_ptr, tr, s()))
         # the data-gradient's copy of conv2's filter (taps flipped, channels swapped) is taken here, while the filter is hot in L2:
         # conv2.weight may then be updated by the optimizer while the data-gradient is still running
-        ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
+        if not early:
+            ck(tc._lib.dcp_flip_weights(p["conv2.weight"].data_ptr(), self.wt2.data_ptr(), 64, 3, 3, 32, 0, s()))
         tc.linear_fwd(self.pooled, p["fc1.weight"], p["fc1.bias"], self.h1, False)
         if ev_buf is not None:
             main.wait_event(ev_buf)
@@ -239,8 +254,11 @@ class FusedConvNetTrainer:
         ev_opt0 = None
         if rows is not None:
             ent, (r0, n0, m0), _ = rows
-            K._push_hyper(self.opt, self.opt.param_groups[0], ent)
-            ck(L.dcp_optim_advance(ent["hp"].data_ptr(), s()))
+            if ev_early is None:
+                K._push_hyper(self.opt, self.opt.param_groups[0], ent)
+                ck(L.dcp_optim_advance(ent["hp"].data_ptr(), s()))
+            else:
+                main.wait_event(ev_early)       # flipped filter + step counter: finished a forward pass ago
             opt_stream = main if "opt0main" in ab else self.side
             if "opt0end" in ab and dp_tail:
                 opt_stream = None        # measurement: bucket 0's update at the very end of the main stream, between the last push and the wait

@@ -159,3 +159,38 @@ def _single(rank, world, port):
 
 def test_world_size_one_backend():
     dcp.spawn(_single, args=(1, free_port()), nprocs=1, join=True)
+
+
+def _channels_worker(rank, world, port):
+    """One-shot all_reduces of ordinary tensors on three channels from three streams AT ONCE (what a small DDP bucket on the
+    communication stream, a SyncBatchNorm statistic on the compute stream and a user collective amount to): every channel owns
+    its staging slots, so nobody's payload lands in somebody else's."""
+    from distributed_compute_pytorch_b200.parallel.p2p_backend import CH_BN, CH_DDP, CH_USER
+    torch.cuda.set_device(rank)
+    dist = init(rank, world, port, "nccl")
+    dev = torch.device("cuda", rank)
+    be = dist.distributed._world().cuda
+    R = dist.ReduceOp
+    streams = [torch.cuda.Stream(dev) for _ in range(3)]
+    chans = (CH_DDP, CH_BN, CH_USER)
+    n = 2048
+    for it in range(100):
+        ts = []
+        for k, (st, ch) in enumerate(zip(streams, chans)):
+            with torch.cuda.stream(st):
+                t = torch.full((n,), float((rank + 1) * (k + 1) + it), device=dev)
+                be.all_reduce(t, R.SUM, stream=st, algo=1, chan=ch)
+                ts.append(t)
+        torch.cuda.synchronize()
+        for k, t in enumerate(ts):
+            exp = float(sum((r + 1) * (k + 1) + it for r in range(world)))
+            assert torch.equal(t, torch.full((n,), exp, device=dev)), (it, k, t[:4].tolist(), exp)
+    be.check_health()
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.multigpu
+def test_concurrent_channels_do_not_share_staging():
+    world = min(_ngpu(), 4)
+    dcp.spawn(_channels_worker, args=(world, free_port()), nprocs=world, join=True)
