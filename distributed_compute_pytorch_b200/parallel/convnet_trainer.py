@@ -101,7 +101,10 @@ class FusedConvNetTrainer:
         self.wg_parts = min(148, -(-P // 128))
         self.wg_scratch = torch.empty(self.wg_parts * 64 * 289, **f32)
         self.flat_wgrad = os.environ.get("DCP_FLAT_WGRAD", "1") == "1"
-        self.early_side = os.environ.get("DCP_EARLY_SIDE", "1") == "1"       # filter flip + optimizer step counter on the side stream at the start of the step
+        # filter flip, dropout step counter and optimizer step counter on the side stream at the start of the step.  Default: single GPU
+        # only (0.1296 -> 0.1251 ms); with two GPUs, where the side stream is the communication stream, the one measurement taken was
+        # slower (0.143 -> 0.151 ms), so the data-parallel step keeps them on the main stream unless DCP_EARLY_SIDE=1
+        self.early_side = os.environ.get("DCP_EARLY_SIDE", "1" if self.be is None else "0") == "1"
         self.fc1_overlap = os.environ.get("DCP_FC1_OVERLAP", "1") == "1"     # fc1 weight gradient on the side stream, next to the data gradient
         self.pool_fused = os.environ.get("DCP_POOL_FUSED", "1") == "1"
         self.off_fwd = (C.c_int * 9)(*[r * 26 + s for r in range(3) for s in range(3)])
@@ -162,7 +165,6 @@ class FusedConvNetTrainer:
         g = {n: t.grad for n, t in p.items()}
         step_ptr = K.graph_step.data_ptr()
         tr = int(self.training)
-        ck(L.dcp_counter_advance(step_ptr, s()))
         ab = self.ablate
         self._conv2_tail = None
         main = torch.cuda.current_stream(self.dev)
@@ -180,8 +182,11 @@ class FusedConvNetTrainer:
         # swapped; conv2.weight may then be updated while the data-gradient is still running) and the optimizer's step counter - go
         # to the side stream right away instead of sitting between the big kernels of the main stream; main picks them up with an
         # event wait long after they finished.
-        ev_early = None
+        ev_early = ev_ctr = None
         early = self.early_side and rows is not None and "opt0main" not in ab and "opt0end" not in ab and ev_buf is None
+        # (the dropout step counter stays at the head of the main stream: moved to the side stream as well, conv2 had to wait for an
+        # event between conv1 and itself, which breaks their programmatic dependent launch - 0.1251 -> 0.1305 ms)
+        ck(L.dcp_counter_advance(step_ptr, s()))
         if early:
             self.side.wait_stream(main)
             with torch.cuda.stream(self.side):
@@ -191,6 +196,8 @@ class FusedConvNetTrainer:
                 ev_early = torch.cuda.Event(); ev_early.record(self.side)
         # ---- forward
         ck(L.dcp_convnet_conv1_fwd(self.x.data_ptr(), p["conv1.weight"].data_ptr(), p["conv1.bias"].data_ptr(), self.a1.data_ptr(), N, s()))
+        if ev_ctr is not None:
+            main.wait_event(ev_ctr)
         if self.pool_fused:
             # conv2 + bias + ReLU + 2x2 max-pool + channel dropout in one kernel: the 22 MB conv2 activation never reaches memory
             ck(L.dcp_conv_flat_pool_tc(self.a1.data_ptr(), p["conv2.weight"].data_ptr(), self.pooled.data_ptr(), self.arg.data_ptr(),
