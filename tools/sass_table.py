@@ -8,7 +8,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 OBJ = os.path.join(ROOT, "build", "obj")
 OUT = os.path.join(ROOT, "docs", "sass")
 FILES = sorted(f[:-len(".cu.o")] for f in os.listdir(OBJ) if f.endswith(".cu.o")) if os.path.isdir(OBJ) else []   # every CUDA object of the library
-COLS = [("UTC*MMA", r"UTC[A-Z]*MMA"), ("LDTM", r"\bLDTM"), ("UTMALDG", r"UTMALDG"), ("UTCBAR", r"UTCBAR"), ("SYNCS", r"\bSYNCS"),
+COLS = [("UTC*MMA", r"UTC[A-Z]*MMA"), ("LDTM", r"\bLDTM"), ("UTMALDG", r"UTMALDG"), ("UTMASTG / UBLKRED (TMA store / bulk reduce-add)", r"(UTMASTG|UBLKRED|UTMAREDG)"),
+        ("UTCBAR", r"UTCBAR"), ("SYNCS", r"\bSYNCS"), ("packed f32x2 / FMNMX3", r"\b(FFMA2|FMUL2|FADD2|FMNMX3)"),
         ("multimem (LDGMC/STGMC/REDGMC)", r"(LDGMC|STGMC|REDGMC)"), ("PDL (ACQBULK/PREEXIT)", r"(ACQBULK|PREEXIT)"),
         ("cluster (UCGABAR/CGAERRBAR... .CLUSTER / remote smem)", r"(UCGABAR|\.CLUSTER|MAPA|CGABAR)"), ("HMMA (legacy)", r"\bHMMA")]
 
@@ -51,7 +52,7 @@ def main():
             rows.append((f, short, c))
     with open(os.path.join(OUT, "README.md"), "w") as w:
         w.write("# SASS evidence (cuobjdump -sass of the sm_100a objects; regenerate with `python tools/sass_table.py`)\n\n")
-        w.write("Mnemonics that prove the Blackwell-native paths (B200_PROFILING.md): `UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTMALDG` = TMA tensor load, "
+        w.write("Mnemonics that prove the Blackwell-native paths (B200_PROFILING.md): `UTCHMMA` = tcgen05.mma, `LDTM` = tcgen05.ld, `UTMALDG` = TMA tensor load, `UTMASTG` = TMA tensor store, `UBLKRED` = cp.reduce.async.bulk (bulk reduce-add), `FFMA2` / `FMUL2` / `FADD2` / `FMNMX3` = packed f32x2 arithmetic and three-input max, "
                 "`UTCBAR` = tcgen05.commit, `SYNCS` = mbarrier; `LDGMC` / `STGMC` / `REDGMC` = multimem.ld_reduce / multimem.red over the NVSwitch "
                 "multicast mapping (multimem.st compiles to an ordinary 16-byte store whose address is the multicast VA, so it has no mnemonic of its own); `ACQBULK` / `PREEXIT` = griddepcontrol.wait / launch_dependents (programmatic dependent launch); cluster column = thread-block-cluster "
                 "barrier / distributed-shared-memory mapping ops of the head kernel.  No kernel contains legacy `HMMA` (mma.sync).\n\n")
