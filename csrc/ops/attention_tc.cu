@@ -718,10 +718,16 @@ int dcp_attn_fwd(const void* qkv, void* out, float* lse, int B, int T, int H, cu
   p.T = T; p.H = H; p.C = C; p.BH = B * H; p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.out = static_cast<__nv_bfloat16*>(out); p.lse = lse; p.trace = g_attn_ftrace; p.trace_x = g_attn_trace_x;
   const size_t smem = (size_t)kTileBytes * (1 + kRing + 2) + sizeof(AttnBars) + 1024;
-  static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  static int sms = 0;
-  if (sms == 0) { int dev = 0; DCP_CUDA_CHECK(cudaGetDevice(&dev)); DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)); }
+  // per device (a process may drive several GPUs): the shared-memory opt-in of the kernel and the SM count
+  static int sms_of[64] = {0};
+  int dev = 0;
+  DCP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { dcp_set_error("attention: device index %d out of range", dev); return -1; }
+  if (sms_of[dev] == 0) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_fwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms_of[dev], cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int sms = sms_of[dev];
   const int items = B * H * (T / kBQ);
   static int per_sm = -1;           // DCP_ATTN_FWD_CTAS_PER_SM: 0 = one CTA per item (no persistence); default two persistent CTAs per SM
   if (per_sm < 0) { const char* e = getenv("DCP_ATTN_FWD_CTAS_PER_SM"); per_sm = e ? atoi(e) : 2; }
@@ -750,10 +756,16 @@ int dcp_attn_bwd(const void* qkv, const void* out, const void* dout, const float
   p.T = T; p.H = H; p.C = C; p.BH = B * H; p.scale = 0.125f; p.scale_log2 = 0.125f * 1.4426950408889634f;
   p.lse = lse; p.delta = delta; p.dq_acc = dq_acc; p.dqkv = static_cast<__nv_bfloat16*>(dqkv); p.trace = g_attn_trace; p.trace_x = g_attn_trace_x; p.trace_y = g_attn_trace_y;
   const size_t smem = (size_t)kTileBytes * 14 + sizeof(AttnBwdBars) + 1024;
-  static bool attr = false;
-  if (!attr) { DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = true; }
-  static int sms = 0;
-  if (sms == 0) { int dev = 0; DCP_CUDA_CHECK(cudaGetDevice(&dev)); DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev)); }
+  // per device (a process may drive several GPUs): the shared-memory opt-in of the kernel and the SM count
+  static int sms_of[64] = {0};
+  int dev = 0;
+  DCP_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { dcp_set_error("attention: device index %d out of range", dev); return -1; }
+  if (sms_of[dev] == 0) {
+    DCP_CUDA_CHECK(cudaFuncSetAttribute(k_attn_bwd, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    DCP_CUDA_CHECK(cudaDeviceGetAttribute(&sms_of[dev], cudaDevAttrMultiProcessorCount, dev));
+  }
+  const int sms = sms_of[dev];
   const int items = B * H * (T / kBK);
   DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_bwd, dim3(items < sms ? items : sms), dim3(kAttnThreads), smem, s, mq, md, mg, p));
   DCP_CUDA_CHECK(dcp_launch_pdl(k_attn_dq_convert, dim3((unsigned)(B * H * (T / kBQ))), dim3(256), 0, s, static_cast<const float*>(dq_acc), static_cast<__nv_bfloat16*>(dqkv), T, H));

@@ -87,6 +87,10 @@ class FusedShardedOptimizer:
         ddp._bucket_override = self._on_bucket_ready
         self._sync_hyper()
         self.refresh_shadows()
+        if self.shadow_bufs:
+            # parameters written through load_state_dict() must reach the shadows too (in-place writes the module system does not
+            # see - p.data.copy_() by hand - need an explicit refresh_shadows())
+            self._load_hook = ddp.module.register_load_state_dict_post_hook(lambda module, incompatible: self.refresh_shadows())
 
     def refresh_shadows(self) -> None:
         """Re-cast every flat parameter buffer into its low-precision shadow (after loading a checkpoint into the parameters)."""
@@ -94,6 +98,9 @@ class FusedShardedOptimizer:
             K._chk(self._lib.dcp_cast_from_f32(pbuf.data_ptr(), sbuf.data_ptr(), pbuf.numel(), K._DT[sbuf.dtype], K._stream()))
 
     def close(self) -> None:
+        if getattr(self, "_load_hook", None) is not None:
+            self._load_hook.remove()
+            self._load_hook = None
         if self.shadow_bufs:
             K.drop_shadows([p.data for b in self.ddp._buckets for p in b.params])
             self.shadow_bufs = []

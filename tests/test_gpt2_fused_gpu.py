@@ -132,6 +132,11 @@ def _shadow_worker(rank, world, port):
         sh = K._SHADOWS[(w.data_ptr(), torch.bfloat16)][0]
         assert torch.equal(sh, w.detach().to(torch.bfloat16))                          # ... and the shadow followed it
         assert K._lowp(w.data, torch.bfloat16).data_ptr() == sh.data_ptr()             # which is what the Linear multiplies with
+    # weights written through load_state_dict reach the shadow as well
+    sd = {k: torch.full_like(v, 0.25) for k, v in model.state_dict().items()}
+    model.load_state_dict(sd)
+    torch.cuda.synchronize()
+    assert torch.equal(K._SHADOWS[(w.data_ptr(), torch.bfloat16)][0], torch.full_like(w, 0.25, dtype=torch.bfloat16))
     opt.close()
     assert (w.data_ptr(), torch.bfloat16) not in K._SHADOWS
     dist.destroy_process_group()
